@@ -1,0 +1,172 @@
+/*
+ * rq_engine.h — C ABI of the B200-native residual-quantization engine.
+ *
+ * Drop-in boundary for the quantization hot path of AdamLTy/RQ-VAE-Recommender.  The
+ * reference is pure Python with no FFI of its own; these entry points
+ * are what a binding for that path attaches to.  Each one names the reference code it
+ * replaces (paths relative to the reference root).  INTEGRATION.md shows the ctypes stub.
+ *
+ * Conventions
+ *   - All pointers are DEVICE pointers unless the function name ends in `_host`.
+ *   - Row-major, contiguous.  fp32 values, int64 indices (the reference's dtypes).
+ *   - `stream` is a cudaStream_t (0 = legacy default stream).  Nothing here synchronises
+ *     the host except the `_host` functions, and nothing allocates except those and
+ *     functions that take an explicit workspace.  All launches are CUDA-graph capturable.
+ *   - Return value: 0 on success; RQ_ERR_* (<0) for argument errors; a positive
+ *     cudaError_t for CUDA failures.  rq_last_error() returns a thread-local message.
+ *   - There is no CPU implementation behind any of these.
+ */
+#ifndef RQ_ENGINE_H_
+#define RQ_ENGINE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+typedef void* rq_stream_t; /* cudaStream_t */
+
+#define RQ_ABI_VERSION 1
+
+/* modules/quantize.py:16-20 (QuantizeForwardMode); 0 = the `not self.training` branch :148-150 */
+#define RQ_MODE_EVAL 0
+#define RQ_MODE_GUMBEL_SOFTMAX 1
+#define RQ_MODE_STE 2
+#define RQ_MODE_ROTATION_TRICK 3
+/* modules/quantize.py:23-25 (QuantizeDistance) */
+#define RQ_DIST_L2 1
+#define RQ_DIST_COSINE 2
+/* kernel family selection */
+#define RQ_IMPL_AUTO 0    /* tcgen05 kernel when the shape is supported, else exact SIMT */
+#define RQ_IMPL_SIMT 1    /* fp32 CUDA-core kernel (exact expanded form), any shape */
+#define RQ_IMPL_TCGEN05 2 /* tensor-core candidate search + fp32 rescoring; error if unsupported */
+
+#define RQ_ERR_INVALID_ARGUMENT (-1)
+#define RQ_ERR_UNSUPPORTED_SHAPE (-2)
+#define RQ_ERR_NULL_POINTER (-3)
+#define RQ_ERR_WORKSPACE_TOO_SMALL (-4)
+#define RQ_ERR_NO_DEVICE (-5)
+
+int rq_abi_version(void);
+const char* rq_last_error(void);
+/* Number of kernel launches issued through this library by the calling process
+ * (bench.py reports it as `gpu_launches`). */
+uint64_t rq_launch_count(void);
+/* Returns 1 if (D, K, L, mode, distance) is served by the tcgen05 kernel. */
+int rq_tcgen05_supported(int D, int K, int L, int mode, int distance);
+
+/*
+ * Fused L-level residual quantisation, forward.
+ * Replaces the level loop of RqVae.get_semantic_ids (modules/rqvae.py:121-131) together with
+ * Quantize.forward (modules/quantize.py:105-150), QuantizeLoss (modules/loss.py:39-42),
+ * efficient_rotation_trick_transform (modules/quantize.py:34-45) and gumbel_softmax_sample
+ * (distributions/gumbel.py:7-17).
+ *
+ *   x           [B, D]     latents (output of RqVae.encode)
+ *   codebooks   [L, K, D]  EFFECTIVE codebooks, i.e. out_proj(embedding.weight) (quantize.py:105)
+ *   gumbel_u    [L, B, K]  the uniform draws of sample_gumbel (gumbel.py:9) or NULL; when NULL
+ *                          and mode == GUMBEL the kernel draws Philox4x32-10 noise from
+ *                          (seed, offset).  Ignored by the other modes.
+ *   emb_out     [L, B, D]  `quantized.embeddings` per level, or NULL (ids-only)
+ *   residuals   [L, B, D]  input of each level (rqvae.py:125), or NULL
+ *   ids         [L, B]     argmin indices, first index wins ties (quantize.py:121); required
+ *   loss        [B]        sum over levels of emb_loss + beta*query_loss, or NULL
+ */
+int rq_quantize_forward(const float* x, const float* codebooks, int64_t B, int D, int K, int L,
+                        int mode, int distance, float beta, float temperature,
+                        const float* gumbel_u, uint64_t seed, uint64_t offset,
+                        float* emb_out, float* residuals, int64_t* ids, float* loss,
+                        int impl, rq_stream_t stream);
+
+/*
+ * Fused backward of the above (the reference relies on autograd).
+ *   g_emb [L,B,D], g_res [L,B,D], g_loss [B]  upstream gradients (any may be NULL = zero)
+ *   residuals, ids                             saved from the forward
+ *   g_x [B, D]          gradient w.r.t. the latents (written)
+ *   g_codebooks [L,K,D] gradient w.r.t. the effective codebooks (overwritten, not accumulated)
+ * distance must be RQ_DIST_L2 for GUMBEL_SOFTMAX (the only mode whose gradient sees `dist`).
+ */
+int rq_quantize_backward(const float* g_emb, const float* g_res, const float* g_loss,
+                         const float* residuals, const int64_t* ids, const float* codebooks,
+                         int64_t B, int D, int K, int L, int mode, float beta, float temperature,
+                         const float* gumbel_u, uint64_t seed, uint64_t offset,
+                         float* g_x, float* g_codebooks, rq_stream_t stream);
+
+/*
+ * One k-means assignment + accumulation pass.  Replaces init/kmeans.py:41-57 (the [B,K,D]
+ * broadcast, argmin, and the per-cluster masked means' numerators).
+ *   x [B,D], centroids [K,D]
+ *   assign [B] int64     in: previous assignment when has_prev != 0; out: new assignment
+ *   sums [K,D] fp32, counts [K] int64   (overwritten)
+ *   n_changed [1] int64  number of rows whose assignment changed (B when !has_prev)
+ */
+int rq_kmeans_assign_accumulate(const float* x, const float* centroids, int64_t B, int D, int K,
+                                int64_t* assign, int has_prev, float* sums, int64_t* counts,
+                                int64_t* n_changed, int impl, rq_stream_t stream);
+
+/*
+ * Centroid update from (all-reduced) sums/counts: c_k = sums_k / counts_k for non-empty
+ * clusters (kmeans.py:57); empty clusters keep their old value and are reported so that the
+ * host re-seeds them (kmeans.py:51-53).
+ *   max_shift [1] fp32   max_k ||c_new - c_old||_2   (kmeans.py:67)
+ *   n_empty [1] int64, empty_ids [K] int64 (first n_empty entries valid, ascending)
+ */
+int rq_kmeans_update(const float* sums, const int64_t* counts, float* centroids, int D, int K,
+                     float* max_shift, int64_t* n_empty, int64_t* empty_ids, rq_stream_t stream);
+
+/*
+ * Dedup column of the corpus id table.  Replaces the O(N^2) hit matrices of
+ * SemanticIdTokenizer.precompute_corpus_ids (modules/tokenizer/semids.py:86-99):
+ * dedup[i] = number of j < i with sem_ids[j,:] == sem_ids[i,:].
+ *   sem_ids [N, L] int64 with arbitrary element strides (the [L,B]-memory view is accepted)
+ *   table   [N, L+1] int64 contiguous: [sem_ids | dedup]
+ *   base_counts/out_counts: optional (may be NULL) — multi-rank use, see DESIGN.md.
+ */
+int64_t rq_corpus_table_workspace_bytes(int64_t N, int L);
+int rq_corpus_table(const int64_t* sem_ids, int64_t stride_n, int64_t stride_l, int64_t N, int L,
+                    int64_t codebook_size, int64_t* table, void* workspace, int64_t workspace_bytes,
+                    rq_stream_t stream);
+
+/*
+ * Prefix index over the cached id table.  Replaces SemanticIdTokenizer.exists_prefix
+ * (semids.py:103-120): out[q] = any_i(table[i, :p] == queries[q, :p]).
+ *   rq_prefix_index_build: sorted_keys [N] uint64 <- packed table[:, :p] (radix codebook_size+? see .cu)
+ *   rq_prefix_exists: binary search, out [Q] uint8 (bool)
+ */
+int64_t rq_prefix_index_workspace_bytes(int64_t N);
+int rq_prefix_index_build(const int64_t* table, int64_t N, int row_stride, int p, int64_t radix,
+                          uint64_t* sorted_keys, void* workspace, int64_t workspace_bytes,
+                          rq_stream_t stream);
+int rq_prefix_exists(const uint64_t* sorted_keys, int64_t N, const int64_t* queries, int64_t Q, int p,
+                     int64_t radix, uint8_t* out, rq_stream_t stream);
+
+/*
+ * Sequence tokenisation by table gather.  Replaces _tokenize_seq_batch_from_cached and the
+ * padding fill (semids.py:122-123, 137-141): out[b, n*W + w] = mask[b,n] ? table[ids[b,n], w] : -1.
+ *   table is [n_rows, W]; negative item ids wrap (torch indexing); seq_mask [n_tokens] may be
+ *   NULL (no padding fill).
+ */
+int rq_gather_tokens(const int64_t* table, int64_t n_rows, int W, const int64_t* item_ids,
+                     const uint8_t* seq_mask, int64_t n_tokens, int64_t* out, rq_stream_t stream);
+
+/*
+ * Host-buffer convenience entry (the call a non-torch integrator makes): copies `x_host`
+ * (pageable or pinned) to the device, runs rq_quantize_forward in RQ_MODE_EVAL, copies the ids
+ * (and loss when non-NULL) back and synchronises `stream`.  Device scratch comes from the
+ * stream-ordered allocator (cudaMallocAsync).  `codebooks` is a DEVICE pointer.
+ */
+int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B, int D, int K, int L,
+                         int distance, int64_t* ids_host, float* loss_host, int impl,
+                         rq_stream_t stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* RQ_ENGINE_H_ */

@@ -1,0 +1,148 @@
+// extern "C" entry points of librqengine.so (see include/rq_engine.h for the contract).
+#include <stdarg.h>
+#include <string.h>
+
+#include "rq_common.cuh"
+#include "rq_kernels.h"
+
+namespace rq {
+
+static thread_local char g_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int sm_count() {
+    static int cached = 0;
+    if (!cached) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+        if (cached <= 0) cached = 148;
+    }
+    return cached;
+}
+
+static bool pow2_dim(int D) { return D == 4 || D == 8 || D == 16 || D == 32 || D == 64 || D == 128; }
+
+}  // namespace rq
+
+using namespace rq;
+
+extern "C" int rq_abi_version(void) { return RQ_ABI_VERSION; }
+extern "C" const char* rq_last_error(void) { return g_err; }
+extern "C" uint64_t rq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+extern "C" int rq_tcgen05_supported(int D, int K, int L, int mode, int distance) {
+    return tc_supported(D, K, L, mode, distance) ? 1 : 0;
+}
+
+extern "C" int rq_quantize_forward(const float* x, const float* codebooks, int64_t B, int D, int K, int L, int mode,
+                                   int distance, float beta, float temperature, const float* gumbel_u,
+                                   uint64_t seed, uint64_t offset, float* emb_out, float* residuals, int64_t* ids,
+                                   float* loss, int impl, rq_stream_t stream) {
+    RQ_CHECK_ARG(B >= 0 && K >= 1 && L >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_forward: need B >= 0, K >= 1, L >= 1");
+    RQ_CHECK_ARG(pow2_dim(D), RQ_ERR_UNSUPPORTED_SHAPE, "rq_quantize_forward: unsupported embed_dim D=%d (4..128, power of 2)", D);
+    RQ_CHECK_ARG(mode >= RQ_MODE_EVAL && mode <= RQ_MODE_ROTATION_TRICK, RQ_ERR_INVALID_ARGUMENT,
+                 "Unsupported Quantize forward mode.");
+    RQ_CHECK_ARG(distance == RQ_DIST_L2 || distance == RQ_DIST_COSINE, RQ_ERR_INVALID_ARGUMENT,
+                 "Unsupported Quantize distance mode.");
+    RQ_CHECK_ARG(!(mode == RQ_MODE_GUMBEL_SOFTMAX && !(temperature > 0.f)), RQ_ERR_INVALID_ARGUMENT,
+                 "rq_quantize_forward: temperature must be > 0");
+    if (B == 0) return 0;
+    RQ_CHECK_ARG(x && codebooks && ids, RQ_ERR_NULL_POINTER, "rq_quantize_forward: x, codebooks and ids are required");
+    FwdParams p;
+    p.x = x; p.cb = codebooks; p.B = B; p.K = K; p.L = L; p.mode = mode; p.dist = distance;
+    p.beta = beta; p.temp = temperature; p.gu = gumbel_u; p.seed = seed; p.offset = offset;
+    p.emb = emb_out; p.res = residuals; p.ids = ids; p.loss = loss; p.KC = 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool tc_ok = tc_supported(D, K, L, mode, distance);
+    if (impl == RQ_IMPL_TCGEN05) {
+        RQ_CHECK_ARG(tc_ok, RQ_ERR_UNSUPPORTED_SHAPE,
+                     "rq_quantize_forward: (D=%d,K=%d,L=%d,mode=%d,dist=%d) is not served by the tcgen05 family", D, K, L,
+                     mode, distance);
+        return quantize_forward_tc(p, D, st);
+    }
+    if (impl == RQ_IMPL_AUTO && tc_ok) return quantize_forward_tc(p, D, st);
+    RQ_CHECK_ARG(impl == RQ_IMPL_AUTO || impl == RQ_IMPL_SIMT, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_forward: bad impl %d", impl);
+    return quantize_forward_simt(p, D, st);
+}
+
+extern "C" int rq_quantize_backward(const float* g_emb, const float* g_res, const float* g_loss,
+                                    const float* residuals, const int64_t* ids, const float* codebooks, int64_t B,
+                                    int D, int K, int L, int mode, float beta, float temperature,
+                                    const float* gumbel_u, uint64_t seed, uint64_t offset, float* g_x,
+                                    float* g_codebooks, rq_stream_t stream) {
+    RQ_CHECK_ARG(B >= 0 && K >= 1 && L >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_backward: need B >= 0, K >= 1, L >= 1");
+    RQ_CHECK_ARG(pow2_dim(D), RQ_ERR_UNSUPPORTED_SHAPE, "rq_quantize_backward: unsupported embed_dim D=%d", D);
+    RQ_CHECK_ARG(mode >= RQ_MODE_EVAL && mode <= RQ_MODE_ROTATION_TRICK, RQ_ERR_INVALID_ARGUMENT,
+                 "Unsupported Quantize forward mode.");
+    RQ_CHECK_ARG(g_codebooks && (g_x || B == 0), RQ_ERR_NULL_POINTER, "rq_quantize_backward: g_x and g_codebooks are required");
+    RQ_CHECK_ARG(B == 0 || (residuals && ids && codebooks), RQ_ERR_NULL_POINTER,
+                 "rq_quantize_backward: residuals, ids and codebooks are required");
+    BwdParams p;
+    p.g_emb = g_emb; p.g_res = g_res; p.g_loss = g_loss; p.res = residuals; p.ids = ids; p.cb = codebooks;
+    p.B = B; p.K = K; p.L = L; p.mode = mode; p.beta = beta; p.g_x = g_x; p.g_cb = g_codebooks;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (mode == RQ_MODE_GUMBEL_SOFTMAX) {
+        RQ_CHECK_ARG(temperature > 0.f, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_backward: temperature must be > 0");
+        return quantize_backward_gumbel(p, D, temperature, gumbel_u, seed, offset, st);
+    }
+    return quantize_backward_simt(p, D, st);
+}
+
+extern "C" int rq_kmeans_assign_accumulate(const float* x, const float* centroids, int64_t B, int D, int K,
+                                           int64_t* assign, int has_prev, float* sums, int64_t* counts,
+                                           int64_t* n_changed, int impl, rq_stream_t stream) {
+    RQ_CHECK_ARG(B >= 0 && K >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_kmeans_assign_accumulate: need B >= 0, K >= 1");
+    RQ_CHECK_ARG(pow2_dim(D), RQ_ERR_UNSUPPORTED_SHAPE, "rq_kmeans_assign_accumulate: unsupported D=%d", D);
+    RQ_CHECK_ARG(sums && counts && n_changed && centroids, RQ_ERR_NULL_POINTER, "rq_kmeans_assign_accumulate: null pointer");
+    RQ_CHECK_ARG(B == 0 || (x && assign), RQ_ERR_NULL_POINTER, "rq_kmeans_assign_accumulate: null pointer");
+    (void)impl;
+    KmeansParams p;
+    p.x = x; p.centroids = centroids; p.B = B; p.K = K; p.assign = assign; p.has_prev = has_prev;
+    p.sums = sums; p.counts = (unsigned long long*)counts; p.n_changed = (unsigned long long*)n_changed; p.KC = 0;
+    return kmeans_assign_accumulate_simt(p, D, (cudaStream_t)stream);
+}
+
+extern "C" int rq_kmeans_update(const float* sums, const int64_t* counts, float* centroids, int D, int K,
+                                float* max_shift, int64_t* n_empty, int64_t* empty_ids, rq_stream_t stream) {
+    RQ_CHECK_ARG(K >= 1 && D >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_kmeans_update: need K >= 1, D >= 1");
+    RQ_CHECK_ARG(sums && counts && centroids && max_shift && n_empty && empty_ids, RQ_ERR_NULL_POINTER,
+                 "rq_kmeans_update: null pointer");
+    return kmeans_update(sums, counts, centroids, D, K, max_shift, n_empty, empty_ids, (cudaStream_t)stream);
+}
+
+extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B, int D, int K, int L,
+                                    int distance, int64_t* ids_host, float* loss_host, int impl,
+                                    rq_stream_t stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    RQ_CHECK_ARG(B >= 0, RQ_ERR_INVALID_ARGUMENT, "rq_semantic_ids_host: B < 0");
+    if (B == 0) return 0;
+    RQ_CHECK_ARG(x_host && codebooks && ids_host, RQ_ERR_NULL_POINTER, "rq_semantic_ids_host: null pointer");
+    float* dx = nullptr;
+    int64_t* dids = nullptr;
+    float* dloss = nullptr;
+    RQ_CUDA(cudaMallocAsync((void**)&dx, (size_t)B * D * sizeof(float), st));
+    RQ_CUDA(cudaMallocAsync((void**)&dids, (size_t)L * B * sizeof(int64_t), st));
+    if (loss_host) RQ_CUDA(cudaMallocAsync((void**)&dloss, (size_t)B * sizeof(float), st));
+    RQ_CUDA(cudaMemcpyAsync(dx, x_host, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, st));
+    int rc = rq_quantize_forward(dx, codebooks, B, D, K, L, RQ_MODE_EVAL, distance, 0.25f, 1.0f, nullptr, 0, 0,
+                                 nullptr, nullptr, dids, dloss, impl, stream);
+    if (rc == 0) {
+        cudaError_t e = cudaMemcpyAsync(ids_host, dids, (size_t)L * B * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess && loss_host)
+            e = cudaMemcpyAsync(loss_host, dloss, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) { set_error("rq_semantic_ids_host: D2H copy failed: %s", cudaGetErrorString(e)); rc = (int)e; }
+    }
+    cudaFreeAsync(dx, st);
+    cudaFreeAsync(dids, st);
+    if (dloss) cudaFreeAsync(dloss, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (rc == 0 && e != cudaSuccess) { set_error("rq_semantic_ids_host: %s", cudaGetErrorString(e)); rc = (int)e; }
+    return rc;
+}

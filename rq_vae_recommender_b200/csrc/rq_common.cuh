@@ -1,0 +1,78 @@
+// Shared helpers for the rq-engine CUDA translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <atomic>
+
+#include "../../include/rq_engine.h"
+
+namespace rq {
+
+void set_error(const char* fmt, ...);
+extern std::atomic<uint64_t> g_launches;
+
+#define RQ_CHECK_ARG(cond, code, ...)     \
+    do {                                  \
+        if (!(cond)) {                    \
+            ::rq::set_error(__VA_ARGS__); \
+            return (code);                \
+        }                                 \
+    } while (0)
+
+#define RQ_CUDA(expr)                                                                      \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            ::rq::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                            __LINE__);                                                     \
+            return (int)_e;                                                                \
+        }                                                                                  \
+    } while (0)
+
+// Call after every kernel launch: counts it and surfaces launch-configuration errors.
+#define RQ_LAUNCHED()                                                                 \
+    do {                                                                              \
+        ::rq::g_launches.fetch_add(1, std::memory_order_relaxed);                     \
+        cudaError_t _e = cudaPeekAtLastError();                                       \
+        if (_e != cudaSuccess) {                                                      \
+            ::rq::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), \
+                            __FILE__, __LINE__);                                      \
+            return (int)_e;                                                           \
+        }                                                                             \
+    } while (0)
+
+int sm_count();
+
+// ---- small device helpers -------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    // REDG.E.ADD.F32x4 — one L2 reduction per 16 bytes (sm_90+)
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+// Philox4x32-10 (Salmon et al. 2011).  Counter = (c0,c1,c2,c3), key = (k0,k1).
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u;
+        k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+// 24-bit uniform in [0,1), the granularity torch.rand uses for fp32
+__device__ __forceinline__ float u01(uint32_t r) { return (float)(r >> 8) * (1.0f / 16777216.0f); }
+
+// gumbel(0,1) from a uniform draw — distributions/gumbel.py:9-10 (eps = 1e-20)
+__device__ __forceinline__ float gumbel_from_u(float u) { return -logf(-logf(u + 1e-20f) + 1e-20f); }
+
+}  // namespace rq

@@ -1,0 +1,63 @@
+// Parameter blocks and host-side launchers of the kernel families (internal).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rq {
+
+struct FwdParams {
+    const float* x;
+    const float* cb;
+    int64_t B;
+    int K, L, mode, dist;
+    float beta, temp;
+    const float* gu;
+    uint64_t seed, offset;
+    float* emb;
+    float* res;
+    int64_t* ids;
+    float* loss;
+    int KC;  // codes per shared-memory chunk (multiple of 4)
+};
+
+struct BwdParams {
+    const float* g_emb;
+    const float* g_res;
+    const float* g_loss;
+    const float* res;
+    const int64_t* ids;
+    const float* cb;
+    int64_t B;
+    int K, L, mode;
+    float beta;
+    float* g_x;
+    float* g_cb;
+};
+
+
+struct KmeansParams {
+    const float* x;
+    const float* centroids;
+    int64_t B;
+    int K;
+    int64_t* assign;
+    int has_prev;
+    float* sums;
+    unsigned long long* counts;
+    unsigned long long* n_changed;
+    int KC;
+};
+
+int quantize_forward_simt(const FwdParams& p, int D, cudaStream_t st);
+int quantize_backward_simt(const BwdParams& p, int D, cudaStream_t st);
+int quantize_backward_gumbel(const BwdParams& p, int D, float temperature, const float* gu, uint64_t seed,
+                             uint64_t offset, cudaStream_t st);
+int kmeans_assign_accumulate_simt(const KmeansParams& p, int D, cudaStream_t st);
+int kmeans_update(const float* sums, const int64_t* counts, float* centroids, int D, int K, float* max_shift,
+                  int64_t* n_empty, int64_t* empty_ids, cudaStream_t st);
+
+// tcgen05 family (rq_quantize_tc.cu)
+bool tc_supported(int D, int K, int L, int mode, int distance);
+int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st);
+
+}  // namespace rq

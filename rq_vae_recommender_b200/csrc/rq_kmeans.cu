@@ -1,0 +1,144 @@
+// K-means assignment + accumulation (init/kmeans.py:40-58 of the reference), exact SIMT family.
+//
+// The reference materialises a [B,K,D] broadcast of (x-c)^2 (655 MB at B=20k) and then runs a
+// Python loop over the K clusters with a host sync each.  Here one thread owns a point, scans
+// the centroids staged in shared memory in the reference's direct form sum_d (x_d - c_d)^2,
+// and scatters its row into per-cluster sums with 16-byte L2 reductions; a second tiny kernel
+// turns (sums, counts) into centroids, the max shift (kmeans.py:67) and the empty-cluster list.
+#include "rq_common.cuh"
+#include "rq_kernels.h"
+#include "rq_rowmath.cuh"
+
+namespace rq {
+
+constexpr int kKmThreads = 256;
+
+template <int D>
+__global__ void __launch_bounds__(kKmThreads) rq_kmeans_assign_simt_kernel(KmeansParams p) {
+    extern __shared__ __align__(16) float smem[];
+    float* sC = smem;
+    const int tid = threadIdx.x;
+    const int64_t row = (int64_t)blockIdx.x * kKmThreads + tid;
+    const bool active = row < p.B;
+    float r[D];
+    if (active) load_row<D>(p.x + row * D, r);
+    else {
+#pragma unroll
+        for (int j = 0; j < D; ++j) r[j] = 0.f;
+    }
+    float best = INFINITY;
+    int bi = 0;
+    for (int k0 = 0; k0 < p.K; k0 += p.KC) {
+        const int kc = min(p.KC, p.K - k0);
+        __syncthreads();
+        for (int i = tid; i < kc * (D / 4); i += kKmThreads)
+            reinterpret_cast<float4*>(sC)[i] = __ldg(reinterpret_cast<const float4*>(p.centroids + (int64_t)k0 * D) + i);
+        __syncthreads();
+        for (int k = 0; k < kc; ++k) {
+            const float4* c = reinterpret_cast<const float4*>(sC + k * D);
+            float a = 0.f;
+#pragma unroll
+            for (int j = 0; j < D / 4; ++j) {
+                float4 v = c[j];
+                float t0 = r[4 * j] - v.x, t1 = r[4 * j + 1] - v.y, t2 = r[4 * j + 2] - v.z, t3 = r[4 * j + 3] - v.w;
+                a = fmaf(t0, t0, a); a = fmaf(t1, t1, a); a = fmaf(t2, t2, a); a = fmaf(t3, t3, a);
+            }
+            if (a < best) { best = a; bi = k0 + k; }
+        }
+    }
+    int changed = 0;
+    if (active) {
+        changed = (!p.has_prev) || (p.assign[row] != (int64_t)bi);
+        p.assign[row] = bi;
+        float* dst = p.sums + (int64_t)bi * D;
+#pragma unroll
+        for (int j = 0; j < D; j += 4) red_add_v4(dst + j, r[j], r[j + 1], r[j + 2], r[j + 3]);
+        atomicAdd(p.counts + bi, 1ull);
+    }
+    unsigned m = __ballot_sync(0xffffffffu, changed);
+    if ((tid & 31) == 0 && m) atomicAdd(p.n_changed, (unsigned long long)__popc(m));
+}
+
+template <int D>
+static int launch_km(const KmeansParams& p0, cudaStream_t st) {
+    KmeansParams p = p0;
+    int kc = 16384 / D;
+    if (kc > p.K) kc = p.K;
+    p.KC = kc;
+    size_t smem = (size_t)kc * D * sizeof(float);
+    auto kern = rq_kmeans_assign_simt_kernel<D>;
+    RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((p.B + kKmThreads - 1) / kKmThreads));
+    kern<<<grid, kKmThreads, smem, st>>>(p);
+    RQ_LAUNCHED();
+    return 0;
+}
+
+int kmeans_assign_accumulate_simt(const KmeansParams& p, int D, cudaStream_t st) {
+    RQ_CUDA(cudaMemsetAsync(p.sums, 0, (size_t)p.K * D * sizeof(float), st));
+    RQ_CUDA(cudaMemsetAsync(p.counts, 0, (size_t)p.K * sizeof(unsigned long long), st));
+    RQ_CUDA(cudaMemsetAsync(p.n_changed, 0, sizeof(unsigned long long), st));
+    if (p.B == 0) return 0;
+    switch (D) {
+        case 4: return launch_km<4>(p, st);
+        case 8: return launch_km<8>(p, st);
+        case 16: return launch_km<16>(p, st);
+        case 32: return launch_km<32>(p, st);
+        case 64: return launch_km<64>(p, st);
+        case 128: return launch_km<128>(p, st);
+        default:
+            set_error("unsupported embed_dim D=%d (supported: 4, 8, 16, 32, 64, 128)", D);
+            return RQ_ERR_UNSUPPORTED_SHAPE;
+    }
+}
+
+// One CTA; thread k owns cluster k (strided).  c_new = sums/count (kmeans.py:57) or unchanged
+// for an empty cluster; shift_k = ||c_new - c_old||_2 (kmeans.py:67).
+__global__ void rq_kmeans_update_kernel(const float* __restrict__ sums, const int64_t* __restrict__ counts,
+                                        float* __restrict__ centroids, int D, int K, float* max_shift,
+                                        int64_t* n_empty, int64_t* empty_ids) {
+    __shared__ float s_max[32];
+    __shared__ int s_nempty;
+    if (threadIdx.x == 0) s_nempty = 0;
+    __syncthreads();
+    float mx = 0.f;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+        int64_t n = counts[k];
+        if (n == 0) {
+            atomicAdd(&s_nempty, 1);
+            continue;
+        }
+        float inv = (float)n;
+        float sh = 0.f;
+        for (int j = 0; j < D; ++j) {
+            float c = sums[(int64_t)k * D + j] / inv;
+            float t = c - centroids[(int64_t)k * D + j];
+            sh = fmaf(t, t, sh);
+            centroids[(int64_t)k * D + j] = c;
+        }
+        mx = fmaxf(mx, sqrtf(sh));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float m = 0.f;
+        for (int w = 0; w < (blockDim.x + 31) / 32; ++w) m = fmaxf(m, s_max[w]);
+        *max_shift = m;
+        *n_empty = s_nempty;
+        // ascending list of empty clusters (K is small; serial scan by one thread)
+        int c = 0;
+        for (int k = 0; k < K; ++k)
+            if (counts[k] == 0) empty_ids[c++] = k;
+    }
+}
+
+int kmeans_update(const float* sums, const int64_t* counts, float* centroids, int D, int K, float* max_shift,
+                  int64_t* n_empty, int64_t* empty_ids, cudaStream_t st) {
+    rq_kmeans_update_kernel<<<1, 256, 0, st>>>(sums, counts, centroids, D, K, max_shift, n_empty, empty_ids);
+    RQ_LAUNCHED();
+    return 0;
+}
+
+}  // namespace rq

@@ -1,0 +1,215 @@
+"""Tensor-level wrappers over the C ABI (torch tensors in, torch tensors out).
+
+These are the calls the module mirrors in `modules/`, `init/` make; they add argument checks,
+output allocation (torch caching allocator, current stream) and the autograd binding.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib as L
+from ._lib import (DIST_COSINE, DIST_L2, IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05, MODE_EVAL,  # noqa: F401
+                   MODE_GUMBEL_SOFTMAX, MODE_ROTATION_TRICK, MODE_STE)
+
+
+def _f32c(t: torch.Tensor, name: str) -> torch.Tensor:
+    L.require_cuda(t, name, torch.float32)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def quantize_forward(x: torch.Tensor, codebooks: torch.Tensor, mode: int = MODE_EVAL, beta: float = 0.25,
+                     temperature: float = 0.2, distance: int = DIST_L2,
+                     gumbel_uniform: Optional[torch.Tensor] = None, seed: int = 0, offset: int = 0,
+                     want_embeddings: bool = True, want_residuals: bool = True, want_loss: bool = True,
+                     impl: int = IMPL_AUTO):
+    """Fused L-level residual quantisation (rq_quantize_forward).
+
+    x [B,D] fp32, codebooks [L,K,D] fp32 (effective).  Returns (emb [L,B,D]|None,
+    residuals [L,B,D]|None, ids [L,B] int64, loss [B]|None)."""
+    x = _f32c(x, "x")
+    codebooks = _f32c(codebooks, "codebooks")
+    if x.dim() != 2 or codebooks.dim() != 3:
+        raise L.RqEngineError("x must be [B,D] and codebooks [L,K,D]")
+    B, D = x.shape
+    Lv, K, Dc = codebooks.shape
+    assert Dc == D, f"codebook dim {Dc} != latent dim {D}"      # modules/quantize.py:100
+    if gumbel_uniform is not None:
+        gumbel_uniform = _f32c(gumbel_uniform, "gumbel_uniform")
+        if tuple(gumbel_uniform.shape) != (Lv, B, K):
+            raise L.RqEngineError(f"gumbel_uniform must be [L,B,K]={Lv, B, K}, got {tuple(gumbel_uniform.shape)}")
+    dev = x.device
+    with torch.cuda.device(dev):
+        emb = torch.empty((Lv, B, D), device=dev, dtype=torch.float32) if want_embeddings else None
+        res = torch.empty((Lv, B, D), device=dev, dtype=torch.float32) if want_residuals else None
+        ids = torch.empty((Lv, B), device=dev, dtype=torch.int64)
+        loss = torch.empty((B,), device=dev, dtype=torch.float32) if want_loss else None
+        rc = L.lib().rq_quantize_forward(L.ptr(x), L.ptr(codebooks), B, D, K, Lv, int(mode), int(distance),
+                                         float(beta), float(temperature), L.ptr(gumbel_uniform), int(seed),
+                                         int(offset), L.ptr(emb), L.ptr(res), L.ptr(ids), L.ptr(loss), int(impl),
+                                         L.stream_of(x))
+    L.check(rc, "rq_quantize_forward")
+    return emb, res, ids, loss
+
+
+def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, beta, temperature,
+                      gumbel_uniform=None, seed: int = 0, offset: int = 0) -> Tuple[torch.Tensor, torch.Tensor]:
+    """rq_quantize_backward: returns (g_x [B,D], g_codebooks [L,K,D])."""
+    residuals = _f32c(residuals, "residuals")
+    codebooks = _f32c(codebooks, "codebooks")
+    L.require_cuda(ids, "ids", torch.int64)
+    ids = ids.contiguous()
+    Lv, B, D = residuals.shape
+    K = codebooks.shape[1]
+    g_emb = None if g_emb is None else _f32c(g_emb, "g_emb")
+    g_res = None if g_res is None else _f32c(g_res, "g_res")
+    g_loss = None if g_loss is None else _f32c(g_loss, "g_loss")
+    gumbel_uniform = None if gumbel_uniform is None else _f32c(gumbel_uniform, "gumbel_uniform")
+    dev = residuals.device
+    with torch.cuda.device(dev):
+        g_x = torch.empty((B, D), device=dev, dtype=torch.float32)
+        g_cb = torch.empty((Lv, K, D), device=dev, dtype=torch.float32)
+        rc = L.lib().rq_quantize_backward(L.ptr(g_emb), L.ptr(g_res), L.ptr(g_loss), L.ptr(residuals), L.ptr(ids),
+                                          L.ptr(codebooks), B, D, K, Lv, int(mode), float(beta), float(temperature),
+                                          L.ptr(gumbel_uniform), int(seed), int(offset), L.ptr(g_x), L.ptr(g_cb),
+                                          L.stream_of(residuals))
+    L.check(rc, "rq_quantize_backward")
+    return g_x, g_cb
+
+
+class ResidualQuantizeFn(torch.autograd.Function):
+    """Autograd binding of the fused forward/backward pair.  Stands in for the ~45-node per-level
+    autograd graph the reference builds implicitly."""
+
+    @staticmethod
+    def forward(ctx, x, codebooks, mode, beta, temperature, distance, gumbel_uniform, seed, offset, impl):
+        emb, res, ids, loss = quantize_forward(x, codebooks, mode, beta, temperature, distance, gumbel_uniform,
+                                               seed, offset, True, True, True, impl)
+        ctx.save_for_backward(res, ids, codebooks, gumbel_uniform if gumbel_uniform is not None else x.new_empty(0))
+        ctx.cfg = (mode, beta, temperature, gumbel_uniform is not None, seed, offset)
+        ctx.mark_non_differentiable(ids)
+        return emb, res, ids, loss
+
+    @staticmethod
+    def backward(ctx, g_emb, g_res, _g_ids, g_loss):
+        res, ids, codebooks, gu = ctx.saved_tensors
+        mode, beta, temperature, has_gu, seed, offset = ctx.cfg
+        g_x, g_cb = quantize_backward(g_emb, g_res, g_loss, res, ids, codebooks, mode, beta, temperature,
+                                      gu if has_gu else None, seed, offset)
+        return g_x, g_cb, None, None, None, None, None, None, None, None
+
+
+def residual_quantize(x, codebooks, mode=MODE_EVAL, beta=0.25, temperature=0.2, distance=DIST_L2,
+                      gumbel_uniform=None, seed=0, offset=0, impl=IMPL_AUTO):
+    """Differentiable fused quantiser: (emb [L,B,D], residuals [L,B,D], ids [L,B], loss [B])."""
+    if torch.is_grad_enabled() and (x.requires_grad or codebooks.requires_grad):
+        return ResidualQuantizeFn.apply(x, codebooks, mode, beta, temperature, distance, gumbel_uniform, seed,
+                                        offset, impl)
+    return quantize_forward(x, codebooks, mode, beta, temperature, distance, gumbel_uniform, seed, offset,
+                            True, True, True, impl)
+
+
+# ---- k-means -------------------------------------------------------------------------------
+def kmeans_assign_accumulate(x, centroids, assign: Optional[torch.Tensor] = None, impl: int = IMPL_AUTO):
+    """One assignment+accumulation pass.  Returns (assign [B] i64, sums [K,D], counts [K] i64,
+    n_changed [1] i64).  `assign`, when given, is the previous assignment and is updated in place."""
+    x = _f32c(x, "x")
+    centroids = _f32c(centroids, "centroids")
+    B, D = x.shape
+    K = centroids.shape[0]
+    dev = x.device
+    with torch.cuda.device(dev):
+        has_prev = assign is not None
+        if not has_prev:
+            assign = torch.empty((B,), device=dev, dtype=torch.int64)
+        else:
+            L.require_cuda(assign, "assign", torch.int64)
+        sums = torch.empty((K, D), device=dev, dtype=torch.float32)
+        counts = torch.empty((K,), device=dev, dtype=torch.int64)
+        n_changed = torch.empty((1,), device=dev, dtype=torch.int64)
+        rc = L.lib().rq_kmeans_assign_accumulate(L.ptr(x), L.ptr(centroids), B, D, K, L.ptr(assign), int(has_prev),
+                                                 L.ptr(sums), L.ptr(counts), L.ptr(n_changed), int(impl),
+                                                 L.stream_of(x))
+    L.check(rc, "rq_kmeans_assign_accumulate")
+    return assign, sums, counts, n_changed
+
+
+def kmeans_update(sums, counts, centroids):
+    """In-place centroid update.  Returns (max_shift [1] f32, n_empty [1] i64, empty_ids [K] i64)."""
+    K, D = centroids.shape
+    dev = centroids.device
+    with torch.cuda.device(dev):
+        max_shift = torch.empty((1,), device=dev, dtype=torch.float32)
+        n_empty = torch.empty((1,), device=dev, dtype=torch.int64)
+        empty_ids = torch.empty((K,), device=dev, dtype=torch.int64)
+        rc = L.lib().rq_kmeans_update(L.ptr(sums), L.ptr(counts), L.ptr(centroids), D, K, L.ptr(max_shift),
+                                      L.ptr(n_empty), L.ptr(empty_ids), L.stream_of(centroids))
+    L.check(rc, "rq_kmeans_update")
+    return max_shift, n_empty, empty_ids
+
+
+# ---- tokenizer integer paths ------------------------------------------------------------------
+def corpus_table(sem_ids: torch.Tensor, codebook_size: int) -> torch.Tensor:
+    """[N,L] int64 (any strides) -> [N,L+1] int64 = [ids | dedup] (semids.py:86-99)."""
+    L.require_cuda(sem_ids, "sem_ids", torch.int64)
+    N, Lv = sem_ids.shape
+    dev = sem_ids.device
+    with torch.cuda.device(dev):
+        table = torch.empty((N, Lv + 1), device=dev, dtype=torch.int64)
+        nbytes = int(L.lib().rq_corpus_table_workspace_bytes(N, Lv))
+        ws = torch.empty((nbytes,), device=dev, dtype=torch.uint8)
+        rc = L.lib().rq_corpus_table(L.ptr(sem_ids), sem_ids.stride(0), sem_ids.stride(1), N, Lv,
+                                     int(codebook_size), L.ptr(table), L.ptr(ws), nbytes, L.stream_of(sem_ids))
+    L.check(rc, "rq_corpus_table")
+    return table
+
+
+def prefix_index(table: torch.Tensor, p: int, radix: int) -> torch.Tensor:
+    """Sorted packed keys of table[:, :p] (uint64 stored in an int64 tensor)."""
+    L.require_cuda(table, "table", torch.int64)
+    table = table.contiguous()
+    N, W = table.shape
+    dev = table.device
+    with torch.cuda.device(dev):
+        keys = torch.empty((N,), device=dev, dtype=torch.int64)
+        nbytes = int(L.lib().rq_prefix_index_workspace_bytes(N))
+        ws = torch.empty((nbytes,), device=dev, dtype=torch.uint8)
+        rc = L.lib().rq_prefix_index_build(L.ptr(table), N, W, int(p), int(radix), L.ptr(keys), L.ptr(ws), nbytes,
+                                           L.stream_of(table))
+    L.check(rc, "rq_prefix_index_build")
+    return keys
+
+
+def prefix_exists(sorted_keys: torch.Tensor, queries: torch.Tensor, radix: int) -> torch.Tensor:
+    """queries [..., p] int64 -> bool [...]."""
+    L.require_cuda(queries, "queries", torch.int64)
+    p = queries.shape[-1]
+    q = queries.reshape(-1, p).contiguous()
+    dev = queries.device
+    with torch.cuda.device(dev):
+        out = torch.empty((q.shape[0],), device=dev, dtype=torch.uint8)
+        rc = L.lib().rq_prefix_exists(L.ptr(sorted_keys), sorted_keys.shape[0], L.ptr(q), q.shape[0], p, int(radix),
+                                      L.ptr(out), L.stream_of(queries))
+    L.check(rc, "rq_prefix_exists")
+    return out.view(torch.bool).reshape(queries.shape[:-1])
+
+
+def gather_tokens(table: torch.Tensor, item_ids: torch.Tensor, seq_mask: Optional[torch.Tensor] = None):
+    """table [N,W], item_ids [B,n] -> [B, n*W] with padding -> -1 (semids.py:122-123, 137-141)."""
+    L.require_cuda(table, "table", torch.int64)
+    L.require_cuda(item_ids, "item_ids", torch.int64)
+    table = table.contiguous()
+    ids = item_ids.contiguous()
+    Bn, n = ids.shape
+    W = table.shape[1]
+    m = None
+    if seq_mask is not None:
+        m = seq_mask.to(torch.bool).contiguous().view(torch.uint8)
+    dev = table.device
+    with torch.cuda.device(dev):
+        out = torch.empty((Bn, n * W), device=dev, dtype=torch.int64)
+        rc = L.lib().rq_gather_tokens(L.ptr(table), table.shape[0], W, L.ptr(ids), L.ptr(m), Bn * n, L.ptr(out),
+                                      L.stream_of(table))
+    L.check(rc, "rq_gather_tokens")
+    return out

@@ -1,0 +1,140 @@
+"""Semantic-ID tokenizer behind the reference's `SemanticIdTokenizer` interface
+(modules/tokenizer/semids.py:23-154).
+
+  * `precompute_corpus_ids` streams the corpus through the fused quantiser and builds the
+    [N, L+1] id table with ONE stable sort (rq_corpus_table) instead of the reference's O(N^2 L)
+    hit matrices that re-pack the growing cache every 512 items (:83-99).
+  * `exists_prefix` answers from a sorted packed-key index by binary search (:103-120).  The
+    reference evaluates `math.ceil(n // 16)` chunks (:114), i.e. silently skips the trailing
+    n % 16 rows (and everything when n < 16); `strict_reference_quirk=True` reproduces that, the
+    default is the mathematically intended answer.
+  * `forward` tokenises sequences by table gather (:137-143) in one kernel.
+"""
+from typing import List, Optional
+
+import torch
+from torch import Tensor, nn
+
+from ... import functional as RF
+from ...data.schemas import SeqBatch, TokenizedSeqBatch, batch_to
+from ..rqvae import RqVae
+from ..utils import eval_mode
+
+BATCH_SIZE = 16
+
+
+class SemanticIdTokenizer(nn.Module):
+    """Tokenizes a batch of sequences of item features into a batch of sequences of semantic ids."""
+
+    def __init__(
+        self,
+        input_dim: int,
+        output_dim: int,
+        hidden_dims: List[int],
+        codebook_size: int,
+        n_layers: int = 3,
+        n_cat_feats: int = 18,
+        commitment_weight: float = 0.25,
+        rqvae_weights_path: Optional[str] = None,
+        rqvae_codebook_normalize: bool = False,
+        rqvae_sim_vq: bool = False,
+    ) -> None:
+        super().__init__()
+        self.rq_vae = RqVae(
+            input_dim=input_dim, embed_dim=output_dim, hidden_dims=hidden_dims, codebook_size=codebook_size,
+            codebook_kmeans_init=False, codebook_normalize=rqvae_codebook_normalize,
+            codebook_sim_vq=rqvae_sim_vq, n_layers=n_layers, n_cat_features=n_cat_feats,
+            commitment_weight=commitment_weight)
+        if rqvae_weights_path is not None:
+            self.rq_vae.load_pretrained(rqvae_weights_path)
+        self.rq_vae.eval()
+        self.codebook_size = codebook_size
+        self.n_layers = n_layers
+        self.strict_reference_quirk = False
+        self.corpus_batch_size = 65536       # items per fused-quantiser launch (the reference uses 512)
+        self.reset()
+
+    def reset(self):
+        self.cached_ids = None
+        self._prefix_index = {}
+
+    @property
+    def sem_ids_dim(self):
+        return self.n_layers + 1
+
+    def _get_hits(self, query: Tensor, key: Tensor) -> Tensor:
+        """Kept for API parity (semids.py:64-65); the engine never materialises hit matrices."""
+        return (key.unsqueeze(0) == query.unsqueeze(1)).all(axis=-1)
+
+    @torch.no_grad()
+    def semantic_ids(self, x: Tensor) -> Tensor:
+        """[n, input_dim] -> [n, L] int64 (ids-only launch: no embeddings / residuals written)."""
+        rq = self.rq_vae
+        lat = rq.encode(x)
+        l0 = rq.layers[0]
+        from ..quantize import kernel_distance
+        _, _, ids, _ = RF.quantize_forward(lat, rq.effective_codebooks(), RF.MODE_EVAL,
+                                           float(l0.quantize_loss.commitment_weight), 1.0,
+                                           kernel_distance(l0.distance_mode), want_embeddings=False,
+                                           want_residuals=False, want_loss=False)
+        return ids.permute(1, 0)
+
+    @torch.no_grad()
+    @eval_mode
+    def precompute_corpus_ids(self, movie_dataset) -> Tensor:
+        """`movie_dataset[list_of_idx]` must return a SeqBatch whose `.x` is [n, input_dim]
+        (data/processed.py:74-84 of the reference)."""
+        n = len(movie_dataset)
+        device = self.rq_vae.device
+        chunks = []
+        for s in range(0, n, self.corpus_batch_size):
+            idx = list(range(s, min(n, s + self.corpus_batch_size)))
+            batch = batch_to(movie_dataset[idx], device)
+            chunks.append(self.semantic_ids(batch.x))
+        ids = torch.cat(chunks, dim=0) if chunks else torch.zeros((0, self.n_layers), dtype=torch.int64, device=device)
+        self.cached_ids = RF.corpus_table(ids, self.codebook_size)
+        self._prefix_index = {}
+        return self.cached_ids
+
+    def _index_for(self, p: int):
+        if p not in self._prefix_index:
+            # the dedup column can exceed codebook_size, so the packing radix covers the whole table
+            radix = max(int(self.cached_ids.max().item()) + 1, self.codebook_size)
+            self._prefix_index[p] = (RF.prefix_index(self.cached_ids, p, radix), radix)
+        return self._prefix_index[p]
+
+    @torch.no_grad()
+    @eval_mode
+    def exists_prefix(self, sem_id_prefix: Tensor) -> Tensor:
+        if self.cached_ids is None:
+            raise Exception("No match can be found in empty cache.")            # semids.py:107
+        p = sem_id_prefix.shape[-1]
+        keys, radix = self._index_for(p)
+        out = RF.prefix_exists(keys, sem_id_prefix.to(self.cached_ids.device), radix).to(sem_id_prefix.device)
+        if self.strict_reference_quirk:
+            n_eval = (sem_id_prefix.shape[0] // BATCH_SIZE) * BATCH_SIZE
+            out[n_eval:] = False
+        return out
+
+    def _tokenize_seq_batch_from_cached(self, ids: Tensor, seq_mask: Optional[Tensor] = None) -> Tensor:
+        return RF.gather_tokens(self.cached_ids, ids, seq_mask)
+
+    @torch.no_grad()
+    @eval_mode
+    def forward(self, batch: SeqBatch) -> TokenizedSeqBatch:
+        if self.cached_ids is None or batch.ids.max() >= self.cached_ids.shape[0]:
+            B, N = batch.ids.shape
+            sem_ids = self.rq_vae.get_semantic_ids(batch.x).sem_ids
+            D = sem_ids.shape[-1]
+            seq_mask, sem_ids_fut = None, None
+        else:
+            B, N = batch.ids.shape
+            _, D = self.cached_ids.shape
+            seq_mask = batch.seq_mask.repeat_interleave(D, dim=1)
+            sem_ids = self._tokenize_seq_batch_from_cached(batch.ids, batch.seq_mask)
+            sem_ids_fut = self._tokenize_seq_batch_from_cached(batch.ids_fut)
+        token_type_ids = torch.arange(D, device=sem_ids.device).repeat(B, N)
+        token_type_ids_fut = torch.arange(D, device=sem_ids.device).repeat(B, 1)
+        return TokenizedSeqBatch(user_ids=batch.user_ids, sem_ids=sem_ids, sem_ids_fut=sem_ids_fut,
+                                 seq_mask=seq_mask, token_type_ids=token_type_ids,
+                                 token_type_ids_fut=token_type_ids_fut)

@@ -1,0 +1,115 @@
+"""CPU: host-side mirror of the reference's module interface (no kernels run)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import rq_vae_recommender_b200 as R
+from rq_vae_recommender_b200.modules.quantize import kernel_distance, kernel_mode
+from rq_vae_recommender_b200 import functional as RF
+from conftest import ROOT, load_golden
+
+
+def test_enum_values_match_reference():
+    assert [m.value for m in R.QuantizeForwardMode] == [1, 2, 3]
+    assert R.QuantizeForwardMode.ROTATION_TRICK.name == "ROTATION_TRICK"
+    assert [d.value for d in R.QuantizeDistance] == [1, 2]
+    assert kernel_mode(R.QuantizeForwardMode.STE, training=False) == RF.MODE_EVAL
+    assert kernel_mode(R.QuantizeForwardMode.GUMBEL_SOFTMAX, True) == RF.MODE_GUMBEL_SOFTMAX
+    with pytest.raises(Exception, match="Unsupported Quantize forward mode"):
+        kernel_mode("nope", True)
+    with pytest.raises(Exception, match="Unsupported Quantize distance mode"):
+        kernel_distance("nope")
+
+
+def test_state_dict_keys_and_load_from_reference_fixture():
+    z = load_golden("rqvae_mlp_small.npz")
+    sd = {k[4:]: torch.from_numpy(z[k]) for k in z.keys() if k.startswith("sd::")}
+    m = R.RqVae(input_dim=64, embed_dim=32, hidden_dims=[48, 40], codebook_size=64, codebook_kmeans_init=False,
+                codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, n_layers=3, n_cat_features=0)
+    assert sorted(m.state_dict().keys()) == sorted(sd.keys())
+    m.load_state_dict(sd)                     # a reference checkpoint's "model" entry loads unchanged
+    assert "kmeans_initted" not in m.state_dict()
+    q = R.Quantize(16, 8, sim_vq=True, codebook_normalize=True)
+    assert sorted(q.state_dict().keys()) == ["embedding.weight", "out_proj.0.weight"]
+    assert float(q.weight.min()) >= 0.0 and float(q.weight.max()) <= 1.0      # U[0,1) init
+
+
+def test_constructor_signatures_match_reference():
+    import inspect
+    sig = inspect.signature(R.Quantize.__init__)
+    assert list(sig.parameters)[1:] == ["embed_dim", "n_embed", "do_kmeans_init", "codebook_normalize", "sim_vq",
+                                        "commitment_weight", "forward_mode", "distance_mode"]
+    assert sig.parameters["forward_mode"].default == R.QuantizeForwardMode.GUMBEL_SOFTMAX
+    sig = inspect.signature(R.RqVae.__init__)
+    assert list(sig.parameters)[1:] == ["input_dim", "embed_dim", "hidden_dims", "codebook_size",
+                                        "codebook_kmeans_init", "codebook_normalize", "codebook_sim_vq",
+                                        "codebook_mode", "n_layers", "commitment_weight", "n_cat_features"]
+    sig = inspect.signature(R.SemanticIdTokenizer.__init__)
+    assert list(sig.parameters)[1:] == ["input_dim", "output_dim", "hidden_dims", "codebook_size", "n_layers",
+                                        "n_cat_feats", "commitment_weight", "rqvae_weights_path",
+                                        "rqvae_codebook_normalize", "rqvae_sim_vq"]
+    sig = inspect.signature(R.Kmeans.__init__)
+    assert list(sig.parameters)[1:4] == ["k", "max_iters", "stop_threshold"]
+    assert sig.parameters["stop_threshold"].default == 1e-10
+
+
+def test_cpu_tensors_are_rejected_not_silently_computed():
+    q = R.Quantize(32, 16, do_kmeans_init=False, forward_mode=R.QuantizeForwardMode.STE)
+    with pytest.raises(R.RqEngineError, match="no CPU"):
+        q(torch.randn(5, 32), 0.2)
+    with pytest.raises(AssertionError):
+        q(torch.randn(5, 31), 0.2)            # quantize.py:100
+    tok = R.SemanticIdTokenizer(24, 8, [16], 6, n_cat_feats=0)
+    assert tok.sem_ids_dim == 4 and not tok.rq_vae.training      # semids.py:58
+    with pytest.raises(Exception, match="No match can be found in empty cache."):
+        tok.exists_prefix(torch.zeros(4, 2, dtype=torch.int64))
+    assert not tok.rq_vae.layers[0].do_kmeans_init
+
+
+def test_product_never_imports_oracle():
+    """The oracle is test infrastructure; the shipped package must not reference it."""
+    pkg = os.path.join(ROOT, "rq_vae_recommender_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "rq_oracle" not in src and "import oracle" not in src and "from oracle" not in src, f
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from rq_vae_recommender_b200.init.kmeans import Kmeans
+        from rq_vae_recommender_b200.parallel import shard_range
+        g = torch.Generator().manual_seed(0)
+        full = torch.randn(11, 4, generator=g)
+        lo, hi = shard_range(11, rank, world)
+        x = full[lo:hi]
+        km = Kmeans(k=3)
+        off, n = km._shard_layout(x.shape[0], x.device)
+        rows = km._global_rows(x, [0, 5, 10, 6], off)
+        np.random.seed(123 + rank)               # ranks disagree on purpose: rank 0's draw must win
+        km._init_centroids(x)
+        q.put((rank, off, n, torch.equal(rows, full[[0, 5, 10, 6]]), km.centroids.clone()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_kmeans_sharding_helpers_gloo_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 500)
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    [p.join(60) for p in procs]
+    assert res[0][1] == 0 and res[1][1] == 6 and res[0][2] == res[1][2] == 11
+    assert res[0][3] and res[1][3]
+    assert torch.equal(res[0][4], res[1][4])     # identical initial centroids on both ranks
