@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""bench.py — items/s through the fused 3-level residual quantiser (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl engine|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (config.workload): BASELINE configs[1] — the quantiser part of one RQ-VAE training step at
+the rqvae_amazon.gin shape: B = 65,536 latents per GPU, d = 32, 3 levels x 256 codes,
+ROTATION_TRICK, beta = 0.25; one step = fused forward (embeddings, residuals, ids, loss) + fused
+backward (g_x, g_codebooks) over one batch, plus the codebook-gradient all-reduce when N > 1.
+Weak scaling: every rank processes its own 65,536-row batch per step.
+
+`value`   : device-resident inputs, CUDA-event timed, max over ranks.
+`e2e`     : the same step through the public module API (`RqVae.quantize_latents` + autograd) with the
+            batch in pinned HOST memory: H2D of the latents and D2H of (loss, sem_ids) every step.
+`roofline`: the dominant kernel's algorithmic bytes / its mean launch duration (CUDA events inside the
+            timed region) against MEASURED_PEAKS.json.
+`cpu_baseline` / `--impl reference`: the CPU restatement of the reference's quantiser (oracle/, the same
+            ATen ops the reference runs on CPU) on the box's host cores; the reference itself is a
+            Python tree that does not travel to the GPU box.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_PER_GPU, D, K, L = 65536, 32, 256, 3
+BETA, TEMP = 0.25, 0.2
+N_SLOTS = 8          # ring of distinct input batches: 8 x (8 MB latents + 24 MB upstream grads) > 126 MB L2
+BYTES_FWD = 4 * D + 2 * 4 * D * L + 8 * L + 4         # 924 B/item full forward
+BYTES_BWD = BYTES_FWD                                  # fwd+bwd = 2x full forward
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--cpu-sample-items", type=int, default=B_PER_GPU)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return float(j["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def make_inputs(torch, device, n_slots, seed):
+    """Synthetic latents with trained-looking codebooks: level l = K residual rows of the data."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    xs = [torch.randn(B_PER_GPU, D, generator=g) for _ in range(n_slots)]
+    gcb = torch.Generator(device="cpu").manual_seed(1234)       # identical codebooks on every rank
+    base = torch.randn(4 * K, D, generator=gcb)
+    cbs, res = [], base.clone()
+    for l in range(L):
+        cb = res[torch.randperm(res.shape[0], generator=gcb)[:K]] * 0.9
+        cbs.append(cb)
+        d = torch.cdist(res, cb)
+        res = res - cb[d.argmin(1)]
+    g_emb = [torch.randn(L, B_PER_GPU, D, generator=g) * 0.01 for _ in range(n_slots)]
+    g_loss = torch.full((B_PER_GPU,), 1.0 / B_PER_GPU)
+    return xs, torch.stack(cbs), g_emb, g_loss
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._h = None
+
+    def _one(self):
+        nv = self._nv
+        self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+        except Exception:
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                 0x80: "hw_power_brake_slowdown"}
+        for bit, n in names.items():
+            if r & bit:
+                self.reasons.add(n)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self._one()
+            except Exception:
+                pass
+            self._stop.wait(0.01)
+
+    def __enter__(self):
+        if self._h is not None:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        if self._h is not None:
+            try:
+                self._one()
+            except Exception:
+                pass
+            self._stop.set()
+            self._t.join(1.0)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_reference_run(n_items, steps, warmup):
+    """Times the CPU restatement of the reference's quantiser (fwd + autograd bwd) with all host
+    threads.  Returns (items_per_s, ms_per_step, cores)."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import rq_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n_items, D, generator=g)
+    gcb = torch.Generator().manual_seed(1234)
+    base = torch.randn(4 * K, D, generator=gcb)
+    cl, res = [], base.clone()
+    for l in range(L):
+        cb = res[torch.randperm(res.shape[0], generator=gcb)[:K]] * 0.9
+        cl.append(cb)
+        res = res - cb[torch.cdist(res, cb).argmin(1)]
+    cbs = torch.stack(cl)
+    g_emb = torch.randn(L, n_items, D, generator=g) * 0.01
+    g_loss = torch.full((n_items,), 1.0 / n_items)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        O.rq_forward_backward(x, list(cbs), O.MODE_ROTATION_TRICK, BETA, TEMP, g_emb, g_loss)
+        t1 = time.perf_counter()
+        if i >= warmup:
+            times.append(t1 - t0)
+    t = sum(times)
+    return n_items * len(times) / t, 1e3 * t / len(times), cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = args.cpu_sample_items
+    steps, warm = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
+    ips, ms, cores = cpu_reference_run(n, steps, warm)
+    cb = {"value": ips, "unit": "items/s", "cores": cores, "kind": "port",
+          "sample": f"{steps} steps x {n} items fwd+bwd (oracle/rq_oracle.py, torch CPU ATen, fp32)"}
+    print(json.dumps({
+        "impl": "reference", "metric": "items/sec semantic-ID quantize (3x256,d=32)", "value": ips,
+        "unit": "items/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus), "cpu_baseline": cb,
+        "e2e": {"value": ips, "unit": "items/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def workload_config(n):
+    return {"workload": "configs[1]: quantiser fwd+bwd of one RQ-VAE training step, rqvae_amazon.gin shape",
+            "batch_per_gpu": B_PER_GPU, "global_batch": B_PER_GPU * n, "embed_dim": D, "codebook_size": K,
+            "n_levels": L, "mode": "ROTATION_TRICK", "commitment_weight": BETA,
+            "l2_policy": f"ring of {N_SLOTS} distinct batches ({N_SLOTS * (B_PER_GPU * D * 4 * (1 + L)) >> 20} MiB of inputs) > 126 MB L2",
+            "parallelism": f"dp{n} row-sharded, replicated codebooks"}
+
+
+def run_engine(args):
+    import torch
+    import torch.distributed as dist
+    import rq_vae_recommender_b200 as R
+    from rq_vae_recommender_b200 import functional as RF
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the engine has no CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    R.lib()
+
+    xs_h, cbs_h, g_emb_h, g_loss_h = make_inputs(torch, dev, N_SLOTS, seed=100 + rank)
+    xs = [t.to(dev) for t in xs_h]
+    g_embs = [t.to(dev) for t in g_emb_h]
+    g_loss = g_loss_h.to(dev)
+    cbs = cbs_h.to(dev)
+    mode = RF.MODE_ROTATION_TRICK
+
+    def step(i, ev=None):
+        s = i % N_SLOTS
+        if ev is not None:
+            ev[0].record()
+        emb, res, ids, loss = RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP)
+        if ev is not None:
+            ev[1].record()
+        g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP)
+        if world > 1:
+            dist.all_reduce(g_cb)            # codebook-gradient all-reduce (98,304 B), the path's one exchange
+        if ev is not None:
+            ev[2].record()
+        return loss, g_x, g_cb
+
+    def fence():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    fence()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    l0 = R.launch_count()
+    with ClockSampler(local) as clk:
+        fence()
+        t_start = torch.cuda.Event(enable_timing=True)
+        t_end = torch.cuda.Event(enable_timing=True)
+        t_start.record()
+        for i in range(args.steps):
+            step(args.warmup + i, evs[i])
+        t_end.record()
+        fence()
+    launches = R.launch_count() - l0
+    ms_total = t_start.elapsed_time(t_end)
+    fwd_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+    bwd_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
+
+    # ---- e2e: public module API, host buffers, copies inside the timed region ------------------
+    model = R.RqVae(input_dim=D, embed_dim=D, hidden_dims=[], codebook_size=K, codebook_kmeans_init=False,
+                    codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, n_layers=L, commitment_weight=BETA,
+                    n_cat_features=0).to(dev)
+    with torch.no_grad():
+        for l in range(L):
+            model.layers[l].embedding.weight.copy_(cbs[l])
+    model.train()
+    xs_pin = [t.pin_memory() for t in xs_h]
+    loss_pin = torch.empty(B_PER_GPU, dtype=torch.float32).pin_memory()
+    ids_pin = torch.empty((L, B_PER_GPU), dtype=torch.int64).pin_memory()
+
+    def e2e_step(i):
+        s = i % N_SLOTS
+        lat = xs_pin[s].to(dev, non_blocking=True).requires_grad_(True)         # H2D, 8 MiB
+        out = model.quantize_latents(lat, TEMP)
+        obj = (out.embeddings.permute(2, 0, 1) * g_embs[s]).sum() + (out.quantize_loss * g_loss).sum()
+        model.zero_grad(set_to_none=True)
+        obj.backward()
+        if world > 1:
+            R.parallel.allreduce_codebook_grads(model)
+        loss_pin.copy_(out.quantize_loss.detach(), non_blocking=True)           # D2H
+        ids_pin.copy_(out.sem_ids.detach().t(), non_blocking=True)              # D2H
+        torch.cuda.current_stream().synchronize()                               # the caller reads the result
+
+    for i in range(max(3, args.warmup)):
+        e2e_step(i)
+    fence()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(args.warmup + i)
+    fence()
+    e2e_s = time.perf_counter() - t0
+
+    # ---- side numbers (outside the timed region): ids-only tokenisation launch -------------------
+    for _ in range(3):
+        RF.quantize_forward(xs[0], cbs, RF.MODE_EVAL, want_embeddings=False, want_residuals=False, want_loss=False)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(10):
+        RF.quantize_forward(xs[i % N_SLOTS], cbs, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
+                            want_loss=False)
+    b.record()
+    torch.cuda.synchronize()
+    ids_only_ms = a.elapsed_time(b) / 10
+
+    stats = torch.tensor([ms_total, e2e_s * 1e3, float(launches)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms_total, e2e_ms, launches = float(mx[0]), float(mx[1]), int(sm[2])
+    else:
+        e2e_ms = float(stats[1])
+    if rank == 0:
+        items = B_PER_GPU * world * args.steps
+        hbm, which = peaks()
+        dom = "rq_fwd" if fwd_ms >= bwd_ms else "rq_bwd"
+        dom_ms = max(fwd_ms, bwd_ms)
+        achieved = B_PER_GPU * BYTES_FWD / (dom_ms * 1e-3) / 1e9
+        out = {
+            "metric": "items/sec semantic-ID quantize (3x256,d=32)", "value": items / (ms_total * 1e-3),
+            "unit": "items/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(world),
+            "e2e": {"value": items / (e2e_ms * 1e-3), "unit": "items/s",
+                    "h2d_bytes_per_step": B_PER_GPU * D * 4, "d2h_bytes_per_step": B_PER_GPU * 4 + L * B_PER_GPU * 8},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",
+                         "frac": achieved / hbm, "traffic": None, "peak_source": which + " (burst copy)",
+                         "algorithmic_bytes_per_launch": B_PER_GPU * BYTES_FWD, "launch_ms": dom_ms},
+            "clocks": clk.summary(),
+            "extra": {"fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "ids_only_ms": ids_only_ms,
+                      "ids_only_items_per_s": B_PER_GPU / (ids_only_ms * 1e-3),
+                      "fwd_items_per_s": B_PER_GPU / (fwd_ms * 1e-3),
+                      "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1))},
+        }
+        if not args.no_cpu_baseline and world == 1:
+            ips, ms, cores = cpu_reference_run(args.cpu_sample_items, 3, 1)
+            out["cpu_baseline"] = {"value": ips, "unit": "items/s", "cores": cores, "kind": "port",
+                                   "sample": f"3 steps x {args.cpu_sample_items} items fwd+bwd, oracle/rq_oracle.py "
+                                             f"(torch CPU ATen fp32, {cores} threads)"}
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_engine(args)
+
+
+if __name__ == "__main__":
+    main()

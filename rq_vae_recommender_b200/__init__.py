@@ -4,7 +4,7 @@ AdamLTy/RQ-VAE-Recommender's quantization path (see DESIGN.md / INTEGRATION.md).
 Importing this package does not load CUDA; the C-ABI library is opened on first use and a
 missing library or a CPU tensor raises — there is no fallback path.
 """
-from . import functional  # noqa: F401
+from . import functional, parallel  # noqa: F401
 from ._lib import LIB_PATH, RqEngineError, launch_count, lib  # noqa: F401
 from .init.kmeans import Kmeans, KmeansOutput, kmeans_init_  # noqa: F401
 from .modules.quantize import (GumbelNoise, Quantize, QuantizeDistance, QuantizeForwardMode,  # noqa: F401

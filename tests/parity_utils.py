@@ -1,0 +1,67 @@
+"""Shared parity checks: CUDA engine vs the CPU oracle (tests only)."""
+import numpy as np
+import torch
+
+import rq_oracle as O
+
+REL_TOL = 1e-3   # north_star: loss, quantized embeddings and gradients within 1e-3 relative
+TIE_REL = 1e-6   # north_star: ids bit-exact unless the fp32 top-2 gap is under 1e-6 relative
+
+
+def rel_err(a, b):
+    a = torch.as_tensor(a).double().cpu()
+    b = torch.as_tensor(b).double().cpu()
+    denom = b.abs().max().clamp_min(1e-30)
+    return float((a - b).abs().max() / denom)
+
+
+def assert_close(a, b, what, tol=REL_TOL):
+    e = rel_err(a, b)
+    assert e <= tol, f"{what}: max rel err {e:.3e} > {tol}"
+
+
+def check_ids(ids_gpu, oracle_out, codebooks, what=""):
+    """ids_gpu [L,B] vs oracle; a row may differ only from a level whose fp32 top-2 gap is inside
+    the tie band (both definitions of SURVEY.md §7.3-3 are evaluated; definition 2 — relative to
+    ||x||^2+||c||^2, the error scale of the expanded form — is the gate).  Returns
+    (n_mismatch_rows, n_outside_band_def1)."""
+    ids_gpu = torch.as_tensor(ids_gpu).cpu()
+    ids_ref = oracle_out.sem_ids
+    Lv, B = ids_ref.shape
+    diff = ids_gpu != ids_ref
+    rows = torch.nonzero(diff.any(dim=0)).flatten()
+    out1 = 0
+    for r in rows.tolist():
+        l = int(torch.nonzero(diff[:, r]).flatten()[0])
+        x = oracle_out.residuals[l, r:r + 1]
+        in1, in2, gap, d1 = O.tie_band(x, codebooks[l], TIE_REL)
+        # the engine's choice must be one of the two nearest codes
+        d = ((x.double() - codebooks[l].double()) ** 2).sum(1)
+        top2 = torch.topk(d, 2, largest=False).indices.tolist()
+        assert int(ids_gpu[l, r]) in top2, f"{what}: row {r} level {l}: id {int(ids_gpu[l, r])} not in top-2 {top2}"
+        assert bool(in2[0]), (f"{what}: row {r} level {l}: ids differ ({int(ids_gpu[l, r])} vs "
+                              f"{int(ids_ref[l, r])}) outside the tie band: gap {float(gap[0]):.3e}, d1 {float(d1[0]):.3e}")
+        out1 += int(not bool(in1[0]))
+    return len(rows), out1
+
+
+def matching_rows(ids_gpu, oracle_out):
+    """Boolean [B]: rows whose ids agree at every level (float outputs are compared on these)."""
+    return (torch.as_tensor(ids_gpu).cpu() == oracle_out.sem_ids).all(dim=0)
+
+
+def synthetic_codebooks(latents: torch.Tensor, L: int, K: int, seed: int = 0):
+    """Codebooks that behave like trained ones: level l = K residual rows (+ jitter) of the data,
+    so assignments are spread and residual norms shrink level by level."""
+    g = torch.Generator().manual_seed(seed)
+    res = latents.clone()
+    cbs = []
+    for l in range(L):
+        idx = torch.randperm(res.shape[0], generator=g)[:K]
+        if idx.numel() < K:
+            idx = torch.randint(0, res.shape[0], (K,), generator=g)
+        cb = res[idx] * 0.9 + 0.02 * res.std() * torch.randn(K, res.shape[1], generator=g)
+        cbs.append(cb.contiguous())
+        out = O.quantize_level(res, cb, O.MODE_EVAL)
+        res = res - out.emb_out
+    return cbs

@@ -1,0 +1,157 @@
+"""GPU parity: k-means and the tokenizer integer paths vs golden fixtures and the CPU oracle."""
+import numpy as np
+import pytest
+import torch
+
+import rq_oracle as O
+import rq_vae_recommender_b200 as R
+from rq_vae_recommender_b200 import functional as RF
+from conftest import load_golden
+from parity_utils import assert_close
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def test_kmeans_single_step_golden():
+    z = load_golden("kmeans_small.npz")
+    x = torch.from_numpy(z["x"]).to(DEV)
+    c = torch.from_numpy(z["step_c0"]).to(DEV).clone()
+    assign, sums, counts, n_changed = RF.kmeans_assign_accumulate(x, c)
+    assert np.array_equal(assign.cpu().numpy(), z["step_assign"])
+    assert int(n_changed) == x.shape[0] and int(counts.sum()) == x.shape[0]
+    max_shift, n_empty, _ = RF.kmeans_update(sums, counts, c)
+    assert int(n_empty) == 0
+    assert_close(c.cpu(), torch.from_numpy(z["step_c1"]), "centroids", tol=1e-5)
+    want_shift = np.linalg.norm(z["step_c1"] - z["step_c0"], axis=1).max()
+    assert abs(float(max_shift) - want_shift) <= 1e-4 * want_shift
+    # second pass from the same assignment: only genuinely moved rows are counted
+    assign2, _, _, n_changed2 = RF.kmeans_assign_accumulate(x, torch.from_numpy(z["step_c0"]).to(DEV), assign)
+    assert int(n_changed2) == 0
+
+
+def test_kmeans_empty_clusters_golden():
+    z = load_golden("kmeans_small.npz")
+    x = torch.from_numpy(z["x"]).to(DEV)
+    c = torch.from_numpy(z["empty_c0"]).to(DEV).clone()
+    assign, sums, counts, _ = RF.kmeans_assign_accumulate(x, c)
+    assert np.array_equal(assign.cpu().numpy(), z["empty_assign"])
+    _, n_empty, empty_ids = RF.kmeans_update(sums, counts, c)
+    assert int(n_empty) == 2 and empty_ids[:2].tolist() == [2, 9]
+    # host re-seed with the rows the reference drew (kmeans.py:53)
+    c[empty_ids[:2]] = x[torch.from_numpy(z["empty_reseed_rows"]).to(DEV)]
+    assert_close(c.cpu(), torch.from_numpy(z["empty_c1"]), "centroids after reseed", tol=1e-5)
+
+
+def test_kmeans_full_run_golden_and_init():
+    z = load_golden("kmeans_small.npz")
+    x = torch.from_numpy(z["x"]).to(DEV)
+    np.random.seed(8)                            # the fixture's seed: same np.random.choice draw (kmeans.py:36)
+    out = R.Kmeans(k=16).run(x)
+    assert out.centroids.shape == (16, 8) and out.assignment.dtype == torch.int64
+    assert np.array_equal(out.assignment.cpu().numpy(), z["run_assignment"])
+    assert_close(out.centroids.cpu(), torch.from_numpy(z["run_centroids"]), "run centroids", tol=1e-5)
+    w = torch.zeros(16, 8, device=DEV)
+    np.random.seed(8)
+    R.kmeans_init_(w, x)
+    assert_close(w.cpu(), torch.from_numpy(z["init_tensor"]), "kmeans_init_", tol=1e-5)
+    with pytest.raises(ValueError):
+        R.Kmeans(k=4).run(torch.zeros(0, 8, device=DEV))     # empty x (np.random.choice / kmeans.py:55)
+
+
+@pytest.mark.parametrize("B,D,K", [(20000, 32, 256), (5000, 64, 100), (3001, 16, 1024)])
+def test_kmeans_step_vs_oracle(B, D, K):
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, D, generator=g) + 2.0 * torch.randn(8, D, generator=g)[torch.randint(0, 8, (B,), generator=g)]
+    c0 = x[torch.randperm(B, generator=g)[:K]].clone()
+    c1, a1 = O.kmeans_update(x, c0, reseed_rows=[0] * K)
+    cd = c0.to(DEV).clone()
+    assign, sums, counts, _ = RF.kmeans_assign_accumulate(x.to(DEV), cd)
+    mism = (assign.cpu() != a1)
+    # direct-form distances: ties only at fp32 rounding level
+    assert mism.float().mean() < 1e-4
+    if not bool(mism.any()):
+        _, n_empty, empty_ids = RF.kmeans_update(sums, counts, cd)
+        keep = torch.ones(K, dtype=torch.bool)
+        keep[empty_ids[:int(n_empty)].cpu()] = False
+        assert_close(cd.cpu()[keep], c1[keep], "centroids", tol=1e-5)
+    # invariants at any size: counts and sums are consistent with the assignment
+    assert int(counts.sum()) == B
+    want = torch.zeros(K, D, dtype=torch.float64).index_add_(0, assign.cpu(), x.double())
+    assert_close(sums.cpu(), want, "sums", tol=1e-5)
+
+
+def test_tokenizer_golden_end_to_end():
+    z = load_golden("tokenizer_small.npz")
+    sd = {k[4:]: torch.from_numpy(z[k]) for k in z.keys() if k.startswith("sd::")}
+    tok = R.SemanticIdTokenizer(input_dim=24, output_dim=8, hidden_dims=[16], codebook_size=6, n_layers=3,
+                                n_cat_feats=0)
+    tok.rq_vae.load_state_dict(sd)
+    tok = tok.to(DEV)
+    tok.corpus_batch_size = 512
+    x = torch.from_numpy(z["x"])
+
+    class Items(torch.utils.data.Dataset):
+        def __len__(self):
+            return x.shape[0]
+
+        def __getitem__(self, idx):
+            ids = torch.tensor(idx).unsqueeze(0)
+            return R.SeqBatch(user_ids=-torch.ones_like(ids.squeeze(0)), ids=ids, ids_fut=-torch.ones_like(ids.squeeze(0)),
+                              x=x[idx], x_fut=-torch.ones_like(ids.squeeze(0)), seq_mask=torch.ones_like(ids, dtype=bool))
+
+    table = tok.precompute_corpus_ids(Items())
+    assert table.dtype == torch.int64 and table.shape == (1300, 4)
+    assert np.array_equal(table.cpu().numpy(), z["cached_ids"])          # bit-exact incl. dedup column
+    for p in (1, 2, 3, 4):
+        q = torch.from_numpy(z[f"prefix_q{p}"]).to(DEV)
+        tok.strict_reference_quirk = True
+        assert np.array_equal(tok.exists_prefix(q).cpu().numpy(), z[f"prefix_r{p}"])
+        tok.strict_reference_quirk = False
+        full = tok.exists_prefix(q).cpu().numpy()
+        assert np.array_equal(full, O.exists_prefix(z["cached_ids"], z[f"prefix_q{p}"]))
+        assert full[36, 4]
+    batch = R.SeqBatch(user_ids=torch.arange(6, device=DEV), ids=torch.from_numpy(z["fw_ids"]).to(DEV),
+                       ids_fut=torch.from_numpy(z["fw_ids_fut"]).to(DEV), x=torch.zeros(6, 5, 24, device=DEV),
+                       x_fut=torch.zeros(6, 1, 24, device=DEV), seq_mask=torch.from_numpy(z["fw_seq_mask"]).to(DEV))
+    tk = tok(batch)
+    assert np.array_equal(tk.sem_ids.cpu().numpy(), z["fw_sem_ids"])
+    assert np.array_equal(tk.sem_ids_fut.cpu().numpy(), z["fw_sem_ids_fut"])
+    assert np.array_equal(tk.seq_mask.cpu().numpy(), z["fw_seq_mask_out"])
+    assert np.array_equal(tk.token_type_ids.cpu().numpy(), z["fw_token_type_ids"])
+    assert np.array_equal(tk.token_type_ids_fut.cpu().numpy(), z["fw_token_type_ids_fut"])
+
+
+@pytest.mark.parametrize("N,L,K", [(0, 3, 256), (1, 3, 256), (100000, 3, 8), (250000, 4, 1024), (5000, 2, 3)])
+def test_corpus_table_vs_oracle(N, L, K):
+    g = torch.Generator().manual_seed(N + L)
+    ids = torch.randint(0, K, (N, L), generator=g)
+    if N > 10:
+        ids[N // 2:N // 2 + 5] = ids[0]           # forced duplicates far apart
+    table = RF.corpus_table(ids.to(DEV), K)
+    assert np.array_equal(table.cpu().numpy(), O.corpus_ids_table(ids.numpy()).reshape(N, L + 1))
+    # the [B,L] view over [L,B] memory the fused kernel hands out is accepted as-is
+    view = ids.t().contiguous().to(DEV).t()
+    assert np.array_equal(RF.corpus_table(view, K).cpu().numpy(), table.cpu().numpy())
+
+
+def test_c_abi_host_entry_point():
+    """rq_semantic_ids_host: host buffers in, host buffers out, copies inside."""
+    import ctypes
+    from rq_vae_recommender_b200 import _lib
+    B, D, K, L = 3000, 32, 256, 3
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(B, D, generator=g)
+    cbs = torch.randn(L, K, D, generator=g)
+    cb_dev = cbs.to(DEV)
+    ids = np.empty((L, B), dtype=np.int64)
+    loss = np.empty((B,), dtype=np.float32)
+    xn = x.numpy()
+    torch.cuda.synchronize()
+    rc = _lib.lib().rq_semantic_ids_host(xn.ctypes.data, cb_dev.data_ptr(), B, D, K, L, 1, ids.ctypes.data,
+                                         loss.ctypes.data, 0, None)
+    _lib.check(rc)
+    ref = O.rq_forward(x, list(cbs), O.MODE_EVAL)
+    assert (torch.from_numpy(ids) == ref.sem_ids).float().mean() > 0.999
+    ok = (torch.from_numpy(ids) == ref.sem_ids).all(0)
+    assert_close(torch.from_numpy(loss)[ok], ref.quantize_loss[ok], "loss")

@@ -1,0 +1,193 @@
+"""GPU parity: fused quantiser (through the module API and the C ABI) vs golden fixtures and the
+CPU oracle.  Run on the B200 box with `-m gpu`."""
+import numpy as np
+import pytest
+import torch
+
+import rq_oracle as O
+import rq_vae_recommender_b200 as R
+from rq_vae_recommender_b200 import functional as RF
+from conftest import load_golden
+from parity_utils import assert_close, check_ids, matching_rows, synthetic_codebooks
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+MODES = {"eval": O.MODE_EVAL, "ste": O.MODE_STE, "rot": O.MODE_ROTATION_TRICK, "gumbel": O.MODE_GUMBEL_SOFTMAX}
+IMPLS = [RF.IMPL_SIMT, RF.IMPL_AUTO]
+
+
+def _as_oracle_out(z, mname):
+    return O.RqOut(torch.from_numpy(z[f"{mname}_emb"]), torch.from_numpy(z[f"{mname}_res"]),
+                   torch.from_numpy(z[f"{mname}_ids"]), torch.from_numpy(z[f"{mname}_loss"]))
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+@pytest.mark.parametrize("name", ["rq_stack_d32_k256_l3.npz", "rq_stack_d64_k256_l3.npz", "rq_stack_d64_k1024_l4.npz"])
+def test_golden_stack_forward_backward(name, impl):
+    """Fixtures produced by the unmodified reference (RqVae.get_semantic_ids + autograd)."""
+    z = load_golden(name)
+    x = torch.from_numpy(z["x"]).to(DEV)
+    cbs_cpu = torch.from_numpy(z["codebooks"])
+    cbs = cbs_cpu.to(DEV)
+    g_emb, g_loss = torch.from_numpy(z["g_emb"]).to(DEV), torch.from_numpy(z["g_loss"]).to(DEV)
+    for mname, mode in MODES.items():
+        if f"{mname}_ids" not in z:
+            continue
+        ref = _as_oracle_out(z, mname)
+        gu = torch.from_numpy(z["gumbel_uniform"]).to(DEV) if mname == "gumbel" else None
+        xin = x.clone().requires_grad_(True)
+        cin = cbs.clone().requires_grad_(True)
+        emb, res, ids, loss = RF.residual_quantize(xin, cin, mode, 0.25, 0.2, RF.DIST_L2, gu, impl=impl)
+        n_mis, _ = check_ids(ids, ref, list(cbs_cpu), f"{name}/{mname}")
+        ok = matching_rows(ids, ref)
+        assert ok.float().mean() > 0.99
+        assert_close(emb.detach().cpu()[:, ok], ref.embeddings[:, ok], f"{mname} emb")
+        assert_close(res.detach().cpu()[:, ok], ref.residuals[:, ok], f"{mname} residuals")
+        assert_close(loss.detach().cpu()[ok], ref.quantize_loss[ok], f"{mname} loss")
+        if mname == "gumbel":
+            continue   # backward covered in test_gpu_gumbel.py
+        ((emb * g_emb).sum() + (loss * g_loss).sum()).backward()
+        assert_close(xin.grad.cpu()[ok], torch.from_numpy(z[f"{mname}_gx"])[ok], f"{mname} grad x")
+        if n_mis == 0:
+            assert_close(cin.grad.cpu(), torch.from_numpy(z[f"{mname}_gcb"]), f"{mname} grad codebooks")
+
+
+@pytest.mark.parametrize("name", ["quantize_level_d32_k256.npz", "quantize_level_d64_k1024.npz"])
+def test_golden_single_level_module(name):
+    """`Quantize.forward` itself, all four branches + COSINE, against the reference's outputs."""
+    z = load_golden(name)
+    x = torch.from_numpy(z["x"]).to(DEV)
+    cb = torch.from_numpy(z["codebook"])
+    D, K = cb.shape[1], cb.shape[0]
+    g_emb, g_loss = torch.from_numpy(z["g_emb"]).to(DEV), torch.from_numpy(z["g_loss"]).to(DEV)
+    R.GumbelNoise.source = "torch"
+    try:
+        for mname, fm, training in [("eval", R.QuantizeForwardMode.STE, False), ("ste", R.QuantizeForwardMode.STE, True),
+                                    ("rot", R.QuantizeForwardMode.ROTATION_TRICK, True)]:
+            layer = R.Quantize(D, K, do_kmeans_init=False, forward_mode=fm, commitment_weight=0.25).to(DEV)
+            with torch.no_grad():
+                layer.embedding.weight.copy_(cb)
+            layer.train(training)
+            xin = x.clone().requires_grad_(True)
+            out = layer(xin, temperature=0.2)
+            assert out.ids.dtype == torch.int64 and out.embeddings.shape == x.shape and out.loss.shape == (x.shape[0],)
+            same = out.ids.cpu() == torch.from_numpy(z[f"{mname}_ids"])
+            assert same.float().mean() > 0.99
+            assert int(out.ids[5]) == 3          # duplicated codeword rows 3/7: first index wins
+            assert_close(out.embeddings.detach().cpu()[same], torch.from_numpy(z[f"{mname}_emb"])[same], f"{mname} emb")
+            assert_close(out.loss.detach().cpu()[same], torch.from_numpy(z[f"{mname}_loss"])[same], f"{mname} loss")
+            ((out.embeddings * g_emb).sum() + (out.loss * g_loss).sum()).backward()
+            assert_close(xin.grad.cpu()[same], torch.from_numpy(z[f"{mname}_gx"])[same], f"{mname} gx")
+            if bool(same.all()):
+                assert_close(layer.embedding.weight.grad.cpu(), torch.from_numpy(z[f"{mname}_gcb"]), f"{mname} gcb")
+        layer = R.Quantize(D, K, do_kmeans_init=False, forward_mode=R.QuantizeForwardMode.STE,
+                           distance_mode=R.QuantizeDistance.COSINE).to(DEV).eval()
+        with torch.no_grad():
+            layer.embedding.weight.copy_(cb)
+        out = layer(x, 0.2)
+        same = out.ids.cpu() == torch.from_numpy(z["cosine_ids"])
+        assert same.float().mean() > 0.99
+        assert_close(out.loss.cpu()[same], torch.from_numpy(z["cosine_loss"])[same], "cosine loss")
+    finally:
+        R.GumbelNoise.source = "philox"
+
+
+def test_golden_norm_simvq_module_stack():
+    """codebook_normalize (level 0) + sim_vq through RqVae, gradients to embedding AND out_proj."""
+    z = load_golden("rq_stack_norm_simvq_d16_k32_l2.npz")
+    D, K, L = 16, 32, 2
+    x = torch.from_numpy(z["x"]).to(DEV)
+    for mname, fm, training in [("eval", R.QuantizeForwardMode.STE, False), ("ste", R.QuantizeForwardMode.STE, True),
+                                ("rot", R.QuantizeForwardMode.ROTATION_TRICK, True)]:
+        m = R.RqVae(input_dim=D, embed_dim=D, hidden_dims=[], codebook_size=K, codebook_kmeans_init=False,
+                    codebook_normalize=True, codebook_sim_vq=True, codebook_mode=fm, n_layers=L,
+                    commitment_weight=0.25, n_cat_features=0).to(DEV)
+        with torch.no_grad():
+            m.encoder.mlp[0].weight.copy_(torch.eye(D))
+            for l in range(L):
+                m.layers[l].embedding.weight.copy_(torch.from_numpy(z["codebooks"][l]))
+                m.layers[l].out_proj[0].weight.copy_(torch.from_numpy(z["sim_vq_weights"][l]))
+        m.train(training)
+        xin = x.clone().requires_grad_(True)
+        out = m.get_semantic_ids(xin, gumbel_t=0.2)
+        B = x.shape[0]
+        assert out.embeddings.shape == (B, D, L) and out.embeddings.stride() == (D, 1, B * D)
+        assert out.sem_ids.shape == (B, L) and out.sem_ids.stride() == (1, B)
+        same = (out.sem_ids.cpu() == torch.from_numpy(z[f"{mname}_ids"]).T).all(dim=1)
+        assert same.float().mean() > 0.97
+        assert_close(out.embeddings.permute(2, 0, 1).detach().cpu()[:, same], torch.from_numpy(z[f"{mname}_emb"])[:, same], "emb")
+        assert_close(out.quantize_loss.detach().cpu()[same], torch.from_numpy(z[f"{mname}_loss"])[same], "loss")
+        obj = (out.embeddings.permute(2, 0, 1) * torch.from_numpy(z["g_emb"]).to(DEV)).sum() + \
+              (out.quantize_loss * torch.from_numpy(z["g_loss"]).to(DEV)).sum()
+        obj.backward()
+        assert_close(xin.grad.cpu()[same], torch.from_numpy(z[f"{mname}_gx"])[same], f"{mname} gx", tol=2e-3)
+        if bool(same.all()):
+            gcb = torch.stack([m.layers[l].embedding.weight.grad for l in range(L)]).cpu()
+            assert_close(gcb, torch.from_numpy(z[f"{mname}_gcb"]), f"{mname} gcb", tol=2e-3)
+
+
+@pytest.mark.parametrize("impl", IMPLS)
+@pytest.mark.parametrize("B,D,K,L", [(1, 32, 256, 3), (255, 32, 256, 3), (1000, 32, 250, 2), (777, 64, 256, 3),
+                                      (513, 16, 7, 4), (300, 8, 16, 1), (20000, 32, 256, 3)])
+def test_seeded_vs_oracle_shapes(B, D, K, L, impl):
+    """Ragged batch sizes, K not a multiple of 4, several D; ids-only launch agrees with full."""
+    g = torch.Generator().manual_seed(B + D + K)
+    x = torch.randn(B, D, generator=g)
+    cbs = synthetic_codebooks(torch.randn(max(B, 2 * K), D, generator=g), L, K, seed=1)
+    for mode in (O.MODE_EVAL, O.MODE_ROTATION_TRICK, O.MODE_STE):
+        ref = O.rq_forward(x, cbs, mode)
+        emb, res, ids, loss = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), mode, impl=impl)
+        check_ids(ids, ref, cbs, f"B{B} D{D} K{K} mode{mode}")
+        ok = matching_rows(ids, ref)
+        assert_close(emb.cpu()[:, ok], ref.embeddings[:, ok], "emb")
+        assert_close(res.cpu()[:, ok], ref.residuals[:, ok], "res")
+        assert_close(loss.cpu()[ok], ref.quantize_loss[ok], "loss")
+    _, _, ids2, _ = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), O.MODE_EVAL, want_embeddings=False,
+                                        want_residuals=False, want_loss=False, impl=impl)
+    _, _, ids1, _ = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), O.MODE_EVAL, impl=impl)
+    assert torch.equal(ids1, ids2)
+
+
+def test_empty_batch_and_errors():
+    cbs = torch.randn(3, 256, 32, device=DEV)
+    emb, res, ids, loss = RF.quantize_forward(torch.zeros(0, 32, device=DEV), cbs)
+    assert emb.shape == (3, 0, 32) and ids.shape == (3, 0) and loss.shape == (0,)
+    with pytest.raises(AssertionError):
+        RF.quantize_forward(torch.zeros(4, 16, device=DEV), cbs)
+    with pytest.raises(R.RqEngineError, match="unsupported"):
+        RF.quantize_forward(torch.zeros(4, 24, device=DEV), torch.randn(1, 8, 24, device=DEV))
+    with pytest.raises(R.RqEngineError):
+        RF.quantize_forward(torch.zeros(4, 32), cbs)
+
+
+def test_full_size_properties_c2():
+    """BASELINE config 2 shape (B = 65,536, d=32, 3x256, ROTATION_TRICK): size-independent
+    invariants instead of an oracle run."""
+    B, D, K, L = 65536, 32, 256, 3
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(B, D, generator=g)
+    cbs = torch.stack(synthetic_codebooks(x[:20000], L, K, seed=2)).to(DEV)
+    xd = x.to(DEV)
+    for mode in (O.MODE_EVAL, O.MODE_ROTATION_TRICK):
+        emb, res, ids, loss = RF.quantize_forward(xd, cbs, mode, beta=0.25)
+        assert int(ids.min()) >= 0 and int(ids.max()) < K
+        assert torch.equal(res[0], xd)
+        for l in range(L - 1):                   # residual chain, rqvae.py:129 — exact
+            assert torch.equal(res[l + 1], res[l] - emb[l])
+        e = torch.stack([cbs[l][ids[l]] for l in range(L)])
+        want = sum(1.25 * ((res[l] - e[l]) ** 2).sum(-1) for l in range(L))
+        assert_close(loss, want, "loss identity", tol=1e-5)
+        if mode == O.MODE_EVAL:
+            assert torch.equal(emb, e)           # eval branch returns the codeword bit-exactly
+        else:
+            assert_close(emb, e, "rotation value ~ codeword", tol=1e-4)
+        # chosen code is (numerically) the nearest: no other code is closer by more than fp32 noise
+        for l in range(L):
+            d = torch.cdist(res[l][:4096].double(), cbs[l].double()) ** 2
+            dmin = d.min(1).values
+            dsel = d.gather(1, ids[l][:4096, None]).squeeze(1)
+            scale = (res[l][:4096].double() ** 2).sum(1) + (e[l][:4096].double() ** 2).sum(1)
+            assert bool(((dsel - dmin) <= 1e-6 * scale + 1e-12).all())
+        # determinism / idempotence of the launch
+        emb2, res2, ids2, loss2 = RF.quantize_forward(xd, cbs, mode, beta=0.25)
+        assert torch.equal(ids, ids2) and torch.equal(emb, emb2) and torch.equal(loss, loss2)
