@@ -163,6 +163,12 @@ int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B,
                          int distance, int64_t* ids_host, float* loss_host, int impl,
                          rq_stream_t stream);
 
+/* Test hooks of the tcgen05 family: 1 if any mbarrier wait timed out since load (synchronises the
+ * device); and a [128][256] fp32 device buffer that receives tile 0 / level 0's raw accumulator
+ * (||c||^2 - 2 x.c) on subsequent launches (NULL disables). */
+int rq_debug_tc_timeout_flag(void);
+int rq_debug_tc_set_accumulator_dump(float* device_buf_128x256);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

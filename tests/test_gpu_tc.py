@@ -1,0 +1,91 @@
+"""GPU: the tcgen05 family against the exact SIMT family (same C ABI, impl switch) and the oracle."""
+import pytest
+import torch
+
+import rq_oracle as O
+import rq_vae_recommender_b200 as R
+from rq_vae_recommender_b200 import _lib
+from rq_vae_recommender_b200 import functional as RF
+from parity_utils import assert_close, check_ids, matching_rows, synthetic_codebooks
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _inputs(B, K, L, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, 32, generator=g) * scale
+    cbs = synthetic_codebooks(torch.randn(max(4 * K, 2048), 32, generator=g) * scale, L, K, seed=seed + 1)
+    return x, cbs
+
+
+def test_tc_is_selected_for_the_headline_shape():
+    assert _lib.lib().rq_tcgen05_supported(32, 256, 3, RF.MODE_ROTATION_TRICK, RF.DIST_L2) == 1
+    assert _lib.lib().rq_tcgen05_supported(64, 256, 3, RF.MODE_EVAL, RF.DIST_L2) in (0, 1)
+    assert _lib.lib().rq_tcgen05_supported(32, 256, 3, RF.MODE_EVAL, RF.DIST_COSINE) == 0
+
+
+def test_tc_accumulator_error_bound():
+    """Raw tensor-core accumulator (||c||^2 - 2 x.c) of tile 0 / level 0 vs float64: the candidate
+    threshold in the kernel is only sound if this error stays inside the stated bound."""
+    x, cbs = _inputs(128, 256, 1, seed=11)
+    buf = torch.zeros(128, 256, device=DEV)
+    _lib.lib().rq_debug_tc_set_accumulator_dump(buf.data_ptr())
+    try:
+        RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), RF.MODE_EVAL, impl=RF.IMPL_TCGEN05)
+        torch.cuda.synchronize()
+    finally:
+        _lib.lib().rq_debug_tc_set_accumulator_dump(None)
+    assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+    c = cbs[0].double()
+    want = (c ** 2).sum(1)[None, :] - 2.0 * x.double() @ c.T
+    err = (buf.cpu().double() - want).abs()
+    xn = x.double().norm(dim=1, keepdim=True)
+    cn = c.norm(dim=1)[None, :]
+    bound = 0.5 * (8e-5 * xn * cn.max() + 3e-6 * cn.max() ** 2)       # the kernel uses 2E as threshold
+    assert bool((err <= bound).all()), f"max err {float(err.max()):.3e}, bound min {float(bound.min()):.3e}"
+    # and it is far tighter than a single bf16 pass would be
+    assert float((err / (xn * cn)).max()) < 4e-5
+
+
+@pytest.mark.parametrize("B,K,L", [(128, 256, 1), (1, 256, 3), (300, 256, 3), (4097, 200, 2), (65536, 256, 3),
+                                    (70001, 256, 4), (1000, 16, 3)])
+def test_tc_ids_bit_identical_to_simt(B, K, L):
+    x, cbs = _inputs(B, K, L, seed=B % 1000 + K)
+    xd, cd = x.to(DEV), torch.stack(cbs).to(DEV)
+    for mode in (RF.MODE_EVAL, RF.MODE_ROTATION_TRICK, RF.MODE_STE):
+        e1, r1, i1, l1 = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_SIMT)
+        e2, r2, i2, l2 = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_TCGEN05)
+        torch.cuda.synchronize()
+        assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+        n_bad = int((i1 != i2).sum())
+        assert n_bad == 0, f"mode {mode}: {n_bad} ids differ between tcgen05 and SIMT families"
+        assert_close(e2, e1, "emb", tol=1e-6)
+        assert_close(r2, r1, "res", tol=1e-6)
+        assert_close(l2, l1, "loss", tol=1e-6)
+    _, _, i3, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
+                                      want_loss=False, impl=RF.IMPL_TCGEN05)
+    _, _, i1, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_SIMT)
+    assert torch.equal(i1, i3)
+
+
+@pytest.mark.parametrize("scale", [1e-3, 1.0, 50.0])
+def test_tc_vs_oracle_scales_and_near_ties(scale):
+    """Different magnitudes, duplicated codewords (exact ties -> first index), and rows sitting
+    almost on the bisector of two codes (the re-scoring path)."""
+    B, K, L = 6000, 256, 3
+    x, cbs = _inputs(B, K, L, seed=3, scale=scale)
+    cbs[0][17] = cbs[0][5]                          # exact duplicate
+    x[:200] = 0.5 * (cbs[0][torch.arange(200) % K] + cbs[0][(torch.arange(200) + 1) % K]) \
+        + 1e-6 * scale * torch.randn(200, 32)
+    x[200:260] = cbs[0][5] + 1e-4 * scale * torch.randn(60, 32)
+    ref = O.rq_forward(x, cbs, O.MODE_EVAL)
+    emb, res, ids, loss = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), RF.MODE_EVAL, impl=RF.IMPL_TCGEN05)
+    assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+    assert int((ids[0] == 17).sum()) == 0           # first index wins
+    check_ids(ids, ref, cbs, f"scale {scale}")
+    ok = matching_rows(ids, ref)
+    assert_close(emb.cpu()[:, ok], ref.embeddings[:, ok], "emb")
+    assert_close(loss.cpu()[ok], ref.quantize_loss[ok], "loss")
+    _, _, ids_s, _ = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), RF.MODE_EVAL, impl=RF.IMPL_SIMT)
+    assert torch.equal(ids, ids_s)
