@@ -59,11 +59,9 @@ __global__ void __launch_bounds__(kSimtThreads) rq_fwd_simt_kernel(FwdParams p) 
                 reinterpret_cast<float4*>(sC)[i] = v;
             }
             __syncthreads();
-            for (int k = warp; k < kc4; k += kSimtThreads / 32) {
-                float s = 0.f;
-                for (int j = lane; j < D; j += 32) { float c = sC[k * D + j]; s = fmaf(c, c, s); }
-                s = warp_sum(s);
-                if (lane == 0) sN[k] = (p.dist == RQ_DIST_COSINE) ? sqrtf(s) : s;
+            for (int k = tid; k < kc4; k += kSimtThreads) {
+                float s = code_sqnorm<D>(sC + k * D);
+                sN[k] = (p.dist == RQ_DIST_COSINE) ? sqrtf(s) : s;
             }
             __syncthreads();
 

@@ -106,30 +106,47 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
         *reinterpret_cast<uint4*>(sOnes + nosw_off(r, c)) = v;
     }
     __syncthreads();
-    // B operand: one warp per code row; lane j holds element j of the codeword
-    for (int l = 0; l < p.L; ++l) {
-        for (int k = warp; k < KC; k += THREADS / 32) {
-            float c = (k < p.K) ? __ldg(p.cb + ((int64_t)l * p.K + k) * D + lane) : 0.f;
-            float hi = ptx::bf16_round(c);
-            float lo = c - hi;
-            // neighbours exchange so that even lanes pack (j, j+1) pairs
-            float hi_n = __shfl_down_sync(0xffffffffu, hi, 1), lo_n = __shfl_down_sync(0xffffffffu, lo, 1);
-            float cc = warp_sum(c * c);      // same reduction shape as the SIMT family's ||c||^2
-            if (k >= p.K) cc = 1e30f;        // padding codes can never be the minimum
-            if ((lane & 1) == 0) {
-                uint32_t ph = ptx::pack_bf16x2(-2.f * hi, -2.f * hi_n);
-                uint32_t pl = ptx::pack_bf16x2(-2.f * lo, -2.f * lo_n);
-                int j = lane;                // element index (even)
-                // hi part: bytes [0,64) of the row, lo part: bytes [64,128)
-                uint8_t* row = sB + l * B_TILE_BYTES;
-                *reinterpret_cast<uint32_t*>(row + sw128_off(k, (j * 2) >> 4) + ((j * 2) & 15)) = ph;
-                *reinterpret_cast<uint32_t*>(row + sw128_off(k, (64 + j * 2) >> 4) + ((j * 2) & 15)) = pl;
+    // B operand: work item = (level, code, 8-element chunk); every thread first issues ALL of its
+    // 32-byte codebook loads (the prologue is pure latency otherwise), then converts.
+    {
+        constexpr int ITEMS = MAX_L * 4;          // L * 256 codes * 4 chunks / 256 threads
+        float cv[ITEMS][8];
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {
+            const int i = it * THREADS + tid, l = i >> 10, k = (i >> 2) & 255, q = i & 3;
+            if (l < p.L && k < p.K) {
+                ptx::ld_global_v8(p.cb + ((int64_t)l * p.K + k) * D + q * 8, cv[it]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) cv[it][j] = 0.f;
             }
-            if (lane == 0) {
+        }
+#pragma unroll
+        for (int it = 0; it < ITEMS; ++it) {
+            const int i = it * THREADS + tid, l = i >> 10, k = (i >> 2) & 255, q = i & 3;
+            if (l >= p.L) break;                   // uniform across the CTA (l = it >> 2)
+            uint32_t h[4], lw[4];
+            float part = 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float a = cv[it][2 * j], b = cv[it][2 * j + 1];
+                part = fmaf(a, a, part);
+                part = fmaf(b, b, part);
+                ptx::split_pair(-2.f * a, -2.f * b, h[j], lw[j]);
+            }
+            uint8_t* tileB = sB + l * B_TILE_BYTES;
+            *reinterpret_cast<uint4*>(tileB + sw128_off(k, q)) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(tileB + sw128_off(k, 4 + q)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            // ||c||^2 in the canonical order shared with the SIMT family (code_sqnorm in rq_rowmath.cuh):
+            // 8-wide sequential partials, then (p0+p1)+(p2+p3)
+            part += __shfl_xor_sync(0xffffffffu, part, 1);
+            part += __shfl_xor_sync(0xffffffffu, part, 2);
+            if (q == 0) {
+                float cc = (k < p.K) ? part : 1e30f;     // padding codes can never be the minimum
                 sCC[l * KC + k] = cc;
-                float h = ptx::bf16_round(cc), m = ptx::bf16_round(cc - h), lw = ptx::bf16_round((cc - h) - m);
-                uint4 v0 = make_uint4(ptx::pack_bf16x2(h, m), ptx::pack_bf16x2(lw, 0.f), 0, 0);
-                *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 0)) = v0;
+                float hh = ptx::bf16_round(cc), mm = ptx::bf16_round(cc - hh), ll = ptx::bf16_round((cc - hh) - mm);
+                *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 0)) =
+                    make_uint4(ptx::pack_bf16x2(hh, mm), ptx::pack_bf16x2(ll, 0.f), 0, 0);
                 *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 1)) = make_uint4(0, 0, 0, 0);
                 if (k < p.K) atomicMax(&cmax_bits[l], __float_as_int(cc));
             }
@@ -166,12 +183,7 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
             for (int c = 0; c < 4; ++c) {
                 uint32_t h[4], lw[4];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    float a = r[c * 8 + 2 * q], b = r[c * 8 + 2 * q + 1];
-                    float ah = ptx::bf16_round(a), bh = ptx::bf16_round(b);
-                    h[q] = ptx::pack_bf16x2(ah, bh);
-                    lw[q] = ptx::pack_bf16x2(a - ah, b - bh);
-                }
+                for (int q = 0; q < 4; ++q) ptx::split_pair(r[c * 8 + 2 * q], r[c * 8 + 2 * q + 1], h[q], lw[q]);
                 *reinterpret_cast<uint4*>(sAw + sw128_off(wtid, c)) = make_uint4(h[0], h[1], h[2], h[3]);
                 *reinterpret_cast<uint4*>(sAw + sw128_off(wtid, 4 + c)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
             }
@@ -198,9 +210,10 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
             // scalars needed by the epilogue while the MMAs run
             const float xx = dot_self<D>(r);
             const float cmax2 = __int_as_float(cmax_bits[l]);
-            // |acc - exact| <= 3*2^-17 |r||c| (dropped lo.lo + split residue) + fp32 accumulation noise;
-            // both the winner and a rival may be off, hence 2x, with margin ("error bound")
-            const float tol = 8e-5f * sqrtf(xx * cmax2) + 3e-6f * cmax2 + 1e-30f;
+            // |acc - exact| <= 2*(2^-18 + 2*2^-17)|r||c| = 3.8e-5 |r||c| (dropped lo.lo term + the two
+            // truncated lo parts) + fp32 accumulation noise; both the winner and a rival may be off,
+            // hence 2x, with margin ("error bound")
+            const float tol = 1e-4f * sqrtf(xx * cmax2) + 3e-6f * cmax2 + 1e-30f;
             if (!ptx::mbar_wait(&mbar[wg], phase)) timed_out = true;
             phase ^= 1;
             ptx::tc_fence_after_sync();
@@ -216,28 +229,48 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
                 }
             }
             // ---- pass 1: row minimum of the accumulator ------------------------------------------------
-            float m = INFINITY;
-#pragma unroll 1
-            for (int c = 0; c < KC / 32; ++c) {
-                uint32_t v[32];
-                ptx::tmem_ld_32x32b_x32(tmem_row + c * 32, v);
-                ptx::tmem_ld_wait();
+            // Both passes double-buffer the TMEM reads: chunk c+1 is in flight while chunk c is reduced.
+            uint32_t va[32], vb[32];
+            float m0 = INFINITY, m1 = INFINITY;
+            ptx::tmem_ld_32x32b_x32(tmem_row, va);
+            ptx::tmem_ld_wait_for(va);
 #pragma unroll
-                for (int j = 0; j < 32; j += 2) m = ptx::fmin3(m, __uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+            for (int c = 0; c < KC / 32; c += 2) {
+                ptx::tmem_ld_32x32b_x32(tmem_row + (c + 1) * 32, vb);
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    m0 = ptx::fmin3(m0, __uint_as_float(va[j]), __uint_as_float(va[j + 1]));
+                    m1 = ptx::fmin3(m1, __uint_as_float(va[j + 2]), __uint_as_float(va[j + 3]));
+                }
+                ptx::tmem_ld_wait_for(vb);
+                // the last prefetch already fetches chunk 0 again for pass 2
+                ptx::tmem_ld_32x32b_x32(tmem_row + ((c + 2) & (KC / 32 - 1)) * 32, va);
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    m0 = ptx::fmin3(m0, __uint_as_float(vb[j]), __uint_as_float(vb[j + 1]));
+                    m1 = ptx::fmin3(m1, __uint_as_float(vb[j + 2]), __uint_as_float(vb[j + 3]));
+                }
+                ptx::tmem_ld_wait_for(va);
             }
-            const float thr = m + tol;
+            const float thr = fminf(m0, m1) + tol;
             // ---- pass 2: flag every code with acc <= thr ---------------------------------------------
             uint32_t cand[KC / 32];
 #pragma unroll
-            for (int c = 0; c < KC / 32; ++c) {
-                uint32_t v[32];
-                ptx::tmem_ld_32x32b_x32(tmem_row + c * 32, v);
-                ptx::tmem_ld_wait();
+            for (int c = 0; c < KC / 32; c += 2) {
+                ptx::tmem_ld_32x32b_x32(tmem_row + (c + 1) * 32, vb);
                 uint32_t msk = 0;
 #pragma unroll
                 for (int j = 0; j < 32; ++j)      // sign(thr - v) = 1 <=> v > thr ; column j ends at bit 31-j
-                    msk = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[j])), msk, 1);
+                    msk = __funnelshift_l(__float_as_uint(thr - __uint_as_float(va[j])), msk, 1);
                 cand[c] = ~msk;
+                ptx::tmem_ld_wait_for(vb);
+                if (c + 2 < KC / 32) ptx::tmem_ld_32x32b_x32(tmem_row + (c + 2) * 32, va);
+                msk = 0;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    msk = __funnelshift_l(__float_as_uint(thr - __uint_as_float(vb[j])), msk, 1);
+                cand[c + 1] = ~msk;
+                if (c + 2 < KC / 32) ptx::tmem_ld_wait_for(va);
             }
             int n_cand = 0;
 #pragma unroll

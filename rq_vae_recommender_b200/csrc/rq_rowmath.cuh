@@ -27,6 +27,31 @@ __device__ __forceinline__ float dot_self(const float (&r)[D]) {
     return s;
 }
 
+// Canonical ||c||^2 of a codeword, bit-identical in both kernel families: sequential fmaf over
+// 8-element chunks, chunk partials combined as a balanced pairwise tree ((p0+p1)+(p2+p3) for D=32).
+template <int D>
+__device__ __forceinline__ float code_sqnorm(const float* __restrict__ c) {
+    constexpr int W = D >= 8 ? 8 : D;
+    constexpr int NP = D / W;
+    float p[NP];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) {
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < W; j += 4) {
+            float4 v = *reinterpret_cast<const float4*>(c + q * W + j);
+            s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
+        }
+        p[q] = s;
+    }
+#pragma unroll
+    for (int s = 1; s < NP; s *= 2) {
+#pragma unroll
+        for (int q = 0; q + s < NP; q += 2 * s) p[q] += p[q + s];
+    }
+    return p[0];
+}
+
 // The per-mode epilogue of one level, shared by the SIMT and tcgen05 families.
 // In: residual r, selected codeword e (EVAL/STE/ROT) .  Out: emb_out (o), returns the
 // per-row loss of this level.  Operation order follows modules/quantize.py:130-150.

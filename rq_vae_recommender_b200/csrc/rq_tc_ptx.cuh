@@ -114,6 +114,18 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)
         : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// Same wait, but the destination registers are tied to it as in/out operands so the compiler can
+// never schedule a use of `r` above the wait (the load itself completes asynchronously).
+__device__ __forceinline__ void tmem_ld_wait_for(uint32_t (&r)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]),
+                   "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]),
+                   "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]),
+                   "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                 :
+                 : "memory");
+}
 
 // ---- misc -------------------------------------------------------------------------------------------
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
@@ -140,6 +152,20 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float bf16_round(float x) {   // value of bf16(x) (round to nearest even) as fp32
     uint32_t r = pack_bf16x2(x, 0.f);
     return __uint_as_float(r << 16);
+}
+
+// bf16 hi/lo split on the integer pipe (F2FP conversions issue on the quarter-rate XU pipe):
+//   hi = x rounded to bf16 (round-half-up on the magnitude), returned as fp32 bits (low 16 bits 0)
+//   lo = bf16 TRUNCATION of (x - hi); x - hi is exact in fp32.
+// |x - hi| <= 2^-9 |x| and |(x - hi) - lo| <= 2^-8 |x - hi| <= 2^-17 |x|.
+__device__ __forceinline__ uint32_t bf16_hi_bits(float x) { return (__float_as_uint(x) + 0x8000u) & 0xFFFF0000u; }
+// pack the upper halves of two fp32 bit patterns: result = {b.hi16 : a.hi16} (a = element 0)
+__device__ __forceinline__ uint32_t pack_hi16(uint32_t a, uint32_t b) { return __byte_perm(a, b, 0x7632); }
+// (hi, lo) packed bf16x2 words for the element pair (a, b)
+__device__ __forceinline__ void split_pair(float a, float b, uint32_t& hi, uint32_t& lo) {
+    uint32_t ah = bf16_hi_bits(a), bh = bf16_hi_bits(b);
+    hi = pack_hi16(ah, bh);
+    lo = pack_hi16(__float_as_uint(a - __uint_as_float(ah)), __float_as_uint(b - __uint_as_float(bh)));
 }
 
 }  // namespace ptx

@@ -42,7 +42,7 @@ def test_tc_accumulator_error_bound():
     err = (buf.cpu().double() - want).abs()
     xn = x.double().norm(dim=1, keepdim=True)
     cn = c.norm(dim=1)[None, :]
-    bound = 0.5 * (8e-5 * xn * cn.max() + 3e-6 * cn.max() ** 2)       # the kernel uses 2E as threshold
+    bound = 0.5 * (1e-4 * xn * cn.max() + 3e-6 * cn.max() ** 2)       # the kernel uses 2E as threshold
     assert bool((err <= bound).all()), f"max err {float(err.max()):.3e}, bound min {float(bound.min()):.3e}"
     # and it is far tighter than a single bf16 pass would be
     assert float((err / (xn * cn)).max()) < 4e-5
@@ -77,7 +77,7 @@ def test_tc_vs_oracle_scales_and_near_ties(scale):
     x, cbs = _inputs(B, K, L, seed=3, scale=scale)
     cbs[0][17] = cbs[0][5]                          # exact duplicate
     x[:200] = 0.5 * (cbs[0][torch.arange(200) % K] + cbs[0][(torch.arange(200) + 1) % K]) \
-        + 1e-6 * scale * torch.randn(200, 32)
+        + 1e-7 * scale * torch.randn(200, 32)
     x[200:260] = cbs[0][5] + 1e-4 * scale * torch.randn(60, 32)
     ref = O.rq_forward(x, cbs, O.MODE_EVAL)
     emb, res, ids, loss = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), RF.MODE_EVAL, impl=RF.IMPL_TCGEN05)
