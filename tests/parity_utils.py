@@ -35,10 +35,13 @@ def check_ids(ids_gpu, oracle_out, codebooks, what=""):
         l = int(torch.nonzero(diff[:, r]).flatten()[0])
         x = oracle_out.residuals[l, r:r + 1]
         in1, in2, gap, d1 = O.tie_band(x, codebooks[l], TIE_REL)
-        # the engine's choice must be one of the two nearest codes
+        # the engine's choice must itself be within the band of the true minimum (with duplicated or
+        # equidistant codewords there can be more than two such codes)
         d = ((x.double() - codebooks[l].double()) ** 2).sum(1)
-        top2 = torch.topk(d, 2, largest=False).indices.tolist()
-        assert int(ids_gpu[l, r]) in top2, f"{what}: row {r} level {l}: id {int(ids_gpu[l, r])} not in top-2 {top2}"
+        scale2 = float((x.double() ** 2).sum() + (codebooks[l][int(ids_gpu[l, r])].double() ** 2).sum())
+        excess = float(d[int(ids_gpu[l, r])] - d.min())
+        assert excess < TIE_REL * scale2, (f"{what}: row {r} level {l}: id {int(ids_gpu[l, r])} is {excess:.3e} "
+                                           f"farther than the nearest code (band {TIE_REL * scale2:.3e})")
         assert bool(in2[0]), (f"{what}: row {r} level {l}: ids differ ({int(ids_gpu[l, r])} vs "
                               f"{int(ids_ref[l, r])}) outside the tie band: gap {float(gap[0]):.3e}, d1 {float(d1[0]):.3e}")
         out1 += int(not bool(in1[0]))

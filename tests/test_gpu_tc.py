@@ -76,9 +76,10 @@ def test_tc_vs_oracle_scales_and_near_ties(scale):
     B, K, L = 6000, 256, 3
     x, cbs = _inputs(B, K, L, seed=3, scale=scale)
     cbs[0][17] = cbs[0][5]                          # exact duplicate
+    g2 = torch.Generator().manual_seed(77)
     x[:200] = 0.5 * (cbs[0][torch.arange(200) % K] + cbs[0][(torch.arange(200) + 1) % K]) \
-        + 1e-7 * scale * torch.randn(200, 32)
-    x[200:260] = cbs[0][5] + 1e-4 * scale * torch.randn(60, 32)
+        + 1e-7 * scale * torch.randn(200, 32, generator=g2)
+    x[200:260] = cbs[0][5] + 1e-4 * scale * torch.randn(60, 32, generator=g2)
     ref = O.rq_forward(x, cbs, O.MODE_EVAL)
     emb, res, ids, loss = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), RF.MODE_EVAL, impl=RF.IMPL_TCGEN05)
     assert _lib.lib().rq_debug_tc_timeout_flag() == 0
