@@ -1,4 +1,4 @@
-// Exact fp32 CUDA-core kernels for the fused L-level residual quantiser (forward + backward).
+// Exact fp32 CUDA-core kernel for the fused L-level residual quantiser (forward).
 //
 // One thread owns one item row for all L levels: the residual never leaves registers
 // between levels (modules/rqvae.py:124-131 in the reference round-trips it through HBM
@@ -162,93 +162,6 @@ __global__ void __launch_bounds__(kSimtThreads) rq_fwd_simt_kernel(FwdParams p) 
 }
 
 // ---------------------------------------------------------------------------------------------
-// Backward for EVAL / STE / ROTATION_TRICK (closed forms of SURVEY.md §8 a11).  One thread per
-// row walks the levels in reverse keeping the running gradient w.r.t. the residual in
-// registers; codebook gradients are scattered with 16-byte L2 reductions (REDG.ADD.F32x4).
-template <int D>
-__global__ void __launch_bounds__(kSimtThreads) rq_bwd_simt_kernel(BwdParams p) {
-    const int64_t row = (int64_t)blockIdx.x * kSimtThreads + threadIdx.x;
-    if (row >= p.B) return;
-    const float gl = p.g_loss ? p.g_loss[row] : 0.f;
-    float G[D];  // d objective / d residual_{l+1} while processing level l
-#pragma unroll
-    for (int j = 0; j < D; ++j) G[j] = 0.f;
-    for (int l = p.L - 1; l >= 0; --l) {
-        const int64_t off = ((int64_t)l * p.B + row) * D;
-        const int64_t id = p.ids[(int64_t)l * p.B + row];
-        const float4* r4 = reinterpret_cast<const float4*>(p.res + off);
-        const float4* e4 = reinterpret_cast<const float4*>(p.cb + ((int64_t)l * p.K + id) * D);
-        const float4* g4 = p.g_emb ? reinterpret_cast<const float4*>(p.g_emb + off) : nullptr;
-        const float4* t4 = p.g_res ? reinterpret_cast<const float4*>(p.g_res + off) : nullptr;
-        float* dst = p.g_cb + ((int64_t)l * p.K + id) * D;
-        // Only G stays in registers; r, e and the upstream gradient are re-read per pass (they
-        // sit in L1 after the first touch), which keeps D=64/128 free of spills.
-        float iu = 0.f, iq = 0.f, iw = 0.f, lam = 0.f, gw = 0.f, gq = 0.f;
-        if (p.mode == RQ_MODE_ROTATION_TRICK) {
-            float nx2 = 0.f, ne2 = 0.f, ns = 0.f;
-#pragma unroll
-            for (int j = 0; j < D / 4; ++j) {
-                float4 r = __ldg(r4 + j), e = __ldg(e4 + j);
-                nx2 = fmaf(r.x, r.x, nx2); nx2 = fmaf(r.y, r.y, nx2); nx2 = fmaf(r.z, r.z, nx2); nx2 = fmaf(r.w, r.w, nx2);
-                ne2 = fmaf(e.x, e.x, ne2); ne2 = fmaf(e.y, e.y, ne2); ne2 = fmaf(e.z, e.z, ne2); ne2 = fmaf(e.w, e.w, ne2);
-            }
-            float nx = sqrtf(nx2), ne = sqrtf(ne2);
-            iu = 1.0f / (nx + 1e-8f); iq = 1.0f / (ne + 1e-8f);
-            lam = ne / (nx + 1e-6f);
-#pragma unroll
-            for (int j = 0; j < D / 4; ++j) {
-                float4 r = __ldg(r4 + j), e = __ldg(e4 + j);
-                float s0 = r.x * iu + e.x * iq, s1 = r.y * iu + e.y * iq, s2 = r.z * iu + e.z * iq, s3 = r.w * iu + e.w * iq;
-                ns = fmaf(s0, s0, ns); ns = fmaf(s1, s1, ns); ns = fmaf(s2, s2, ns); ns = fmaf(s3, s3, ns);
-            }
-            iw = 1.0f / fmaxf(sqrtf(ns), 1e-6f);
-#pragma unroll
-            for (int j = 0; j < D / 4; ++j) {
-                float4 r = __ldg(r4 + j), e = __ldg(e4 + j);
-                float4 g = g4 ? __ldg(g4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-                const float rr[4] = {r.x, r.y, r.z, r.w}, ee[4] = {e.x, e.y, e.z, e.w}, gg[4] = {g.x, g.y, g.z, g.w};
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    float u = rr[c] * iu, q = ee[c] * iq, w = (u + q) * iw;
-                    float gs = lam * (gg[c] - G[4 * j + c]);     // out_l receives g_emb - G
-                    gw = fmaf(gs, w, gw);
-                    gq = fmaf(gs, q, gq);
-                }
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < D / 4; ++j) {
-            float4 r = __ldg(r4 + j), e = __ldg(e4 + j);
-            float4 g = g4 ? __ldg(g4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-            float4 t = t4 ? __ldg(t4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-            const float rr[4] = {r.x, r.y, r.z, r.w}, ee[4] = {e.x, e.y, e.z, e.w}, gg[4] = {g.x, g.y, g.z, g.w},
-                        tt[4] = {t.x, t.y, t.z, t.w};
-            float gc[4];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                // res_{l+1} = r_l - out_l  =>  out_l receives -G, r_l receives +G
-                float go = gg[c] - G[4 * j + c];
-                float Gn = G[4 * j + c];
-                gc[c] = 2.f * (ee[c] - rr[c]) * gl;                        // d emb_loss / d e
-                if (p.mode == RQ_MODE_STE) {
-                    Gn += go;                                              // d out / d r = I
-                } else if (p.mode == RQ_MODE_ROTATION_TRICK) {
-                    float u = rr[c] * iu, q = ee[c] * iq, w = (u + q) * iw;
-                    Gn += (lam * go - 2.f * gw * w) + 2.f * gq * u;
-                } else {                                                   // EVAL: out = C[ids]
-                    gc[c] += go;
-                }
-                Gn += 2.f * p.beta * (rr[c] - ee[c]) * gl;                 // d query_loss / d r
-                Gn += tt[c];
-                G[4 * j + c] = Gn;
-            }
-            red_add_v4(dst + 4 * j, gc[0], gc[1], gc[2], gc[3]);
-        }
-    }
-    store_row<D>(p.g_x + row * D, G);
-}
-
-// ---------------------------------------------------------------------------------------------
 template <int D>
 static int launch_fwd(const FwdParams& p0, cudaStream_t st) {
     FwdParams p = p0;
@@ -281,30 +194,6 @@ int quantize_forward_simt(const FwdParams& p, int D, cudaStream_t st) {
         case 32: return launch_fwd<32>(p, st);
         case 64: return launch_fwd<64>(p, st);
         case 128: return launch_fwd<128>(p, st);
-        default:
-            set_error("unsupported embed_dim D=%d (supported: 4, 8, 16, 32, 64, 128)", D);
-            return RQ_ERR_UNSUPPORTED_SHAPE;
-    }
-}
-
-template <int D>
-static int launch_bwd(const BwdParams& p, cudaStream_t st) {
-    dim3 grid((unsigned)((p.B + kSimtThreads - 1) / kSimtThreads));
-    rq_bwd_simt_kernel<D><<<grid, kSimtThreads, 0, st>>>(p);
-    RQ_LAUNCHED();
-    return 0;
-}
-
-int quantize_backward_simt(const BwdParams& p, int D, cudaStream_t st) {
-    RQ_CUDA(cudaMemsetAsync(p.g_cb, 0, (size_t)p.L * p.K * D * sizeof(float), st));
-    if (p.B == 0) return 0;
-    switch (D) {
-        case 4: return launch_bwd<4>(p, st);
-        case 8: return launch_bwd<8>(p, st);
-        case 16: return launch_bwd<16>(p, st);
-        case 32: return launch_bwd<32>(p, st);
-        case 64: return launch_bwd<64>(p, st);
-        case 128: return launch_bwd<128>(p, st);
         default:
             set_error("unsupported embed_dim D=%d (supported: 4, 8, 16, 32, 64, 128)", D);
             return RQ_ERR_UNSUPPORTED_SHAPE;
