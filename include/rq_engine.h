@@ -168,6 +168,10 @@ int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B,
  * (||c||^2 - 2 x.c) on subsequent launches (NULL disables). */
 int rq_debug_tc_timeout_flag(void);
 int rq_debug_tc_set_accumulator_dump(float* device_buf_128x256);
+/* Profiling hook: a [32 warps][64 marks] int64 device buffer that receives clock64() stamps of CTA 0's
+ * phases (prologue end, then per level: operand written, MMAs issued, accumulator ready, scan done,
+ * level done) on subsequent launches (NULL disables). */
+int rq_debug_tc_set_timeline(long long* device_buf_32x64);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

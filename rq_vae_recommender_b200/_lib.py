@@ -45,6 +45,7 @@ SIGNATURES = {
     "rq_gather_tokens": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "rq_debug_tc_timeout_flag": (c_int, []),
     "rq_debug_tc_set_accumulator_dump": (c_int, [c_void_p]),
+    "rq_debug_tc_set_timeline": (c_int, [c_void_p]),
     "rq_semantic_ids_host": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                      c_int, c_void_p]),
 }

@@ -60,7 +60,8 @@ extern "C" int rq_quantize_forward(const float* x, const float* codebooks, int64
     p.beta = beta; p.temp = temperature; p.gu = gumbel_u; p.seed = seed; p.offset = offset;
     p.emb = emb_out; p.res = residuals; p.ids = ids; p.loss = loss; p.KC = 0;
     cudaStream_t st = (cudaStream_t)stream;
-    const bool tc_ok = tc_supported(D, K, L, mode, distance);
+    // the tcgen05 family stages the codebooks with TMA bulk copies (16-byte aligned source rows)
+    const bool tc_ok = tc_supported(D, K, L, mode, distance) && (((uintptr_t)codebooks & 15) == 0) && (((uintptr_t)x & 31) == 0);
     if (impl == RQ_IMPL_TCGEN05) {
         RQ_CHECK_ARG(tc_ok, RQ_ERR_UNSUPPORTED_SHAPE,
                      "rq_quantize_forward: (D=%d,K=%d,L=%d,mode=%d,dist=%d) is not served by the tcgen05 family", D, K, L,

@@ -51,6 +51,18 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// MUFU-based reciprocal / square root (<= 1-2 ulp): scalar coefficients of the estimators only, never distances
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_sqrt(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
     // REDG.E.ADD.F32x4 — one L2 reduction per 16 bytes (sm_90+)
     asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)

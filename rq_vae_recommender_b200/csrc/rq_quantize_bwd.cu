@@ -37,7 +37,47 @@ __device__ __forceinline__ float4 ldg_stream4(const float* p) {
     return v;
 }
 
-template <int D>
+constexpr int kBwdMaxL = 4;          // levels whose loads are hoisted (all of them in flight at once)
+
+// One level of the reverse walk.  G = d objective / d residual_{l+1} on entry, d/d residual_l on exit.
+template <int LPR>
+__device__ __forceinline__ void bwd_level(int mode, float beta, float gl, const float4& r, const float4& go_in,
+                                          const float4& t, const float4& e, float4& G, float4& gc) {
+    // res_{l+1} = r_l - out_l  =>  out_l receives -G, r_l receives +G
+    const float4 go = make_float4(go_in.x - G.x, go_in.y - G.y, go_in.z - G.z, go_in.w - G.w);
+    gc = make_float4(2.f * (e.x - r.x) * gl, 2.f * (e.y - r.y) * gl, 2.f * (e.z - r.z) * gl,
+                     2.f * (e.w - r.w) * gl);                                  // d emb_loss / d e
+    if (mode == RQ_MODE_STE) {
+        G.x += go.x; G.y += go.y; G.z += go.z; G.w += go.w;                    // d out / d r = I
+    } else if (mode == RQ_MODE_ROTATION_TRICK) {
+        const float nx2 = group_sum<LPR>(dot4(r, r)), ne2 = group_sum<LPR>(dot4(e, e));
+        const float nx = sqrtf(nx2), ne = sqrtf(ne2);
+        const float iu = 1.0f / (nx + 1e-8f), iq = 1.0f / (ne + 1e-8f);
+        const float lam = ne / (nx + 1e-6f);
+        const float4 u = make_float4(r.x * iu, r.y * iu, r.z * iu, r.w * iu);
+        const float4 q = make_float4(e.x * iq, e.y * iq, e.z * iq, e.w * iq);
+        float4 w = make_float4(u.x + q.x, u.y + q.y, u.z + q.z, u.w + q.w);
+        const float iw = 1.0f / fmaxf(sqrtf(group_sum<LPR>(dot4(w, w))), 1e-6f);
+        w.x *= iw; w.y *= iw; w.z *= iw; w.w *= iw;
+        const float4 gs = make_float4(lam * go.x, lam * go.y, lam * go.z, lam * go.w);
+        const float gw = group_sum<LPR>(dot4(gs, w)), gq = group_sum<LPR>(dot4(gs, q));
+        G.x += (gs.x - 2.f * gw * w.x) + 2.f * gq * u.x;
+        G.y += (gs.y - 2.f * gw * w.y) + 2.f * gq * u.y;
+        G.z += (gs.z - 2.f * gw * w.z) + 2.f * gq * u.z;
+        G.w += (gs.w - 2.f * gw * w.w) + 2.f * gq * u.w;
+    } else {                                                                   // EVAL: out = C[ids]
+        gc.x += go.x; gc.y += go.y; gc.z += go.z; gc.w += go.w;
+    }
+    const float b2 = 2.f * beta * gl;                                          // d query_loss / d r
+    G.x += b2 * (r.x - e.x) + t.x; G.y += b2 * (r.y - e.y) + t.y;
+    G.z += b2 * (r.z - e.z) + t.z; G.w += b2 * (r.w - e.w) + t.w;
+}
+
+// HOIST = true (L <= kBwdMaxL): the ids of every level are loaded first, then every level's
+// residual / upstream-gradient / codeword loads are issued before any arithmetic, so one lane
+// group has 3L+ independent 16-byte loads in flight — the kernel is pure latency otherwise
+// (ids -> codeword gather -> math, L times in series).
+template <int D, bool HOIST>
 __global__ void __launch_bounds__(kBwdThreads) rq_bwd_stream_kernel(BwdParams p, int64_t n_groups) {
     constexpr int LPR = D / 4;          // lanes per row
     constexpr int RPW = 32 / LPR;       // rows per warp instruction
@@ -45,52 +85,53 @@ __global__ void __launch_bounds__(kBwdThreads) rq_bwd_stream_kernel(BwdParams p,
     const int sub = lane % LPR, rsel = lane / LPR;
     const int64_t warp_global = ((int64_t)blockIdx.x * kBwdThreads + threadIdx.x) >> 5;
     const int64_t n_warps = ((int64_t)gridDim.x * kBwdThreads) >> 5;
-    const float zero4[4] = {0.f, 0.f, 0.f, 0.f};
-    (void)zero4;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
 
     for (int64_t g = warp_global; g < n_groups; g += n_warps) {
         const int64_t row = g * RPW + rsel;
         const bool valid = row < p.B;
         const int64_t rowc = valid ? row : (p.B - 1);      // clamp: tail lanes recompute the last row, never store
         const float gl = p.g_loss ? __ldg(p.g_loss + rowc) : 0.f;
-        float4 G = make_float4(0.f, 0.f, 0.f, 0.f);        // d objective / d residual_{l+1}
-        for (int l = p.L - 1; l >= 0; --l) {
-            const int64_t off = ((int64_t)l * p.B + rowc) * D + sub * 4;
-            const int64_t id = __ldg(p.ids + (int64_t)l * p.B + rowc);
-            const float4 r = ldg_stream4(p.res + off);
-            const float4 go_in = p.g_emb ? ldg_stream4(p.g_emb + off) : make_float4(0.f, 0.f, 0.f, 0.f);
-            const float4 t = p.g_res ? ldg_stream4(p.g_res + off) : make_float4(0.f, 0.f, 0.f, 0.f);
-            const int64_t coff = ((int64_t)l * p.K + id) * D + sub * 4;
-            const float4 e = ldg_nc4(p.cb + coff);
-            // res_{l+1} = r_l - out_l  =>  out_l receives -G, r_l receives +G
-            const float4 go = make_float4(go_in.x - G.x, go_in.y - G.y, go_in.z - G.z, go_in.w - G.w);
-            float4 gc = make_float4(2.f * (e.x - r.x) * gl, 2.f * (e.y - r.y) * gl, 2.f * (e.z - r.z) * gl,
-                                    2.f * (e.w - r.w) * gl);                       // d emb_loss / d e
-            if (p.mode == RQ_MODE_STE) {
-                G.x += go.x; G.y += go.y; G.z += go.z; G.w += go.w;                // d out / d r = I
-            } else if (p.mode == RQ_MODE_ROTATION_TRICK) {
-                const float nx2 = group_sum<LPR>(dot4(r, r)), ne2 = group_sum<LPR>(dot4(e, e));
-                const float nx = sqrtf(nx2), ne = sqrtf(ne2);
-                const float iu = 1.0f / (nx + 1e-8f), iq = 1.0f / (ne + 1e-8f);
-                const float lam = ne / (nx + 1e-6f);
-                const float4 u = make_float4(r.x * iu, r.y * iu, r.z * iu, r.w * iu);
-                const float4 q = make_float4(e.x * iq, e.y * iq, e.z * iq, e.w * iq);
-                float4 w = make_float4(u.x + q.x, u.y + q.y, u.z + q.z, u.w + q.w);
-                const float iw = 1.0f / fmaxf(sqrtf(group_sum<LPR>(dot4(w, w))), 1e-6f);
-                w.x *= iw; w.y *= iw; w.z *= iw; w.w *= iw;
-                const float4 gs = make_float4(lam * go.x, lam * go.y, lam * go.z, lam * go.w);
-                const float gw = group_sum<LPR>(dot4(gs, w)), gq = group_sum<LPR>(dot4(gs, q));
-                G.x += (gs.x - 2.f * gw * w.x) + 2.f * gq * u.x;
-                G.y += (gs.y - 2.f * gw * w.y) + 2.f * gq * u.y;
-                G.z += (gs.z - 2.f * gw * w.z) + 2.f * gq * u.z;
-                G.w += (gs.w - 2.f * gw * w.w) + 2.f * gq * u.w;
-            } else {                                                               // EVAL: out = C[ids]
-                gc.x += go.x; gc.y += go.y; gc.z += go.z; gc.w += go.w;
+        float4 G = z4;                                     // d objective / d residual_{l+1}
+        if (HOIST) {
+            int64_t id[kBwdMaxL];
+            float4 r[kBwdMaxL], go[kBwdMaxL], t[kBwdMaxL], e[kBwdMaxL];
+#pragma unroll
+            for (int l = 0; l < kBwdMaxL; ++l)
+                if (l < p.L) id[l] = __ldg(p.ids + (int64_t)l * p.B + rowc);
+#pragma unroll
+            for (int l = 0; l < kBwdMaxL; ++l) {
+                if (l < p.L) {
+                    const int64_t off = ((int64_t)l * p.B + rowc) * D + sub * 4;
+                    r[l] = ldg_stream4(p.res + off);
+                    go[l] = p.g_emb ? ldg_stream4(p.g_emb + off) : z4;
+                    t[l] = p.g_res ? ldg_stream4(p.g_res + off) : z4;
+                }
             }
-            const float b2 = 2.f * p.beta * gl;                                    // d query_loss / d r
-            G.x += b2 * (r.x - e.x) + t.x; G.y += b2 * (r.y - e.y) + t.y;
-            G.z += b2 * (r.z - e.z) + t.z; G.w += b2 * (r.w - e.w) + t.w;
-            if (valid) red_add_v4(p.g_cb + coff, gc.x, gc.y, gc.z, gc.w);
+#pragma unroll
+            for (int l = 0; l < kBwdMaxL; ++l)
+                if (l < p.L) e[l] = ldg_nc4(p.cb + ((int64_t)l * p.K + id[l]) * D + sub * 4);
+#pragma unroll
+            for (int l = kBwdMaxL - 1; l >= 0; --l) {
+                if (l < p.L) {
+                    float4 gc;
+                    bwd_level<LPR>(p.mode, p.beta, gl, r[l], go[l], t[l], e[l], G, gc);
+                    if (valid) red_add_v4(p.g_cb + ((int64_t)l * p.K + id[l]) * D + sub * 4, gc.x, gc.y, gc.z, gc.w);
+                }
+            }
+        } else {
+            for (int l = p.L - 1; l >= 0; --l) {
+                const int64_t off = ((int64_t)l * p.B + rowc) * D + sub * 4;
+                const int64_t id = __ldg(p.ids + (int64_t)l * p.B + rowc);
+                const float4 r = ldg_stream4(p.res + off);
+                const float4 go_in = p.g_emb ? ldg_stream4(p.g_emb + off) : z4;
+                const float4 t = p.g_res ? ldg_stream4(p.g_res + off) : z4;
+                const int64_t coff = ((int64_t)l * p.K + id) * D + sub * 4;
+                const float4 e = ldg_nc4(p.cb + coff);
+                float4 gc;
+                bwd_level<LPR>(p.mode, p.beta, gl, r, go_in, t, e, G, gc);
+                if (valid) red_add_v4(p.g_cb + coff, gc.x, gc.y, gc.z, gc.w);
+            }
         }
         if (valid) *reinterpret_cast<float4*>(p.g_x + row * D + sub * 4) = G;
     }
@@ -102,9 +143,10 @@ static int launch_bwd(const BwdParams& p, cudaStream_t st) {
     const int64_t n_groups = (p.B + RPW - 1) / RPW;
     const int warps_per_block = kBwdThreads / 32;
     int64_t blocks = (n_groups + warps_per_block - 1) / warps_per_block;
-    const int64_t cap = (int64_t)sm_count() * 8;           // 8 resident CTAs of 256 threads per SM
+    const int64_t cap = (int64_t)sm_count() * 32;          // a few waves; each warp walks <= a handful of row groups
     if (blocks > cap) blocks = cap;
-    rq_bwd_stream_kernel<D><<<(unsigned)blocks, kBwdThreads, 0, st>>>(p, n_groups);
+    if (p.L <= kBwdMaxL) rq_bwd_stream_kernel<D, true><<<(unsigned)blocks, kBwdThreads, 0, st>>>(p, n_groups);
+    else rq_bwd_stream_kernel<D, false><<<(unsigned)blocks, kBwdThreads, 0, st>>>(p, n_groups);
     RQ_LAUNCHED();
     return 0;
 }

@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(kSimtThreads) rq_fwd_simt_kernel(FwdParams p) 
                 lvl = dsq + p.beta * dsq;
             } else {
                 load_row<D>(cbl + (int64_t)bi * D, e);
-                lvl = level_epilogue<D>(p.mode, p.beta, r, e, o);
+                lvl = level_epilogue<D>(p.mode, p.beta, r, e, xx, o);
             }
             loss_acc += lvl;
             const int64_t off = ((int64_t)l * p.B + row) * D;

@@ -1,21 +1,28 @@
 // tcgen05 family: fused L-level residual quantiser on the 5th-gen tensor cores (sm_100a).
 //
-// Per CTA (one per SM, persistent over 128-row tiles; two 128-thread warpgroups, each owning one
-// tile at a time and one 128x256 fp32 accumulator in TMEM — 2 x 256 = all 512 columns):
+// One persistent CTA per SM, NWG (4, or 2 when the operand tiles of L levels leave no room) 128-thread
+// warpgroups.  A warpgroup owns one 128-row tile at a time (UMMA M = 128; one thread = one row = one
+// TMEM lane) and walks its L levels with the residual in registers.  TMEM holds two 128x256 fp32
+// accumulators; warpgroups w and w+2 take turns on accumulator w&1 (a shared-memory try-lock), so
+// while one of them is in its MMA + scan phase the other does its CUDA-core epilogue.
 //
 //   prologue   every level's codebook is converted once per CTA into the UMMA B operand
 //              [-2*hi(c) | -2*lo(c)] (bf16 split, 128-byte swizzled rows, K-major) plus a small
-//              [hi, mid, lo] split of ||c||^2 (no-swizzle tile) and kept in shared memory.
-//   per level  each thread owns one row: it writes [hi(r) | lo(r)] of its residual as the A
-//              operand row, one elected thread issues 7 tcgen05.mma (N=256, K=16 each):
+//              [hi, mid, lo] split of ||c||^2 (no-swizzle tile), kept in shared memory.
+//   per level  each thread writes [hi(r) | lo(r)] of its residual as the A operand row; one elected
+//              thread issues 7 tcgen05.mma (N=256, K=16 each):
 //                 hi(r).hi(c) + lo(r).hi(c) + hi(r).lo(c)  (+ 1 . ||c||^2)
-//              so the accumulator holds  ||c||^2 - 2 r.c  to ~2^-17 relative.  The epilogue reads
-//              its row from TMEM twice: pass 1 takes the row minimum (FMNMX3), pass 2 flags every
-//              code within a proven error bound of it.  A single flagged code (the usual case) is
-//              the argmin; several are re-scored in fp32 with exactly the arithmetic of the SIMT
-//              family, lowest index winning ties — so ids are bit-identical to the SIMT kernel.
-//              Then: gather the fp32 codeword, mode epilogue (STE / rotation trick / eval), loss,
-//              outputs, residual update in registers — the next level never touches HBM.
+//              so the accumulator holds  ||c||^2 - 2 r.c  to ~2^-17 relative.
+//   scan       ONE pass over the TMEM row keeps two families of running minima: per 16-column group
+//              (A, 16 of them) and per column-mod-16 class (B, 16 of them) — one FMNMX3 per two values
+//              each.  Any two distinct columns differ in group or in class, so "a second value within
+//              the error bound of the minimum" shows up as a close runner-up in A or in B; when neither
+//              has one (the usual case) argmin = (argmin group, argmin class).  Otherwise the warp
+//              re-reads the row, flags every code within the bound and re-scores those in fp32 with
+//              exactly the arithmetic of the SIMT family, lowest index winning — so ids are
+//              bit-identical to the SIMT kernel.
+//   epilogue   gather the fp32 codeword, estimator (STE / rotation trick / eval), loss, outputs,
+//              residual update in registers — the next level never touches HBM.
 #include <stdlib.h>
 
 #include "rq_common.cuh"
@@ -30,24 +37,26 @@ constexpr int D = 32;            // latent dim served by this kernel
 constexpr int KC = 256;          // codes per level (UMMA N)
 constexpr int TILE_M = 128;      // rows per tile (UMMA M)
 constexpr int MAX_L = 4;
-constexpr int THREADS = 256;     // two warpgroups
 constexpr int B_TILE_BYTES = KC * 128;       // [256 codes][-2hi(32) | -2lo(32)] bf16, SW128
 constexpr int CC_TILE_BYTES = KC * 32;       // [256 codes][16 bf16], no swizzle, 8x16B core matrices
 constexpr int A_TILE_BYTES = TILE_M * 128;   // [128 rows][hi(32) | lo(32)] bf16, SW128
 constexpr int ONES_TILE_BYTES = TILE_M * 32; // [128 rows][1,1,1,0...] bf16, no swizzle
 
 struct SmemLayout {
-    int b_tiles, cc_tiles, cc_f32, a_tiles, ones, misc, total;
+    int b_tiles, cc_tiles, cc_f32, a_tiles, park, ones, misc, total;
 };
-__host__ __device__ inline SmemLayout smem_layout(int L) {
+// nwg == 4: one A tile per accumulator (the two warpgroups sharing it take turns) and a 16 KB fp32
+// parking area per warpgroup for the residual rows while the scan needs the registers.
+__host__ __device__ inline SmemLayout smem_layout(int L, int nwg) {
     SmemLayout s;
     int off = 0;
     s.b_tiles = off; off += L * B_TILE_BYTES;
     s.a_tiles = off; off += 2 * A_TILE_BYTES;
+    s.park = off; off += (nwg == 4 ? 4 : 0) * A_TILE_BYTES;
     s.cc_tiles = off; off += L * CC_TILE_BYTES;
     s.ones = off; off += ONES_TILE_BYTES;
     s.cc_f32 = off; off += L * KC * 4;
-    s.misc = off; off += 128;
+    s.misc = off; off += 256;
     s.total = off;
     return s;
 }
@@ -64,85 +73,177 @@ __device__ __forceinline__ uint32_t nosw_off(int r, int c) {
 }
 }  // namespace tc
 
+
 struct TcParams {
     FwdParams f;
-    int* err;        // device flag: set when an mbarrier wait timed out
+    int* err;        // device flag: set when an mbarrier / lock wait timed out
     int n_tiles;
     float* dbg_acc;  // optional [128][256] dump of tile 0 / level 0's accumulator (tests only)
+    long long* dbg_tl;  // optional [32 warps][64 marks] clock64 timeline of CTA 0 (profiling only)
 };
+#define RQ_TL(mark)                                                                           \
+    do {                                                                                      \
+        if (P.dbg_tl && blockIdx.x == 0 && lane == 0) P.dbg_tl[warp * 64 + (mark)] = clock64(); \
+    } while (0)
+// same, but the stamp is taken only once `val` (a float) has arrived
+#define RQ_TL_DEP(mark, val)                                                                  \
+    do {                                                                                      \
+        if (P.dbg_tl && blockIdx.x == 0 && lane == 0)                                         \
+            P.dbg_tl[warp * 64 + (mark)] = clock64() + (__float_as_int(val) == 0x7fc12345);  \
+    } while (0)
 
-__global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
+namespace tc {
+
+// top-2 of 16 packed keys (value bits with the entry index in the low 4 mantissa bits)
+__device__ __forceinline__ void top2_of16(const float (&k)[16], float& m1, float& m2) {
+    float lo[8], hi[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        lo[i] = fminf(k[2 * i], k[2 * i + 1]);
+        hi[i] = fmaxf(k[2 * i], k[2 * i + 1]);
+    }
+#pragma unroll
+    for (int s = 1; s < 8; s *= 2) {
+#pragma unroll
+        for (int i = 0; i + s < 8; i += 2 * s) {
+            const float a = fmaxf(lo[i], lo[i + s]);
+            hi[i] = ptx::fmin3(a, hi[i], hi[i + s]);
+            lo[i] = fminf(lo[i], lo[i + s]);
+        }
+    }
+    m1 = lo[0];
+    m2 = hi[0];
+}
+__device__ __forceinline__ float pack_idx(float v, int i) {
+    return __uint_as_float((__float_as_uint(v) & 0xFFFFFFF0u) | (uint32_t)i);
+}
+
+}  // namespace tc
+
+template <int NWG>
+__global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     using namespace tc;
+    constexpr int THREADS = 128 * NWG;
+    constexpr bool SHARE = (NWG == 4);      // warpgroups w and w+2 alternate on accumulator / A tile w&1
     const FwdParams& p = P.f;
     extern __shared__ uint8_t smem_raw[];
     // 128B-swizzled UMMA tiles need 1024-byte alignment; the launch over-allocates by 1 KB
     uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
-    const SmemLayout S = smem_layout(p.L);
+    const SmemLayout S = smem_layout(p.L, NWG);
     uint8_t* sB = smem + S.b_tiles;
     uint8_t* sA = smem + S.a_tiles;
+    uint8_t* sPark = smem + S.park;
     uint8_t* sCCt = smem + S.cc_tiles;
     uint8_t* sOnes = smem + S.ones;
     float* sCC = reinterpret_cast<float*>(smem + S.cc_f32);
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + S.misc);          // [2]
-    uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(smem + S.misc + 16);
-    int* cmax_bits = reinterpret_cast<int*>(smem + S.misc + 32);           // [MAX_L] max ||c||^2 per level
+    uint64_t* mbar_full = reinterpret_cast<uint64_t*>(smem + S.misc);        // [4] accumulator ready (per warpgroup)
+    uint64_t* mbar_free = reinterpret_cast<uint64_t*>(smem + S.misc + 32);   // [2] accumulator read out (per slot)
+    uint64_t* mbar_load = reinterpret_cast<uint64_t*>(smem + S.misc + 48);   // [1] codebook bulk copy landed
+    uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(smem + S.misc + 64);
+    int* cmax_bits = reinterpret_cast<int*>(smem + S.misc + 80);             // [MAX_L] max ||c||^2 per level
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wg = tid >> 7, wtid = tid & 127;
+    const int slot = wg & 1;
+    RQ_TL(0);
 
-    // ---- prologue: barriers, TMEM, operand tiles ---------------------------------------------------
+    // ---- codebooks: one TMA bulk copy per level, fp32 rows straight into that level's B-tile space --------
     if (tid == 0) {
-        ptx::mbar_init(&mbar[0], 1);
-        ptx::mbar_init(&mbar[1], 1);
-        ptx::fence_mbar_init();
-    }
-    if (tid < MAX_L) cmax_bits[tid] = 0;
-    if (warp == 0) ptx::tmem_alloc(tmem_base_s, 512);
-    // ones tile: k = 0,1,2 -> 1.0 (multiplies hi/mid/lo of ||c||^2), rest 0
-    for (int i = tid; i < TILE_M * 2; i += THREADS) {
-        int r = i >> 1, c = i & 1;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (c == 0) { v.x = 0x3F803F80u; v.y = 0x00003F80u; }
-        *reinterpret_cast<uint4*>(sOnes + nosw_off(r, c)) = v;
-    }
-    __syncthreads();
-    // B operand: work item = (level, code, 8-element chunk); every thread first issues ALL of its
-    // 32-byte codebook loads (the prologue is pure latency otherwise), then converts.
-    {
-        constexpr int ITEMS = MAX_L * 4;          // L * 256 codes * 4 chunks / 256 threads
-        float cv[ITEMS][8];
 #pragma unroll
-        for (int it = 0; it < ITEMS; ++it) {
-            const int i = it * THREADS + tid, l = i >> 10, k = (i >> 2) & 255, q = i & 3;
-            if (l < p.L && k < p.K) {
-                ptx::ld_global_v8(p.cb + ((int64_t)l * p.K + k) * D + q * 8, cv[it]);
+        for (int i = 0; i < 4; ++i) ptx::mbar_init(&mbar_full[i], 1);
+        ptx::mbar_init(&mbar_free[0], 4);
+        ptx::mbar_init(&mbar_free[1], 4);
+        ptx::mbar_init(mbar_load, 1);
+        ptx::fence_mbar_init();
+        const uint32_t level_bytes = (uint32_t)p.K * D * 4;
+        ptx::mbar_arrive_expect_tx(mbar_load, level_bytes * p.L);
+        for (int l = 0; l < p.L; ++l)
+            ptx::bulk_g2s(sB + l * B_TILE_BYTES, p.cb + (int64_t)l * p.K * D, level_bytes, mbar_load);
+    }
+    RQ_TL(45);
+    // ---- first tile's rows: HBM loads in flight during the whole prologue ------------------------------
+    // tile t -> CTA t % grid, warpgroup (t / grid) % NWG: every SM gets floor or ceil of n_tiles / grid
+    const int my_tiles = (P.n_tiles > (int)blockIdx.x) ? (P.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    // tiles of this CTA are numbered 0..my_tiles-1; warpgroup w owns those with index % NWG == w
+    const int n_mine = (my_tiles > wg) ? (my_tiles - 1 - wg) / NWG + 1 : 0;
+    const int n_partner = SHARE ? ((my_tiles > (wg ^ 2)) ? (my_tiles - 1 - (wg ^ 2)) / NWG + 1 : 0) : 0;
+    float r[D];
+    float4 xin[8];                          // SHARE: coalesced image of this warp's 32 rows (lane = 16-byte chunk)
+    const int wrow0 = (warp & 3) * 32;      // first tile row of this warp
+    {
+        const int64_t trow0 = ((int64_t)blockIdx.x + (int64_t)gridDim.x * wg) * TILE_M;
+        if (SHARE) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int rr = wrow0 + 4 * i + (lane >> 3);
+                xin[i] = (n_mine > 0 && trow0 + rr < p.B)
+                             ? ptx::ld_global_stream_v4(p.x + (trow0 + rr) * D + (lane & 7) * 4)
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        } else {
+            const int64_t row = trow0 + wtid;
+            if (n_mine > 0 && row < p.B) {
+#pragma unroll
+                for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + row * D + j, &r[j]);
             } else {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) cv[it][j] = 0.f;
+                for (int j = 0; j < D; ++j) r[j] = 0.f;
             }
         }
+    }
+    RQ_TL(46);
+    if (tid < MAX_L) cmax_bits[tid] = 0;
+    if (warp == 1) ptx::tmem_alloc(tmem_base_s, 512);
+    RQ_TL(47);
+    // ones tile: k = 0,1,2 -> 1.0 (multiplies hi/mid/lo of ||c||^2), rest 0
+    for (int i = tid; i < TILE_M * 2; i += THREADS) {
+        int rr = i >> 1, c = i & 1;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (c == 0) { v.x = 0x3F803F80u; v.y = 0x00003F80u; }
+        *reinterpret_cast<uint4*>(sOnes + nosw_off(rr, c)) = v;
+    }
+    RQ_TL(48);
+    __syncthreads();                                   // barrier inits + cmax zeros visible
+    RQ_TL(1);
+    if (!ptx::mbar_wait(mbar_load, 0)) {
+        if (P.err) atomicExch(P.err, 1);
+    }
+    RQ_TL(2);
+    // ---- in-place conversion: work item = (level, code, 8-element chunk); the four lanes of a code read
+    // its 128-byte fp32 row and rewrite the same 128 bytes as [-2hi | -2lo] bf16 in the swizzled order ------
+    {
+        const int n_items = p.L * KC * 4;                          // multiple of THREADS
+        for (int i = tid; i < n_items; i += THREADS) {
+            const int l = i >> 10, k = (i >> 2) & 255, q = i & 3;
+            uint8_t* tileB = sB + l * B_TILE_BYTES;
+            float cv[8];
+            if (k < p.K) {
+                const float4 v0 = *reinterpret_cast<const float4*>(tileB + k * 128 + q * 32);
+                const float4 v1 = *reinterpret_cast<const float4*>(tileB + k * 128 + q * 32 + 16);
+                cv[0] = v0.x; cv[1] = v0.y; cv[2] = v0.z; cv[3] = v0.w;
+                cv[4] = v1.x; cv[5] = v1.y; cv[6] = v1.z; cv[7] = v1.w;
+            } else {
 #pragma unroll
-        for (int it = 0; it < ITEMS; ++it) {
-            const int i = it * THREADS + tid, l = i >> 10, k = (i >> 2) & 255, q = i & 3;
-            if (l >= p.L) break;                   // uniform across the CTA (l = it >> 2)
+                for (int j = 0; j < 8; ++j) cv[j] = 0.f;
+            }
             uint32_t h[4], lw[4];
             float part = 0.f;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const float a = cv[it][2 * j], b = cv[it][2 * j + 1];
+                const float a = cv[2 * j], b = cv[2 * j + 1];
                 part = fmaf(a, a, part);
                 part = fmaf(b, b, part);
                 ptx::split_pair(-2.f * a, -2.f * b, h[j], lw[j]);
             }
-            uint8_t* tileB = sB + l * B_TILE_BYTES;
-            *reinterpret_cast<uint4*>(tileB + sw128_off(k, q)) = make_uint4(h[0], h[1], h[2], h[3]);
-            *reinterpret_cast<uint4*>(tileB + sw128_off(k, 4 + q)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
             // ||c||^2 in the canonical order shared with the SIMT family (code_sqnorm in rq_rowmath.cuh):
             // 8-wide sequential partials, then (p0+p1)+(p2+p3)
             part += __shfl_xor_sync(0xffffffffu, part, 1);
-            part += __shfl_xor_sync(0xffffffffu, part, 2);
+            part += __shfl_xor_sync(0xffffffffu, part, 2);          // also orders the quad's reads before its writes
+            __syncwarp();
+            *reinterpret_cast<uint4*>(tileB + sw128_off(k, q)) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4*>(tileB + sw128_off(k, 4 + q)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
             if (q == 0) {
-                float cc = (k < p.K) ? part : 1e30f;     // padding codes can never be the minimum
+                float cc = (k < p.K) ? part : 1e30f;              // padding codes can never be the minimum
                 sCC[l * KC + k] = cc;
                 float hh = ptx::bf16_round(cc), mm = ptx::bf16_round(cc - hh), ll = ptx::bf16_round((cc - hh) - mm);
                 *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 0)) =
@@ -152,33 +253,69 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
             }
         }
     }
+    RQ_TL(3);
     ptx::fence_proxy_async_smem();
     ptx::tc_fence_before_sync();
     __syncthreads();
     ptx::tc_fence_after_sync();
+    RQ_TL(4);
     const uint32_t tmem_base = *tmem_base_s;
-    const uint32_t tmem_acc = tmem_base + (uint32_t)(wg * KC);                       // column offset
+    const uint32_t tmem_acc = tmem_base + (uint32_t)(slot * KC);                     // column offset
     const uint32_t tmem_row = tmem_acc + ((uint32_t)((warp & 3) * 32) << 16);        // this warp's lanes
-    uint8_t* sAw = sA + wg * A_TILE_BYTES;
+    uint8_t* sAw = sA + slot * A_TILE_BYTES;
+    uint8_t* sPw = sPark + wg * A_TILE_BYTES;
     const uint32_t idesc = ptx::make_idesc_bf16_f32(TILE_M, KC);
-    uint32_t phase = 0;
+    // Global <-> register traffic of a warp's 32 rows goes through its 4 KB of the parking tile so that
+    // every global instruction covers 4 whole rows (4 lines) instead of one sector of 32 different lines.
+    auto park_store_row = [&](const float (&v)[D]) {              // my row -> parking tile (swizzled, conflict-free)
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<float4*>(sPw + sw128_off(wtid, c)) =
+                make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+    };
+    auto park_load_row = [&](float (&v)[D]) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const float4 t = *reinterpret_cast<const float4*>(sPw + sw128_off(wtid, c));
+            v[4 * c] = t.x; v[4 * c + 1] = t.y; v[4 * c + 2] = t.z; v[4 * c + 3] = t.w;
+        }
+    };
+    auto park_copy_out = [&](float* dst_tile, int64_t trow0) {     // parking tile -> 4 KB of global, coalesced
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int rr = wrow0 + 4 * i + (lane >> 3);
+            const float4 t = *reinterpret_cast<const float4*>(sPw + sw128_off(rr, lane & 7));
+            if (trow0 + rr < p.B) ptx::st_global_v4(dst_tile + (int64_t)rr * D + (lane & 7) * 4, t);
+        }
+    };
+    if (SHARE) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(sPw + sw128_off(wrow0 + 4 * i + (lane >> 3), lane & 7)) = xin[i];
+        __syncwarp();
+        park_load_row(r);
+        __syncwarp();
+    }
+    const int n_partner_uses = n_partner * p.L;
+    const bool is_hi = SHARE && (wg >= 2);
     bool timed_out = false;
+    int use = 0;                                   // this warpgroup's running (tile, level) count
 
-    for (int tile = blockIdx.x * 2 + wg; tile < P.n_tiles; tile += gridDim.x * 2) {
+    for (int it = 0; it < n_mine; ++it) {
+        const int tile = (int)blockIdx.x + (int)gridDim.x * (wg + NWG * it);
         const int64_t row = (int64_t)tile * TILE_M + wtid;
         const bool active = row < p.B;
-        float r[D];
-        if (active) {
-#pragma unroll
-            for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + row * D + j, &r[j]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < D; ++j) r[j] = 0.f;
-        }
+        float xx = dot_self<D>(r);
         float loss_acc = 0.f;
 
-        for (int l = 0; l < p.L; ++l) {
-            // ---- A operand row: [hi(r) | lo(r)] ------------------------------------------------------
+        for (int l = 0; l < p.L; ++l, ++use) {
+            // The use of (accumulator, A tile) `slot` that precedes this one is the partner's: its use
+            // `use` when we are the second warpgroup of the pair, `use - 1` when we are the first.
+            const int prev = is_hi ? use : use - 1;
+            const bool wait_partner = SHARE && prev >= 0 && prev < n_partner_uses;
+            // its MMAs must have finished reading the A tile before we overwrite it
+            if (wait_partner && !ptx::mbar_wait(&mbar_full[wg ^ 2], prev & 1)) timed_out = true;
+            // ---- A operand row: [hi(r) | lo(r)]; the exact row is parked in shared memory ----------------
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 uint32_t h[4], lw[4];
@@ -188,9 +325,12 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
                 *reinterpret_cast<uint4*>(sAw + sw128_off(wtid, 4 + c)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
             }
             ptx::fence_proxy_async_smem();
-            ptx::tc_fence_before_sync();        // orders this thread's earlier tcgen05.ld before the barrier
+            RQ_TL_DEP(5 + 8 * l, xx);
             ptx::named_bar_sync(1 + wg, 128);
             if (wtid == 0) {
+                // the partner must have read its accumulator out: completion #(2*use - 1) resp. #(2*use) of
+                // the slot's read-out barrier, parity 1 resp. 0
+                if (wait_partner && !ptx::mbar_wait(&mbar_free[slot], is_hi ? 0 : 1)) timed_out = true;
                 ptx::tc_fence_after_sync();
                 const uint32_t a0 = ptx::smem_u32(sAw), b0 = ptx::smem_u32(sB + l * B_TILE_BYTES);
                 // (A k-offset bytes, B k-offset bytes): hi.hi, hi.hi, lo.hi, lo.hi, hi.lo, hi.lo
@@ -205,18 +345,30 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
                 uint64_t od = ptx::make_smem_desc(ptx::smem_u32(sOnes), 128, 256, ptx::kLayoutNone);
                 uint64_t cd = ptx::make_smem_desc(ptx::smem_u32(sCCt + l * CC_TILE_BYTES), 128, 256, ptx::kLayoutNone);
                 ptx::umma_bf16(tmem_acc, od, cd, idesc, 1);
-                ptx::umma_commit(&mbar[wg]);
+                ptx::umma_commit(&mbar_full[wg]);
+                RQ_TL(6 + 8 * l);
             }
-            // scalars needed by the epilogue while the MMAs run
-            const float xx = dot_self<D>(r);
+            // ---- while the MMAs run: this level's input residual goes out (HBM) and to the parking rows ----
+            const int64_t off = ((int64_t)l * p.B + row) * D;
+            const int64_t trow0 = (int64_t)tile * TILE_M;
+            if (SHARE) {
+                park_store_row(r);
+                if (p.res) {
+                    __syncwarp();
+                    park_copy_out(p.res + ((int64_t)l * p.B + trow0) * D, trow0);
+                }
+            } else if (active && p.res) {
+#pragma unroll
+                for (int j = 0; j < D; j += 8) ptx::st_global_v8(p.res + off + j, &r[j]);
+            }
             const float cmax2 = __int_as_float(cmax_bits[l]);
             // |acc - exact| <= 2*(2^-18 + 2*2^-17)|r||c| = 3.8e-5 |r||c| (dropped lo.lo term + the two
             // truncated lo parts) + fp32 accumulation noise; both the winner and a rival may be off,
             // hence 2x, with margin ("error bound")
             const float tol = 1e-4f * sqrtf(xx * cmax2) + 3e-6f * cmax2 + 1e-30f;
-            if (!ptx::mbar_wait(&mbar[wg], phase)) timed_out = true;
-            phase ^= 1;
+            if (!ptx::mbar_wait(&mbar_full[wg], use & 1)) timed_out = true;
             ptx::tc_fence_after_sync();
+            RQ_TL(7 + 8 * l);
 
             if (P.dbg_acc && tile == 0 && l == 0) {
 #pragma unroll 1
@@ -228,96 +380,147 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
                     for (int j = 0; j < 32; ++j) P.dbg_acc[wtid * KC + c * 32 + j] = __uint_as_float(v[j]);
                 }
             }
-            // ---- pass 1: row minimum of the accumulator ------------------------------------------------
-            // Both passes double-buffer the TMEM reads: chunk c+1 is in flight while chunk c is reduced.
-            uint32_t va[32], vb[32];
-            float m0 = INFINITY, m1 = INFINITY;
-            ptx::tmem_ld_32x32b_x32(tmem_row, va);
-            ptx::tmem_ld_wait_for(va);
+            // ---- scan: group minima (A: columns 16g..16g+15) and class minima (B: column mod 16) -----------
+            // The TMEM loads are double-buffered: chunk c+1 is in flight while chunk c is reduced.
+            float accA[16], accB[16];
+            {
+                uint32_t va[32], vb[32];
+                auto reduce_chunk = [&](const uint32_t (&v)[32], int c) {
+                    float f[32];
 #pragma unroll
-            for (int c = 0; c < KC / 32; c += 2) {
-                ptx::tmem_ld_32x32b_x32(tmem_row + (c + 1) * 32, vb);
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
 #pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    m0 = ptx::fmin3(m0, __uint_as_float(va[j]), __uint_as_float(va[j + 1]));
-                    m1 = ptx::fmin3(m1, __uint_as_float(va[j + 2]), __uint_as_float(va[j + 3]));
-                }
-                ptx::tmem_ld_wait_for(vb);
-                // the last prefetch already fetches chunk 0 again for pass 2
-                ptx::tmem_ld_32x32b_x32(tmem_row + ((c + 2) & (KC / 32 - 1)) * 32, va);
+                    for (int h = 0; h < 2; ++h) {
+                        const float* g = f + 16 * h;
+                        float a0 = ptx::fmin3(g[0], g[1], g[2]), a1 = ptx::fmin3(g[3], g[4], g[5]);
+                        float a2 = ptx::fmin3(g[6], g[7], g[8]), a3 = ptx::fmin3(g[9], g[10], g[11]);
+                        float a4 = ptx::fmin3(g[12], g[13], g[14]);
+                        a0 = ptx::fmin3(a0, a1, a2);
+                        a3 = ptx::fmin3(a3, a4, g[15]);
+                        accA[2 * c + h] = fminf(a0, a3);
+                    }
+                    if (c == 0) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                    m0 = ptx::fmin3(m0, __uint_as_float(vb[j]), __uint_as_float(vb[j + 1]));
-                    m1 = ptx::fmin3(m1, __uint_as_float(vb[j + 2]), __uint_as_float(vb[j + 3]));
-                }
-                ptx::tmem_ld_wait_for(va);
-            }
-            const float thr = fminf(m0, m1) + tol;
-            // ---- pass 2: flag every code with acc <= thr ---------------------------------------------
-            uint32_t cand[KC / 32];
+                        for (int i = 0; i < 16; ++i) accB[i] = fminf(f[i], f[16 + i]);
+                    } else {
 #pragma unroll
-            for (int c = 0; c < KC / 32; c += 2) {
-                ptx::tmem_ld_32x32b_x32(tmem_row + (c + 1) * 32, vb);
-                uint32_t msk = 0;
+                        for (int i = 0; i < 16; ++i) accB[i] = ptx::fmin3(accB[i], f[i], f[16 + i]);
+                    }
+                };
+                ptx::tmem_ld_32x32b_x32(tmem_row, va);
+                ptx::tmem_ld_32x32b_x32(tmem_row + 32, vb);
+                ptx::tmem_ld_wait_for2(va, vb);
 #pragma unroll
-                for (int j = 0; j < 32; ++j)      // sign(thr - v) = 1 <=> v > thr ; column j ends at bit 31-j
-                    msk = __funnelshift_l(__float_as_uint(thr - __uint_as_float(va[j])), msk, 1);
-                cand[c] = ~msk;
-                ptx::tmem_ld_wait_for(vb);
-                if (c + 2 < KC / 32) ptx::tmem_ld_32x32b_x32(tmem_row + (c + 2) * 32, va);
-                msk = 0;
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    msk = __funnelshift_l(__float_as_uint(thr - __uint_as_float(vb[j])), msk, 1);
-                cand[c + 1] = ~msk;
-                if (c + 2 < KC / 32) ptx::tmem_ld_wait_for(va);
-            }
-            int n_cand = 0;
-#pragma unroll
-            for (int c = 0; c < KC / 32; ++c) n_cand += __popc(cand[c]);
-            int bi = 0;
-            const float* cbl = p.cb + (int64_t)l * p.K * D;
-            if (n_cand == 1) {
-#pragma unroll
-                for (int c = 0; c < KC / 32; ++c)
-                    if (cand[c]) bi = c * 32 + __clz(cand[c]);
-            } else {
-                // fp32 re-score in ascending index order, strict '<': exactly the SIMT family's arithmetic
-                float best = INFINITY;
-#pragma unroll 1
-                for (int c = 0; c < KC / 32; ++c) {
-                    uint32_t mk = cand[c];
-                    while (mk) {
-                        int pos = __clz(mk);
-                        mk &= ~(0x80000000u >> pos);
-                        int k = c * 32 + pos;
-                        if (k >= p.K) continue;
-                        const float4* c4 = reinterpret_cast<const float4*>(cbl + (int64_t)k * D);
-                        float a = 0.f;
-#pragma unroll
-                        for (int j = 0; j < D / 4; ++j) {
-                            float4 cv = __ldg(c4 + j);
-                            a = fmaf(r[4 * j], cv.x, a); a = fmaf(r[4 * j + 1], cv.y, a);
-                            a = fmaf(r[4 * j + 2], cv.z, a); a = fmaf(r[4 * j + 3], cv.w, a);
-                        }
-                        float d = (xx + sCC[l * KC + k]) - 2.f * a;
-                        if (d < best) { best = d; bi = k; }
+                for (int c = 0; c < KC / 32; c += 2) {
+                    reduce_chunk(va, c);
+                    if (c + 2 < KC / 32) ptx::tmem_ld_32x32b_x32(tmem_row + (c + 2) * 32, va);
+                    reduce_chunk(vb, c + 1);
+                    if (c + 2 < KC / 32) {
+                        ptx::tmem_ld_32x32b_x32(tmem_row + (c + 3) * 32, vb);
+                        ptx::tmem_ld_wait_for2(va, vb);
                     }
                 }
+            }
+            RQ_TL_DEP(8 + 8 * l, accB[0]);
+            float m1a, m2a, m1b, m2b;
+            {
+                float k[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) k[i] = pack_idx(accA[i], i);
+                top2_of16(k, m1a, m2a);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) k[i] = pack_idx(accB[i], i);
+                top2_of16(k, m1b, m2b);
+            }
+            int bi = (int)(((__float_as_uint(m1a) & 15u) << 4) | (__float_as_uint(m1b) & 15u));
+            // packing the index moves a value by < 2^-19 |v|: widen the band by 2^-17 |m1|
+            const float m1 = fminf(m1a, m1b);
+            const float thr = m1 + (tol + 8e-6f * fabsf(m1));
+            const bool ambiguous = (m2a <= thr) || (m2b <= thr);
+            const float* cbl = p.cb + (int64_t)l * p.K * D;
+            // the exact residual row comes back from its parking place
+            if (SHARE) park_load_row(r);
+            if (__any_sync(0xffffffffu, ambiguous)) {
+                // ---- rare: flag every code with acc <= thr, re-score those in fp32 ---------------------------
+                uint32_t cand[KC / 32];
+#pragma unroll 1
+                for (int c = 0; c < KC / 32; ++c) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32b_x32(tmem_row + c * 32, v);
+                    ptx::tmem_ld_wait_for(v);
+                    uint32_t msk = 0;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)      // sign(thr - v) = 1 <=> v > thr ; column j ends at bit 31-j
+                        msk = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[j])), msk, 1);
+                    cand[c] = ~msk;
+                }
+                if (ambiguous) {
+                    // ascending index order, strict '<': exactly the SIMT family's arithmetic
+                    float best = INFINITY;
+#pragma unroll 1
+                    for (int c = 0; c < KC / 32; ++c) {
+                        uint32_t mk = cand[c];
+                        while (mk) {
+                            int pos = __clz(mk);
+                            mk &= ~(0x80000000u >> pos);
+                            int k = c * 32 + pos;
+                            if (k >= p.K) continue;
+                            const float4* c4 = reinterpret_cast<const float4*>(cbl + (int64_t)k * D);
+                            float a = 0.f;
+#pragma unroll
+                            for (int j = 0; j < D / 4; ++j) {
+                                float4 cv = __ldg(c4 + j);
+                                a = fmaf(r[4 * j], cv.x, a); a = fmaf(r[4 * j + 1], cv.y, a);
+                                a = fmaf(r[4 * j + 2], cv.z, a); a = fmaf(r[4 * j + 3], cv.w, a);
+                            }
+                            float d = (xx + sCC[l * KC + k]) - 2.f * a;
+                            if (d < best) { best = d; bi = k; }
+                        }
+                    }
+                }
+            }
+            RQ_TL(9 + 8 * l);
+            // ---- hand the accumulator back: one arrival per warp ------------------------------------------------
+            ptx::tc_fence_before_sync();            // orders this thread's tcgen05.ld before the arrival / next barrier
+            if (SHARE) {
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&mbar_free[slot]);
             }
             if (bi >= p.K) bi = p.K - 1;        // unreachable unless inputs are NaN; keeps the gather in range
 
             // ---- gather, estimator, loss, outputs, residual update ---------------------------------------
             float e[D], o[D];
+            if (SHARE) {
+                // cooperative gather: 8 lanes fetch the 8 chunks of one row's codeword (4 rows per instruction)
+                float4 g[8];
 #pragma unroll
-            for (int j = 0; j < D; j += 8) ptx::ld_global_v8(cbl + (int64_t)bi * D + j, &e[j]);
-            loss_acc += level_epilogue<D>(p.mode, p.beta, r, e, o);
-            if (active) {
-                const int64_t off = ((int64_t)l * p.B + row) * D;
-                if (p.res) {
-#pragma unroll
-                    for (int j = 0; j < D; j += 8) ptx::st_global_v8(p.res + off + j, &r[j]);
+                for (int i = 0; i < 8; ++i) {
+                    const int k = __shfl_sync(0xffffffffu, bi, 4 * i + (lane >> 3));
+                    g[i] = __ldg(reinterpret_cast<const float4*>(cbl + (int64_t)k * D) + (lane & 7));
                 }
+                __syncwarp();                       // everybody has re-read its parked residual
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    *reinterpret_cast<float4*>(sPw + sw128_off(wrow0 + 4 * i + (lane >> 3), lane & 7)) = g[i];
+                __syncwarp();
+                park_load_row(e);
+            } else {
+#pragma unroll
+                for (int j = 0; j < D; j += 8) ptx::ld_global_v8(cbl + (int64_t)bi * D + j, &e[j]);
+            }
+            RQ_TL_DEP(10 + 8 * l, e[31]);
+            loss_acc += level_epilogue<D>(p.mode, p.beta, r, e, xx, o);
+            RQ_TL_DEP(11 + 8 * l, o[31]);
+            if (SHARE) {
+                if (p.emb) {
+                    __syncwarp();                   // everybody has read its codeword row
+                    park_store_row(o);
+                    __syncwarp();
+                    park_copy_out(p.emb + ((int64_t)l * p.B + trow0) * D, trow0);
+                    __syncwarp();                   // copied out before the next level parks its residual
+                }
+                if (active) p.ids[(int64_t)l * p.B + row] = bi;
+            } else if (active) {
                 if (p.emb) {
 #pragma unroll
                     for (int j = 0; j < D; j += 8) ptx::st_global_v8(p.emb + off + j, &o[j]);
@@ -325,15 +528,41 @@ __global__ void __launch_bounds__(tc::THREADS, 1) rq_fwd_tc_kernel(TcParams P) {
                 p.ids[(int64_t)l * p.B + row] = bi;
             }
 #pragma unroll
-            for (int j = 0; j < D; ++j) r[j] = r[j] - o[j];
+            for (int j = 0; j < D; ++j) r[j] = r[j] - o[j];                     // rqvae.py:129
+            xx = dot_self<D>(r);
+            RQ_TL_DEP(12 + 8 * l, xx);
         }
         if (active && p.loss) p.loss[row] = loss_acc;
+        // next tile of this warpgroup
+        if (it + 1 < n_mine) {
+            const int64_t ntrow0 = ((int64_t)blockIdx.x + (int64_t)gridDim.x * (wg + NWG * (it + 1))) * TILE_M;
+            if (SHARE) {
+                __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int rr = wrow0 + 4 * i + (lane >> 3);
+                    const float4 t = (ntrow0 + rr < p.B)
+                                         ? ptx::ld_global_stream_v4(p.x + (ntrow0 + rr) * D + (lane & 7) * 4)
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+                    *reinterpret_cast<float4*>(sPw + sw128_off(rr, lane & 7)) = t;
+                }
+                __syncwarp();
+                park_load_row(r);
+                __syncwarp();
+            } else if (ntrow0 + wtid < p.B) {
+#pragma unroll
+                for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + (ntrow0 + wtid) * D + j, &r[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < D; ++j) r[j] = 0.f;
+            }
+        }
     }
 
     if (timed_out && P.err) atomicExch(P.err, 1);
     ptx::tc_fence_before_sync();
     __syncthreads();
-    if (warp == 0) ptx::tmem_dealloc(tmem_base, 512);
+    if (warp == 1) ptx::tmem_dealloc(tmem_base, 512);
 }
 
 bool tc_supported(int D, int K, int L, int mode, int distance) {
@@ -344,6 +573,22 @@ bool tc_supported(int D, int K, int L, int mode, int distance) {
 
 static int* d_err = nullptr;
 static float* g_dbg_acc = nullptr;
+static long long* g_dbg_tl = nullptr;
+constexpr int kMaxSmem = 227 * 1024;
+
+template <int NWG>
+static int launch_tc(const TcParams& P, cudaStream_t st) {
+    const tc::SmemLayout S = tc::smem_layout(P.f.L, NWG);
+    static bool attr_set = false;
+    if (!attr_set) {
+        RQ_CUDA(cudaFuncSetAttribute(rq_fwd_tc_kernel<NWG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+        attr_set = true;
+    }
+    int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
+    rq_fwd_tc_kernel<NWG><<<grid, 128 * NWG, S.total + 1024, st>>>(P);
+    RQ_LAUNCHED();
+    return 0;
+}
 
 int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st) {
     (void)D;
@@ -356,18 +601,11 @@ int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st) {
     P.f = p;
     P.err = d_err;
     P.dbg_acc = g_dbg_acc;
+    P.dbg_tl = g_dbg_tl;
     P.n_tiles = (int)((p.B + tc::TILE_M - 1) / tc::TILE_M);
-    const tc::SmemLayout S = tc::smem_layout(p.L);
-    static bool attr_set = false;
-    if (!attr_set) {
-        RQ_CUDA(cudaFuncSetAttribute(rq_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
-    int grid = (P.n_tiles + 1) / 2;
-    if (grid > sm_count()) grid = sm_count();
-    rq_fwd_tc_kernel<<<grid, tc::THREADS, S.total + 1024, st>>>(P);
-    RQ_LAUNCHED();
-    return 0;
+    // four warpgroups when the operand tiles of L levels + four A tiles fit in shared memory (L <= 3)
+    const bool four = tc::smem_layout(p.L, 4).total + 1024 <= kMaxSmem && !getenv("RQ_TC_TWO_WARPGROUPS");
+    return four ? launch_tc<4>(P, st) : launch_tc<2>(P, st);
 }
 
 }  // namespace rq
@@ -382,7 +620,7 @@ extern "C" int rq_debug_tc_set_accumulator_dump(float* device_buf_128x256) {
     rq::g_dbg_acc = device_buf_128x256;
     return 0;
 }
-
-namespace rq {
-
-}  // namespace rq
+extern "C" int rq_debug_tc_set_timeline(long long* device_buf_32x64) {
+    rq::g_dbg_tl = device_buf_32x64;
+    return 0;
+}

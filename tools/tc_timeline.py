@@ -1,0 +1,30 @@
+"""Prints the clock64 phase timeline of CTA 0 of the tcgen05 forward kernel (rq_debug_tc_set_timeline)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import bench
+from rq_vae_recommender_b200 import functional as RF, _lib
+
+dev = torch.device("cuda:0")
+xs, cbs, g_emb, g_loss = bench.make_inputs(torch, dev, 2, seed=1)
+xs = [t.to(dev) for t in xs]; cbs = cbs.to(dev)
+mode = RF.MODE_ROTATION_TRICK
+for i in range(3):
+    RF.quantize_forward(xs[i % 2], cbs, mode, 0.25, 0.2)
+buf = torch.zeros(32, 64, dtype=torch.int64, device=dev)
+_lib.lib().rq_debug_tc_set_timeline(buf.data_ptr())
+RF.quantize_forward(xs[1], cbs, mode, 0.25, 0.2)
+torch.cuda.synchronize()
+_lib.lib().rq_debug_tc_set_timeline(None)
+t = buf.cpu()
+t0 = int(t[t > 0].min())
+names = ["start", "init", "tma", "conv", "prolog"] + [f"L{l}:{n}" for l in range(3) for n in ("Awr", "mmaiss", "accrdy", "scan", "slow", "gather", "epi", "done")]
+print("prologue detail (tma_issued, x_issued, tmem_alloc, ones):")
+for w in range(32):
+    if int(t[w, 0]):
+        print(w, [int(v) - t0 if int(v) else -1 for v in t[w, 45:49]])
+print("warp " + " ".join(f"{n:>7s}" for n in names))
+for w in range(32):
+    if int(t[w, 0]) == 0:
+        continue
+    print(f"{w:4d} " + " ".join(f"{(int(v) - t0) if int(v) else -1:7d}" for v in t[w, :len(names)]))
