@@ -214,18 +214,12 @@ def run_engine(args):
     cbs = cbs_h.to(dev)
     mode = RF.MODE_ROTATION_TRICK
 
-    def step(i, ev=None):
+    def step(i):
         s = i % N_SLOTS
-        if ev is not None:
-            ev[0].record()
         emb, res, ids, loss = RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP)
-        if ev is not None:
-            ev[1].record()
         g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP)
         if world > 1:
             dist.all_reduce(g_cb)            # codebook-gradient all-reduce (98,304 B), the path's one exchange
-        if ev is not None:
-            ev[2].record()
         return loss, g_x, g_cb
 
     def fence():
@@ -233,24 +227,76 @@ def run_engine(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # The step is 2-3 launches of ~10-30 us each: launched eagerly from Python the host is the bottleneck, so
+    # every ring slot's step is captured once into a CUDA graph (the library is capture-safe: caller's stream,
+    # no host sync, torch-allocator outputs) and the timed loop replays graph[i % N_SLOTS].
+    def capture(fn):
+        graphs, keep, per_graph = [], [], 0
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for s in range(N_SLOTS):
+                fn(s)                                   # warm the allocator / lazy inits outside capture
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        for s in range(N_SLOTS):
+            g = torch.cuda.CUDAGraph()
+            n0 = R.launch_count()
+            with torch.cuda.graph(g):
+                keep.append(fn(s))
+            per_graph = R.launch_count() - n0
+            graphs.append(g)
+        return graphs, keep, per_graph
+
+    use_graphs = os.environ.get("RQ_BENCH_EAGER") is None
+    try:
+        if not use_graphs:
+            raise RuntimeError("eager requested")
+        step_graphs, _keep1, launches_per_step = capture(step)
+        fwd_graphs, _keep2, _ = capture(lambda s: RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP))
+        _fwd_out = [RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP) for s in range(N_SLOTS)]
+        bwd_graphs, _keep3, _ = capture(lambda s: RF.quantize_backward(g_embs[s], None, g_loss, _fwd_out[s][1],
+                                                                       _fwd_out[s][2], cbs, mode, BETA, TEMP))
+        run_step = lambda i: step_graphs[i % N_SLOTS].replay()
+        run_fwd = lambda i: fwd_graphs[i % N_SLOTS].replay()
+        run_bwd = lambda i: bwd_graphs[i % N_SLOTS].replay()
+        launch_mode = "cuda-graph replay (one graph per ring slot)"
+    except Exception as e:                              # pragma: no cover - capture unsupported in this setup
+        if use_graphs:
+            print(f"bench.py: CUDA-graph capture failed ({e}); timing eager launches", file=sys.stderr)
+        use_graphs = False
+        _fwd_out = [RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP) for s in range(N_SLOTS)]
+        run_step = step
+        run_fwd = lambda i: RF.quantize_forward(xs[i % N_SLOTS], cbs, mode, BETA, TEMP)
+        run_bwd = lambda i: RF.quantize_backward(g_embs[i % N_SLOTS], None, g_loss, _fwd_out[i % N_SLOTS][1],
+                                                 _fwd_out[i % N_SLOTS][2], cbs, mode, BETA, TEMP)
+        launches_per_step = None
+        launch_mode = "eager launches"
+
+    def timed(fn, n):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(n):
+            fn(args.warmup + i)
+        b.record()
+        return a, b
+
     for i in range(args.warmup):
-        step(i)
+        run_step(i)
     fence()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
     l0 = R.launch_count()
     with ClockSampler(local) as clk:
         fence()
-        t_start = torch.cuda.Event(enable_timing=True)
-        t_end = torch.cuda.Event(enable_timing=True)
-        t_start.record()
-        for i in range(args.steps):
-            step(args.warmup + i, evs[i])
-        t_end.record()
+        t_start, t_end = timed(run_step, args.steps)
         fence()
-    launches = R.launch_count() - l0
+        # the dominant kernels on their own, same ring, same clocks window (roofline legs)
+        f0, f1 = timed(run_fwd, args.steps)
+        b0, b1 = timed(run_bwd, args.steps)
+        fence()
+    launches = (launches_per_step * args.steps) if use_graphs else (R.launch_count() - l0)
     ms_total = t_start.elapsed_time(t_end)
-    fwd_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
-    bwd_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
+    fwd_ms = f0.elapsed_time(f1) / args.steps
+    bwd_ms = b0.elapsed_time(b1) / args.steps
 
     # ---- e2e: public module API, host buffers, copies inside the timed region ------------------
     model = R.RqVae(input_dim=D, embed_dim=D, hidden_dims=[], codebook_size=K, codebook_kmeans_init=False,
@@ -287,16 +333,22 @@ def run_engine(args):
     e2e_s = time.perf_counter() - t0
 
     # ---- side numbers (outside the timed region): ids-only tokenisation launch -------------------
-    for _ in range(3):
-        RF.quantize_forward(xs[0], cbs, RF.MODE_EVAL, want_embeddings=False, want_residuals=False, want_loss=False)
+    ids_fn = lambda s: RF.quantize_forward(xs[s], cbs, RF.MODE_EVAL, want_embeddings=False,  # noqa: E731
+                                           want_residuals=False, want_loss=False)
+    if use_graphs:
+        ids_graphs, _keep4, _ = capture(ids_fn)
+        run_ids = lambda i: ids_graphs[i % N_SLOTS].replay()                              # noqa: E731
+    else:
+        run_ids = lambda i: ids_fn(i % N_SLOTS)                                           # noqa: E731
+    for i in range(3):
+        run_ids(i)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    for i in range(10):
-        RF.quantize_forward(xs[i % N_SLOTS], cbs, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
-                            want_loss=False)
+    for i in range(20):
+        run_ids(i)
     b.record()
     torch.cuda.synchronize()
-    ids_only_ms = a.elapsed_time(b) / 10
+    ids_only_ms = a.elapsed_time(b) / 20
 
     stats = torch.tensor([ms_total, e2e_s * 1e3, float(launches)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -328,7 +380,7 @@ def run_engine(args):
             "extra": {"fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "ids_only_ms": ids_only_ms,
                       "ids_only_items_per_s": B_PER_GPU / (ids_only_ms * 1e-3),
                       "fwd_items_per_s": B_PER_GPU / (fwd_ms * 1e-3),
-                      "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1))},
+                      "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode},
         }
         if not args.no_cpu_baseline and world == 1:
             ips, ms, cores = cpu_reference_run(args.cpu_sample_items, 3, 1)

@@ -79,6 +79,7 @@ struct TcParams {
     int* err;        // device flag: set when an mbarrier / lock wait timed out
     int n_tiles;
     float* dbg_acc;  // optional [128][256] dump of tile 0 / level 0's accumulator (tests only)
+    int dbg_flags;      // experiments only (RQ_TC_DBG_FLAGS): 1 = skip first x load, 2 = skip codebook TMA
     long long* dbg_tl;  // optional [32 warps][64 marks] clock64 timeline of CTA 0 (profiling only)
 };
 #define RQ_TL(mark)                                                                           \
@@ -139,6 +140,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     uint64_t* mbar_full = reinterpret_cast<uint64_t*>(smem + S.misc);        // [4] accumulator ready (per warpgroup)
     uint64_t* mbar_free = reinterpret_cast<uint64_t*>(smem + S.misc + 32);   // [2] accumulator read out (per slot)
     uint64_t* mbar_load = reinterpret_cast<uint64_t*>(smem + S.misc + 48);   // [1] codebook bulk copy landed
+    uint64_t* mbar_x = reinterpret_cast<uint64_t*>(smem + S.misc + 96);     // [4] x tile landed (per warpgroup)
     uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(smem + S.misc + 64);
     int* cmax_bits = reinterpret_cast<int*>(smem + S.misc + 80);             // [MAX_L] max ||c||^2 per level
 
@@ -154,11 +156,13 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
         ptx::mbar_init(&mbar_free[0], 4);
         ptx::mbar_init(&mbar_free[1], 4);
         ptx::mbar_init(mbar_load, 1);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) ptx::mbar_init(&mbar_x[i], 1);
         ptx::fence_mbar_init();
         const uint32_t level_bytes = (uint32_t)p.K * D * 4;
-        ptx::mbar_arrive_expect_tx(mbar_load, level_bytes * p.L);
+        ptx::mbar_arrive_expect_tx(mbar_load, (P.dbg_flags & 2) ? 0u : level_bytes * p.L);
         for (int l = 0; l < p.L; ++l)
-            ptx::bulk_g2s(sB + l * B_TILE_BYTES, p.cb + (int64_t)l * p.K * D, level_bytes, mbar_load);
+            if (!(P.dbg_flags & 2)) ptx::bulk_g2s(sB + l * B_TILE_BYTES, p.cb + (int64_t)l * p.K * D, level_bytes, mbar_load);
     }
     RQ_TL(45);
     // ---- first tile's rows: HBM loads in flight during the whole prologue ------------------------------
@@ -168,27 +172,23 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     const int n_mine = (my_tiles > wg) ? (my_tiles - 1 - wg) / NWG + 1 : 0;
     const int n_partner = SHARE ? ((my_tiles > (wg ^ 2)) ? (my_tiles - 1 - (wg ^ 2)) / NWG + 1 : 0) : 0;
     float r[D];
-    float4 xin[8];                          // SHARE: coalesced image of this warp's 32 rows (lane = 16-byte chunk)
     const int wrow0 = (warp & 3) * 32;      // first tile row of this warp
-    {
-        const int64_t trow0 = ((int64_t)blockIdx.x + (int64_t)gridDim.x * wg) * TILE_M;
-        if (SHARE) {
+    uint8_t* sPw = sPark + wg * A_TILE_BYTES;
+    // rows of a tile are contiguous in x ([B, D] row-major): one TMA bulk copy per tile into the warpgroup's
+    // parking tile (linear layout), issued by one thread, no load instructions in anybody's way
+    auto issue_x_tile = [&](int64_t trow0) {
+        const int64_t rows = (p.B - trow0 < TILE_M) ? (p.B - trow0) : TILE_M;
+        ptx::mbar_arrive_expect_tx(&mbar_x[wg], (uint32_t)rows * D * 4);
+        ptx::bulk_g2s(sPw, p.x + trow0 * D, (uint32_t)rows * D * 4, &mbar_x[wg]);
+    };
+    if (!SHARE) {
+        const int64_t row = ((int64_t)blockIdx.x + (int64_t)gridDim.x * wg) * TILE_M + wtid;
+        if (n_mine > 0 && row < p.B) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int rr = wrow0 + 4 * i + (lane >> 3);
-                xin[i] = (n_mine > 0 && trow0 + rr < p.B)
-                             ? ptx::ld_global_stream_v4(p.x + (trow0 + rr) * D + (lane & 7) * 4)
-                             : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
+            for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + row * D + j, &r[j]);
         } else {
-            const int64_t row = trow0 + wtid;
-            if (n_mine > 0 && row < p.B) {
 #pragma unroll
-                for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + row * D + j, &r[j]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < D; ++j) r[j] = 0.f;
-            }
+            for (int j = 0; j < D; ++j) r[j] = 0.f;
         }
     }
     RQ_TL(46);
@@ -205,6 +205,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     RQ_TL(48);
     __syncthreads();                                   // barrier inits + cmax zeros visible
     RQ_TL(1);
+    if (SHARE && wtid == 0 && n_mine > 0) issue_x_tile(((int64_t)blockIdx.x + (int64_t)gridDim.x * wg) * TILE_M);
     if (!ptx::mbar_wait(mbar_load, 0)) {
         if (P.err) atomicExch(P.err, 1);
     }
@@ -212,49 +213,73 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     // ---- in-place conversion: work item = (level, code, 8-element chunk); the four lanes of a code read
     // its 128-byte fp32 row and rewrite the same 128 bytes as [-2hi | -2lo] bf16 in the swizzled order ------
     {
-        const int n_items = p.L * KC * 4;                          // multiple of THREADS
-        for (int i = tid; i < n_items; i += THREADS) {
-            const int l = i >> 10, k = (i >> 2) & 255, q = i & 3;
-            uint8_t* tileB = sB + l * B_TILE_BYTES;
-            float cv[8];
-            if (k < p.K) {
-                const float4 v0 = *reinterpret_cast<const float4*>(tileB + k * 128 + q * 32);
-                const float4 v1 = *reinterpret_cast<const float4*>(tileB + k * 128 + q * 32 + 16);
-                cv[0] = v0.x; cv[1] = v0.y; cv[2] = v0.z; cv[3] = v0.w;
-                cv[4] = v1.x; cv[5] = v1.y; cv[6] = v1.z; cv[7] = v1.w;
-            } else {
+        const int n_items = p.L * KC * 4;                          // multiple of 2 * THREADS
+        constexpr int U = 2;                                       // items in flight per thread
+        for (int i0 = tid; i0 < n_items; i0 += U * THREADS) {
+            float cv[U][8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) cv[j] = 0.f;
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * THREADS;
+                const int l = i >> 10, k = (i >> 2) & 255, q = i & 3;
+                const uint8_t* src = sB + l * B_TILE_BYTES + k * 128 + q * 32;
+                if (k < p.K) {
+                    const float4 v0 = *reinterpret_cast<const float4*>(src);
+                    const float4 v1 = *reinterpret_cast<const float4*>(src + 16);
+                    cv[u][0] = v0.x; cv[u][1] = v0.y; cv[u][2] = v0.z; cv[u][3] = v0.w;
+                    cv[u][4] = v1.x; cv[u][5] = v1.y; cv[u][6] = v1.z; cv[u][7] = v1.w;
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) cv[u][j] = 0.f;
+                }
             }
-            uint32_t h[4], lw[4];
-            float part = 0.f;
+            uint32_t h[U][4], lw[U][4];
+            float part[U];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float a = cv[2 * j], b = cv[2 * j + 1];
-                part = fmaf(a, a, part);
-                part = fmaf(b, b, part);
-                ptx::split_pair(-2.f * a, -2.f * b, h[j], lw[j]);
+            for (int u = 0; u < U; ++u) {
+                part[u] = 0.f;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float a = cv[u][2 * j], b = cv[u][2 * j + 1];
+                    part[u] = fmaf(a, a, part[u]);
+                    part[u] = fmaf(b, b, part[u]);
+                    ptx::split_pair(-2.f * a, -2.f * b, h[u][j], lw[u][j]);
+                }
             }
             // ||c||^2 in the canonical order shared with the SIMT family (code_sqnorm in rq_rowmath.cuh):
             // 8-wide sequential partials, then (p0+p1)+(p2+p3)
-            part += __shfl_xor_sync(0xffffffffu, part, 1);
-            part += __shfl_xor_sync(0xffffffffu, part, 2);          // also orders the quad's reads before its writes
-            __syncwarp();
-            *reinterpret_cast<uint4*>(tileB + sw128_off(k, q)) = make_uint4(h[0], h[1], h[2], h[3]);
-            *reinterpret_cast<uint4*>(tileB + sw128_off(k, 4 + q)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-            if (q == 0) {
-                float cc = (k < p.K) ? part : 1e30f;              // padding codes can never be the minimum
-                sCC[l * KC + k] = cc;
-                float hh = ptx::bf16_round(cc), mm = ptx::bf16_round(cc - hh), ll = ptx::bf16_round((cc - hh) - mm);
-                *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 0)) =
-                    make_uint4(ptx::pack_bf16x2(hh, mm), ptx::pack_bf16x2(ll, 0.f), 0, 0);
-                *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 1)) = make_uint4(0, 0, 0, 0);
-                if (k < p.K) atomicMax(&cmax_bits[l], __float_as_int(cc));
+#pragma unroll
+            for (int u = 0; u < U; ++u) part[u] += __shfl_xor_sync(0xffffffffu, part[u], 1);
+#pragma unroll
+            for (int u = 0; u < U; ++u) part[u] += __shfl_xor_sync(0xffffffffu, part[u], 2);
+            __syncwarp();                                           // the quad's reads precede its writes
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * THREADS;
+                const int l = i >> 10, k = (i >> 2) & 255, q = i & 3;
+                uint8_t* tileB = sB + l * B_TILE_BYTES;
+                *reinterpret_cast<uint4*>(tileB + sw128_off(k, q)) = make_uint4(h[u][0], h[u][1], h[u][2], h[u][3]);
+                *reinterpret_cast<uint4*>(tileB + sw128_off(k, 4 + q)) = make_uint4(lw[u][0], lw[u][1], lw[u][2], lw[u][3]);
+                if (q == 0) {
+                    float cc = (k < p.K) ? part[u] : 1e30f;        // padding codes can never be the minimum
+                    sCC[l * KC + k] = cc;
+                    float hh = ptx::bf16_round(cc), mm = ptx::bf16_round(cc - hh), ll = ptx::bf16_round((cc - hh) - mm);
+                    *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 0)) =
+                        make_uint4(ptx::pack_bf16x2(hh, mm), ptx::pack_bf16x2(ll, 0.f), 0, 0);
+                    *reinterpret_cast<uint4*>(sCCt + l * CC_TILE_BYTES + nosw_off(k, 1)) = make_uint4(0, 0, 0, 0);
+                }
             }
         }
     }
     RQ_TL(3);
     ptx::fence_proxy_async_smem();
+    __syncthreads();
+    if (warp < p.L) {                                  // max ||c||^2 per level (the scan's error bound)
+        float m = 0.f;
+        for (int k = lane; k < p.K; k += 32) m = fmaxf(m, sCC[warp * KC + k]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) cmax_bits[warp] = __float_as_int(m);
+    }
     ptx::tc_fence_before_sync();
     __syncthreads();
     ptx::tc_fence_after_sync();
@@ -263,8 +288,8 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     const uint32_t tmem_acc = tmem_base + (uint32_t)(slot * KC);                     // column offset
     const uint32_t tmem_row = tmem_acc + ((uint32_t)((warp & 3) * 32) << 16);        // this warp's lanes
     uint8_t* sAw = sA + slot * A_TILE_BYTES;
-    uint8_t* sPw = sPark + wg * A_TILE_BYTES;
     const uint32_t idesc = ptx::make_idesc_bf16_f32(TILE_M, KC);
+    bool timed_out = false;
     // Global <-> register traffic of a warp's 32 rows goes through its 4 KB of the parking tile so that
     // every global instruction covers 4 whole rows (4 lines) instead of one sector of 32 different lines.
     auto park_store_row = [&](const float (&v)[D]) {              // my row -> parking tile (swizzled, conflict-free)
@@ -280,32 +305,59 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
             v[4 * c] = t.x; v[4 * c + 1] = t.y; v[4 * c + 2] = t.z; v[4 * c + 3] = t.w;
         }
     };
+    // this lane's (row, chunk) in the 4-rows-per-instruction coalesced pattern: row = wrow0 + 4 i + lane/8
+    const uint32_t co_row = (uint32_t)(wrow0 + (lane >> 3)), co_sw = sw128_off((int)co_row, lane & 7);
+    auto co_off = [&](int i) -> uint32_t { return (co_sw + 512u * i) ^ ((i & 1) ? 64u : 0u); };
     auto park_copy_out = [&](float* dst_tile, int64_t trow0) {     // parking tile -> 4 KB of global, coalesced
+        float* dst = dst_tile + (int64_t)co_row * D + (lane & 7) * 4;
+        // rows 4 i further down keep (row & 7) parity only for even i: 4 i rows = 512 i bytes, the swizzle term
+        // flips bit 2 of the chunk index for odd i
+        if (trow0 + TILE_M <= p.B) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int rr = wrow0 + 4 * i + (lane >> 3);
-            const float4 t = *reinterpret_cast<const float4*>(sPw + sw128_off(rr, lane & 7));
-            if (trow0 + rr < p.B) ptx::st_global_v4(dst_tile + (int64_t)rr * D + (lane & 7) * 4, t);
+            for (int i = 0; i < 8; ++i) {
+                const float4 t = *reinterpret_cast<const float4*>(sPw + co_off(i));
+                ptx::st_global_v4(dst + i * 4 * D, t);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 t = *reinterpret_cast<const float4*>(sPw + co_off(i));
+                if (trow0 + co_row + 4 * i < p.B) ptx::st_global_v4(dst + i * 4 * D, t);
+            }
         }
     };
-    if (SHARE) {
+    auto take_x_tile = [&](int it, bool active) {                  // linear parking tile -> my row
+        if (!ptx::mbar_wait(&mbar_x[wg], it & 1)) timed_out = true;
+        RQ_TL(49);
+        // linear -> swizzled in place (conflict-free both ways: 8 lanes cover one 128-byte row), then my row
+        float4 t[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-            *reinterpret_cast<float4*>(sPw + sw128_off(wrow0 + 4 * i + (lane >> 3), lane & 7)) = xin[i];
+            t[i] = *reinterpret_cast<const float4*>(sPw + (wrow0 + 4 * i + (lane >> 3)) * 128 + (lane & 7) * 16);
         __syncwarp();
-        park_load_row(r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(sPw + co_off(i)) = t[i];
         __syncwarp();
-    }
+        if (active) {
+            park_load_row(r);
+        } else {
+#pragma unroll
+            for (int j = 0; j < D; ++j) r[j] = 0.f;
+        }
+        __syncwarp();
+    };
     const int n_partner_uses = n_partner * p.L;
     const bool is_hi = SHARE && (wg >= 2);
-    bool timed_out = false;
     int use = 0;                                   // this warpgroup's running (tile, level) count
 
     for (int it = 0; it < n_mine; ++it) {
         const int tile = (int)blockIdx.x + (int)gridDim.x * (wg + NWG * it);
         const int64_t row = (int64_t)tile * TILE_M + wtid;
         const bool active = row < p.B;
+        if (SHARE) take_x_tile(it, active);
         float xx = dot_self<D>(r);
+        RQ_TL_DEP(50, xx);
         float loss_acc = 0.f;
 
         for (int l = 0; l < p.L; ++l, ++use) {
@@ -422,6 +474,12 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
                 }
             }
             RQ_TL_DEP(8 + 8 * l, accB[0]);
+            // ---- the accumulator is read out: hand it back (one arrival per warp) --------------------------------
+            ptx::tc_fence_before_sync();            // orders this thread's tcgen05.ld before the arrival / next barrier
+            if (SHARE) {
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive(&mbar_free[slot]);
+            }
             float m1a, m2a, m1b, m2b;
             {
                 float k[16];
@@ -441,37 +499,33 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
             // the exact residual row comes back from its parking place
             if (SHARE) park_load_row(r);
             if (__any_sync(0xffffffffu, ambiguous)) {
-                // ---- rare: flag every code with acc <= thr, re-score those in fp32 ---------------------------
-                uint32_t cand[KC / 32];
-#pragma unroll 1
-                for (int c = 0; c < KC / 32; ++c) {
-                    uint32_t v[32];
-                    ptx::tmem_ld_32x32b_x32(tmem_row + c * 32, v);
-                    ptx::tmem_ld_wait_for(v);
-                    uint32_t msk = 0;
+                // ---- rare: every code within the band lies in a group with accA <= thr AND a class with
+                // accB <= thr; re-score those (group, class) pairs in fp32, ascending index, strict '<':
+                // exactly the SIMT family's arithmetic.  Extra pairs are harmless (their exact distance loses).
+                uint32_t gm = 0, cm = 0;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)      // sign(thr - v) = 1 <=> v > thr ; column j ends at bit 31-j
-                        msk = __funnelshift_l(__float_as_uint(thr - __uint_as_float(v[j])), msk, 1);
-                    cand[c] = ~msk;
+                for (int i = 0; i < 16; ++i) {
+                    gm |= (accA[i] <= thr) ? (1u << i) : 0u;
+                    cm |= (accB[i] <= thr) ? (1u << i) : 0u;
                 }
                 if (ambiguous) {
-                    // ascending index order, strict '<': exactly the SIMT family's arithmetic
                     float best = INFINITY;
 #pragma unroll 1
-                    for (int c = 0; c < KC / 32; ++c) {
-                        uint32_t mk = cand[c];
-                        while (mk) {
-                            int pos = __clz(mk);
-                            mk &= ~(0x80000000u >> pos);
-                            int k = c * 32 + pos;
+                    for (uint32_t g = gm; g; g &= g - 1) {
+                        const int gi = __ffs(g) - 1;
+#pragma unroll 1
+                        for (uint32_t c = cm; c; c &= c - 1) {
+                            const int k = gi * 16 + (__ffs(c) - 1);
                             if (k >= p.K) continue;
                             const float4* c4 = reinterpret_cast<const float4*>(cbl + (int64_t)k * D);
+                            float4 cv[D / 4];
+#pragma unroll
+                            for (int j = 0; j < D / 4; ++j) cv[j] = __ldg(c4 + j);
                             float a = 0.f;
 #pragma unroll
                             for (int j = 0; j < D / 4; ++j) {
-                                float4 cv = __ldg(c4 + j);
-                                a = fmaf(r[4 * j], cv.x, a); a = fmaf(r[4 * j + 1], cv.y, a);
-                                a = fmaf(r[4 * j + 2], cv.z, a); a = fmaf(r[4 * j + 3], cv.w, a);
+                                a = fmaf(r[4 * j], cv[j].x, a); a = fmaf(r[4 * j + 1], cv[j].y, a);
+                                a = fmaf(r[4 * j + 2], cv[j].z, a); a = fmaf(r[4 * j + 3], cv[j].w, a);
                             }
                             float d = (xx + sCC[l * KC + k]) - 2.f * a;
                             if (d < best) { best = d; bi = k; }
@@ -480,12 +534,6 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
                 }
             }
             RQ_TL(9 + 8 * l);
-            // ---- hand the accumulator back: one arrival per warp ------------------------------------------------
-            ptx::tc_fence_before_sync();            // orders this thread's tcgen05.ld before the arrival / next barrier
-            if (SHARE) {
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&mbar_free[slot]);
-            }
             if (bi >= p.K) bi = p.K - 1;        // unreachable unless inputs are NaN; keeps the gather in range
 
             // ---- gather, estimator, loss, outputs, residual update ---------------------------------------
@@ -501,7 +549,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
                 __syncwarp();                       // everybody has re-read its parked residual
 #pragma unroll
                 for (int i = 0; i < 8; ++i)
-                    *reinterpret_cast<float4*>(sPw + sw128_off(wrow0 + 4 * i + (lane >> 3), lane & 7)) = g[i];
+                    *reinterpret_cast<float4*>(sPw + co_off(i)) = g[i];
                 __syncwarp();
                 park_load_row(e);
             } else {
@@ -537,18 +585,9 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
         if (it + 1 < n_mine) {
             const int64_t ntrow0 = ((int64_t)blockIdx.x + (int64_t)gridDim.x * (wg + NWG * (it + 1))) * TILE_M;
             if (SHARE) {
-                __syncwarp();
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int rr = wrow0 + 4 * i + (lane >> 3);
-                    const float4 t = (ntrow0 + rr < p.B)
-                                         ? ptx::ld_global_stream_v4(p.x + (ntrow0 + rr) * D + (lane & 7) * 4)
-                                         : make_float4(0.f, 0.f, 0.f, 0.f);
-                    *reinterpret_cast<float4*>(sPw + sw128_off(rr, lane & 7)) = t;
-                }
-                __syncwarp();
-                park_load_row(r);
-                __syncwarp();
+                ptx::fence_proxy_async_smem();          // our generic accesses to the parking tile, then the TMA write
+                ptx::named_bar_sync(1 + wg, 128);
+                if (wtid == 0) issue_x_tile(ntrow0);
             } else if (ntrow0 + wtid < p.B) {
 #pragma unroll
                 for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + (ntrow0 + wtid) * D + j, &r[j]);
@@ -602,6 +641,7 @@ int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st) {
     P.err = d_err;
     P.dbg_acc = g_dbg_acc;
     P.dbg_tl = g_dbg_tl;
+    P.dbg_flags = getenv("RQ_TC_DBG_FLAGS") ? atoi(getenv("RQ_TC_DBG_FLAGS")) : 0;
     P.n_tiles = (int)((p.B + tc::TILE_M - 1) / tc::TILE_M);
     // four warpgroups when the operand tiles of L levels + four A tiles fit in shared memory (L <= 3)
     const bool four = tc::smem_layout(p.L, 4).total + 1024 <= kMaxSmem && !getenv("RQ_TC_TWO_WARPGROUPS");

@@ -13,16 +13,20 @@ for i in range(3):
     RF.quantize_forward(xs[i % 2], cbs, mode, 0.25, 0.2)
 buf = torch.zeros(32, 64, dtype=torch.int64, device=dev)
 _lib.lib().rq_debug_tc_set_timeline(buf.data_ptr())
+if os.environ.get("TL_WARM_X"):
+    s = xs[1].sum().item()          # x tile source now L2-resident, GPU idle before the launch
+if os.environ.get("TL_SYNC"):
+    torch.cuda.synchronize()
 RF.quantize_forward(xs[1], cbs, mode, 0.25, 0.2)
 torch.cuda.synchronize()
 _lib.lib().rq_debug_tc_set_timeline(None)
 t = buf.cpu()
 t0 = int(t[t > 0].min())
 names = ["start", "init", "tma", "conv", "prolog"] + [f"L{l}:{n}" for l in range(3) for n in ("Awr", "mmaiss", "accrdy", "scan", "slow", "gather", "epi", "done")]
-print("prologue detail (tma_issued, x_issued, tmem_alloc, ones):")
+print("prologue detail (tma_issued, -, tmem_alloc, ones, x_landed, xx_ready):")
 for w in range(32):
     if int(t[w, 0]):
-        print(w, [int(v) - t0 if int(v) else -1 for v in t[w, 45:49]])
+        print(w, [int(v) - t0 if int(v) else -1 for v in t[w, 45:51]])
 print("warp " + " ".join(f"{n:>7s}" for n in names))
 for w in range(32):
     if int(t[w, 0]) == 0:
