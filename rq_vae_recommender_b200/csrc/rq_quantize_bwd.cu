@@ -226,118 +226,430 @@ __device__ __forceinline__ void bwd_level_lc(int mode, float beta, float gl, con
     G.w += fmaf(cg, go.w, fmaf(cr, r.w, fmaf(ce, e.w, t.w)));
 }
 
+// The same level split in two: everything that does not depend on the gradient carried down from the level
+// above (norms, r.e, the MUFU chain) is computed for all levels up front — independent work the scheduler can
+// interleave — so the serial chain per level is two dot products and a handful of FMAs.
+struct BwdLevelPre {
+    float4 r, go, t, e;
+    float lam, iu, iq, iw;
+    int coff;
+};
+template <int LPR, int MODE>
+__device__ __forceinline__ void bwd_level_pre(BwdLevelPre& v) {
+    if (MODE == RQ_MODE_ROTATION_TRICK) {
+        const float rr = group_sum<LPR>(dot4(v.r, v.r)), ee = group_sum<LPR>(dot4(v.e, v.e));
+        const float re = group_sum<LPR>(dot4(v.r, v.e));
+        const float nx = fast_sqrt(rr), ne = fast_sqrt(ee);
+        v.iu = fast_rcp(nx + 1e-8f);
+        v.iq = fast_rcp(ne + 1e-8f);
+        v.lam = ne * fast_rcp(nx + 1e-6f);
+        float ns = fmaf(v.iu * v.iu, rr, fmaf(2.f * v.iu * v.iq, re, v.iq * v.iq * ee));
+        if (ns < 0.0625f) {                             // u ~ -q: the expansion cancels, sum directly (group-uniform)
+            const float4 w = make_float4(fmaf(v.r.x, v.iu, v.e.x * v.iq), fmaf(v.r.y, v.iu, v.e.y * v.iq),
+                                         fmaf(v.r.z, v.iu, v.e.z * v.iq), fmaf(v.r.w, v.iu, v.e.w * v.iq));
+            float x = dot4(w, w);
+            const unsigned gmask = (LPR == 32) ? 0xffffffffu : (((1u << LPR) - 1u) << ((threadIdx.x & 31) / LPR * LPR));
+#pragma unroll
+            for (int o = LPR / 2; o > 0; o >>= 1) x += __shfl_xor_sync(gmask, x, o);
+            ns = x;
+        }
+        v.iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f));
+    }
+}
+template <int LPR, int MODE>
+__device__ __forceinline__ void bwd_level_chain(const BwdLevelPre& v, float beta, float gl, float4& G, float4& gc) {
+    const float4 go = make_float4(v.go.x - G.x, v.go.y - G.y, v.go.z - G.z, v.go.w - G.w);
+    const float g2 = 2.f * gl, b2 = g2 * beta;
+    gc = make_float4(g2 * (v.e.x - v.r.x), g2 * (v.e.y - v.r.y), g2 * (v.e.z - v.r.z), g2 * (v.e.w - v.r.w));
+    float cg, cr, ce;
+    if (MODE == RQ_MODE_ROTATION_TRICK) {
+        const float gr = group_sum<LPR>(dot4(go, v.r)), ge = group_sum<LPR>(dot4(go, v.e));
+        const float gw = v.lam * v.iw * fmaf(v.iu, gr, v.iq * ge);
+        const float gq = v.lam * v.iq * ge;
+        cg = v.lam;
+        cr = 2.f * v.iu * (gq - gw * v.iw) + b2;
+        ce = -2.f * gw * v.iw * v.iq - b2;
+    } else if (MODE == RQ_MODE_STE) {
+        cg = 1.f; cr = b2; ce = -b2;
+    } else {
+        gc.x += go.x; gc.y += go.y; gc.z += go.z; gc.w += go.w;
+        cg = 0.f; cr = b2; ce = -b2;
+    }
+    G.x += fmaf(cg, go.x, fmaf(cr, v.r.x, fmaf(ce, v.e.x, v.t.x)));
+    G.y += fmaf(cg, go.y, fmaf(cr, v.r.y, fmaf(ce, v.e.y, v.t.y)));
+    G.z += fmaf(cg, go.z, fmaf(cr, v.r.z, fmaf(ce, v.e.z, v.t.z)));
+    G.w += fmaf(cg, go.w, fmaf(cr, v.r.w, fmaf(ce, v.e.w, v.t.w)));
+}
+
 struct BwdTmaCfg {
     int T;            // rows per tile
     int cb_smem;      // codebooks staged in shared memory
     int n_tiles;
     int stage_bytes, cb_bytes;
+    int dbg;          // experiments (RQ_BWD_DBG): 1 = no codebook-gradient reductions, 2 = no g_x stores
 };
 
-template <int D>
+template <int D, int MODE>
 __global__ void __launch_bounds__(bwdtma::THREADS, 1) rq_bwd_tma_kernel(BwdParams p, BwdTmaCfg cfg) {
     using namespace bwdtma;
     constexpr int LPR = D / 4, RPW = 32 / LPR;
     constexpr int ROWS_PER_PASS = (THREADS / 32) * RPW;
     extern __shared__ __align__(128) uint8_t smem[];
-    // [stage 0 | stage 1 | codebooks | barriers]; a stage = L x (res tile, g_emb tile), tile = T x D fp32
+    // [stage 0 | stage 1 | ids 0 | ids 1 | codebooks | barriers]; a stage = L x (res tile, g_emb tile),
+    // tile = T x D fp32; ids s = [L][T] int64
     uint8_t* sStage = smem;
-    const float* sCb = reinterpret_cast<const float*>(smem + STAGES * cfg.stage_bytes);
-    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + STAGES * cfg.stage_bytes + cfg.cb_bytes);   // [STAGES] + [1]
+    const int T = cfg.T;
+    const int ids_bytes = p.L * T * 8 + T * 4;              // [L][T] int64 ids, then [T] fp32 g_loss
+    uint8_t* sIds = smem + STAGES * cfg.stage_bytes;
+    const float* sCb = reinterpret_cast<const float*>(sIds + STAGES * ids_bytes);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sIds + STAGES * ids_bytes + cfg.cb_bytes);   // [STAGES] + [1]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int sub = lane % LPR, rsel = lane / LPR;
-    const int T = cfg.T;
     const uint32_t tile_bytes = (uint32_t)T * D * 4;
+    const bool has_gemb = p.g_emb != nullptr, has_gres = p.g_res != nullptr, cb_smem = cfg.cb_smem != 0;
 
     auto issue_tile = [&](int tile, int s) {             // one thread
         const int64_t row0 = (int64_t)tile * T;
         const int64_t rows = (p.B - row0 < T) ? (p.B - row0) : T;
         const uint32_t bytes = (uint32_t)rows * D * 4;
-        mbar_expect_tx(&bar[s], bytes * (p.g_emb ? 2u : 1u) * p.L);
+        mbar_expect_tx(&bar[s], bytes * (has_gemb ? 2u : 1u) * p.L);
         for (int l = 0; l < p.L; ++l) {
             uint8_t* dst = sStage + s * cfg.stage_bytes + (size_t)l * 2 * tile_bytes;
             bulk_g2s(dst, p.res + ((int64_t)l * p.B + row0) * D, bytes, &bar[s]);
-            if (p.g_emb) bulk_g2s(dst + tile_bytes, p.g_emb + ((int64_t)l * p.B + row0) * D, bytes, &bar[s]);
+            if (has_gemb) bulk_g2s(dst + tile_bytes, p.g_emb + ((int64_t)l * p.B + row0) * D, bytes, &bar[s]);
         }
+    };
+    // ids of a tile: 8-byte cp.async per (level, row), one element per thread and round
+    auto issue_ids = [&](int tile, int s) {
+        if (tile < cfg.n_tiles) {
+            for (int i = tid; i < p.L * T; i += THREADS) {
+                const int l = i / T, rr = i - l * T;
+                const int64_t row = (int64_t)tile * T + rr;
+                if (row < p.B) {
+                    const uint32_t dst = smem_u32(sIds + s * ids_bytes + i * 8);
+                    const int64_t* src = p.ids + (int64_t)l * p.B + row;
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+                }
+            }
+            if (p.g_loss && tid < T && (int64_t)tile * T + tid < p.B) {
+                const uint32_t dst = smem_u32(sIds + s * ids_bytes + p.L * T * 8 + tid * 4);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(p.g_loss + (int64_t)tile * T + tid)
+                             : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
     if (tid == 0) {
         for (int i = 0; i <= STAGES; ++i) mbar_init(&bar[i], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        if (cfg.cb_smem) {
+        if (cb_smem) {
             mbar_expect_tx(&bar[STAGES], (uint32_t)cfg.cb_bytes);
-            bulk_g2s(smem + STAGES * cfg.stage_bytes, p.cb, (uint32_t)cfg.cb_bytes, &bar[STAGES]);
+            bulk_g2s(const_cast<float*>(sCb), p.cb, (uint32_t)cfg.cb_bytes, &bar[STAGES]);
         }
         for (int s = 0; s < STAGES; ++s) {
             const int tile = blockIdx.x + s * gridDim.x;
             if (tile < cfg.n_tiles) issue_tile(tile, s);
         }
     }
+    for (int s = 0; s < STAGES; ++s) issue_ids(blockIdx.x + s * gridDim.x, s);
     __syncthreads();
-    // ids of the first tile (this lane's row in every pass handled below is row = pass*ROWS_PER_PASS + warp*RPW + rsel)
-    const int my_row = warp * RPW + rsel;
-    constexpr int MAXP = 4;                               // passes per tile (T <= 4 * ROWS_PER_PASS)
-    int32_t ids_next[MAXP][kBwdMaxL];
-    auto load_ids = [&](int tile, int32_t (&dst)[MAXP][kBwdMaxL]) {
-#pragma unroll
-        for (int ps = 0; ps < MAXP; ++ps) {
-            const int64_t row = (int64_t)tile * T + ps * ROWS_PER_PASS + my_row;
-#pragma unroll
-            for (int l = 0; l < kBwdMaxL; ++l)
-                dst[ps][l] = (ps * ROWS_PER_PASS < T && l < p.L && tile < cfg.n_tiles && row < p.B)
-                                 ? (int32_t)__ldg(p.ids + (int64_t)l * p.B + row) : 0;
-        }
-    };
-    load_ids(blockIdx.x, ids_next);
     bool timed_out = false;
-    if (cfg.cb_smem && !mbar_wait(&bar[STAGES], 0)) timed_out = true;
+    if (cb_smem && !mbar_wait(&bar[STAGES], 0)) timed_out = true;
+    const int my_row = warp * RPW + rsel;
 
     int it = 0;
     for (int tile = blockIdx.x; tile < cfg.n_tiles; tile += gridDim.x, ++it) {
         const int s = it % STAGES;
-        int32_t ids_cur[MAXP][kBwdMaxL];
-#pragma unroll
-        for (int ps = 0; ps < MAXP; ++ps)
-#pragma unroll
-            for (int l = 0; l < kBwdMaxL; ++l) ids_cur[ps][l] = ids_next[ps][l];
-        load_ids(tile + gridDim.x, ids_next);             // in flight during this tile's arithmetic
+        // this tile's ids: all but the newest cp.async group are complete, then make them CTA-visible
+        asm volatile("cp.async.wait_group %0;" ::"n"(STAGES - 1) : "memory");
+        __syncthreads();
         if (!mbar_wait(&bar[s], (it / STAGES) & 1)) timed_out = true;
         const uint8_t* st = sStage + s * cfg.stage_bytes;
-#pragma unroll
-        for (int ps = 0; ps < MAXP; ++ps) {
-            if (ps * ROWS_PER_PASS >= T) break;
-            const int trow = ps * ROWS_PER_PASS + my_row;
+        const int64_t* ids_s = reinterpret_cast<const int64_t*>(sIds + s * ids_bytes);
+#pragma unroll 1
+        for (int trow = my_row; trow < ((cfg.dbg & 4) ? 0 : T); trow += ROWS_PER_PASS) {
             const int64_t row = (int64_t)tile * T + trow;
             const bool valid = row < p.B;
-            const float gl = (p.g_loss && valid) ? __ldg(p.g_loss + row) : 0.f;
+            const float gl = (p.g_loss && valid) ? reinterpret_cast<const float*>(ids_s + p.L * T)[trow] : 0.f;
             float4 G = make_float4(0.f, 0.f, 0.f, 0.f);
             // rows past B run the arithmetic on whatever the stage holds (the lane-group shuffles need every
             // lane of the warp) and are masked at the stores
+            BwdLevelPre lv[kBwdMaxL];
+            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int l = 0; l < kBwdMaxL; ++l) {
+                if (l < p.L) {
+                    const uint8_t* src = st + (size_t)l * 2 * tile_bytes + (size_t)trow * D * 4 + sub * 16;
+                    lv[l].r = *reinterpret_cast<const float4*>(src);
+                    lv[l].go = has_gemb ? *reinterpret_cast<const float4*>(src + tile_bytes) : z4;
+                    lv[l].t = (has_gres && valid) ? ldg_stream4(p.g_res + ((int64_t)l * p.B + row) * D + sub * 4) : z4;
+                    const int id = valid ? (int)ids_s[l * T + trow] : 0;
+                    lv[l].coff = (l * p.K + id) * D + sub * 4;
+                    lv[l].e = cb_smem ? *reinterpret_cast<const float4*>(sCb + lv[l].coff) : ldg_nc4(p.cb + lv[l].coff);
+                }
+            }
+#pragma unroll
+            for (int l = 0; l < kBwdMaxL; ++l)
+                if (l < p.L) bwd_level_pre<LPR, MODE>(lv[l]);
 #pragma unroll
             for (int l = kBwdMaxL - 1; l >= 0; --l) {
                 if (l < p.L) {
-                    const uint8_t* lv = st + (size_t)l * 2 * tile_bytes + (size_t)trow * D * 4 + sub * 16;
-                    const float4 r = *reinterpret_cast<const float4*>(lv);
-                    const float4 go = p.g_emb ? *reinterpret_cast<const float4*>(lv + tile_bytes)
-                                              : make_float4(0.f, 0.f, 0.f, 0.f);
-                    const float4 t = (p.g_res && valid) ? ldg_stream4(p.g_res + ((int64_t)l * p.B + row) * D + sub * 4)
-                                                        : make_float4(0.f, 0.f, 0.f, 0.f);
-                    const int64_t coff = ((int64_t)l * p.K + ids_cur[ps][l]) * D + sub * 4;
-                    const float4 e = cfg.cb_smem ? *reinterpret_cast<const float4*>(sCb + coff) : ldg_nc4(p.cb + coff);
                     float4 gc;
-                    bwd_level_lc<LPR>(p.mode, p.beta, gl, r, go, t, e, G, gc);
-                    if (valid) red_add_v4(p.g_cb + coff, gc.x, gc.y, gc.z, gc.w);
+                    bwd_level_chain<LPR, MODE>(lv[l], p.beta, gl, G, gc);
+                    if (valid && !(cfg.dbg & 1)) red_add_v4(p.g_cb + lv[l].coff, gc.x, gc.y, gc.z, gc.w);
                 }
             }
-            if (valid) *reinterpret_cast<float4*>(p.g_x + row * D + sub * 4) = G;
+            if (valid && !(cfg.dbg & 2)) *reinterpret_cast<float4*>(p.g_x + row * D + sub * 4) = G;
         }
         // everybody is done with stage s: refill it with the tile STAGES iterations ahead
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
-        if (tid == 0) {
-            const int nt = tile + STAGES * gridDim.x;
-            if (nt < cfg.n_tiles) issue_tile(nt, s);
+        const int nt = tile + STAGES * gridDim.x;
+        if (tid == 0 && nt < cfg.n_tiles) issue_tile(nt, s);
+        issue_ids(nt, s);
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    (void)timed_out;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Row-per-thread variant for D = 32 (the headline shape).  The lane-group kernels above spend 8 lanes on a
+// row, so every warp instruction advances 4 rows; here a thread owns a row (as in the forward kernel) and a
+// warp instruction advances 32 — ~4x fewer instructions, no shuffles in the arithmetic.
+//
+// Every WARP is an independent pipeline over 32-row tiles: the (residual, upstream gradient) rows of one
+// (tile, level) are one 8 KB stage, fetched with 16-byte cp.async in the coalesced pattern (8 lanes per
+// 128-byte row) into a 128-byte-swizzled layout and read back row-wise by the owning lanes without bank
+// conflicts; a 3-stage ring per warp keeps two stages (16 KB) in flight while one is processed, 8 warps per
+// SM.  Rows are warp-private, so __syncwarp is the only synchronisation.  Codeword gathers, the codebook-
+// gradient reductions (REDG.128) and the g_x stores also use the coalesced pattern: the stage just consumed
+// doubles as the staging tile.
+namespace bwdrow {
+constexpr int D = 32, TW = 32, WARPS = 4, THREADS = 32 * WARPS, STAGES = 3;
+constexpr int STAGE_BYTES = 2 * TW * D * 4;            // 8 KB: residual rows, then gradient rows
+__device__ __forceinline__ uint32_t sw_off(int r, int c) {
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+}
+}  // namespace bwdrow
+
+template <int MODE>
+__global__ void __launch_bounds__(bwdrow::THREADS, 2) rq_bwd_row_kernel(BwdParams p, int n_tiles, int dbg) {
+    using namespace bwdrow;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* ring = smem + warp * (STAGES * STAGE_BYTES);
+    const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(ring);
+    const bool has_gemb = p.g_emb != nullptr;
+    const int chunk = lane & 7;
+    const uint32_t co_sw = sw_off(lane >> 3, chunk);        // coalesced pattern: chunk of rows 4 i + lane / 8
+    auto co_off = [&](int i) -> uint32_t { return (co_sw + 512u * i) ^ ((i & 1) ? 64u : 0u); };
+    const int wglobal = blockIdx.x * WARPS + warp, nwarps = gridDim.x * WARPS;
+    const int my_tiles = (n_tiles > wglobal) ? (n_tiles - 1 - wglobal) / nwarps + 1 : 0;
+    const int n_items = my_tiles * p.L;                      // (tile, level) pairs in processing order
+
+    // item q -> tile index, level (levels walk downwards inside a tile)
+    auto issue_item = [&](int q) {
+        if (q < n_items && !(dbg & 8)) {
+            const int ti = q / p.L, l = p.L - 1 - (q - ti * p.L);
+            const int64_t row0 = ((int64_t)wglobal + (int64_t)ti * nwarps) * TW;
+            const uint32_t dst0 = ring_u32 + (q % STAGES) * STAGE_BYTES;
+            const float* src_r = p.res + ((int64_t)l * p.B + row0 + (lane >> 3)) * D + chunk * 4;
+            const float* src_g = has_gemb ? p.g_emb + ((int64_t)l * p.B + row0 + (lane >> 3)) * D + chunk * 4 : nullptr;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (row0 + (lane >> 3) + 4 * i < p.B) {
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + co_off(i)), "l"(src_r + i * 4 * D)
+                                 : "memory");
+                    if (has_gemb)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + TW * D * 4 + co_off(i)),
+                                     "l"(src_g + i * 4 * D)
+                                     : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto gather = [&](int l, int id, float4 (&g)[8]) {       // coalesced codeword fetch for the warp's 32 rows
+        const float* base = p.cb + (int64_t)l * p.K * D + chunk * 4;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int k = __shfl_sync(0xffffffffu, id, 4 * i + (lane >> 3));
+            g[i] = __ldg(reinterpret_cast<const float4*>(base + (int64_t)k * D));
+        }
+    };
+    int ids_n[kBwdMaxL];
+    float gl_n = 0.f;
+    auto load_ids = [&](int ti) {                            // ids / g_loss of this lane's row in tile ti
+        const int64_t row = ((int64_t)wglobal + (int64_t)ti * nwarps) * TW + lane;
+        const bool ok = ti < my_tiles && row < p.B;
+#pragma unroll
+        for (int l = 0; l < kBwdMaxL; ++l) ids_n[l] = (ok && l < p.L) ? (int)__ldg(p.ids + (int64_t)l * p.B + row) : 0;
+        gl_n = (ok && p.g_loss) ? __ldg(p.g_loss + row) : 0.f;
+    };
+    auto pick = [&](const int (&a)[kBwdMaxL], int l) { return (l == 3) ? a[3] : (l == 2) ? a[2] : (l == 1) ? a[1] : a[0]; };
+
+    issue_item(0);
+    issue_item(1);
+    load_ids(0);
+    float4 gnext[8];
+    if (my_tiles > 0) gather(p.L - 1, pick(ids_n, p.L - 1), gnext);
+
+    int q = 0;
+    for (int ti = 0; ti < my_tiles; ++ti) {
+        const int64_t row0 = ((int64_t)wglobal + (int64_t)ti * nwarps) * TW;
+        const int64_t row = row0 + lane;
+        const bool valid = row < p.B;
+        int ids[kBwdMaxL];
+#pragma unroll
+        for (int l = 0; l < kBwdMaxL; ++l) ids[l] = ids_n[l];
+        const float gl = gl_n;
+        load_ids(ti + 1);                                    // next tile's ids / g_loss in flight
+        const float g2 = 2.f * gl, b2 = g2 * p.beta;
+        float G[D];
+#pragma unroll
+        for (int j = 0; j < D; ++j) G[j] = 0.f;
+#pragma unroll 1
+        for (int l = (dbg & 4) ? -1 : p.L - 1; l >= 0; --l, ++q) {
+            const int id = pick(ids, l);
+            issue_item(q + 2);                               // into the stage consumed at q - 1
+            asm volatile("cp.async.wait_group 2;" ::: "memory");   // item q landed (two newer groups may be pending)
+            __syncwarp();
+            uint8_t* st = ring + (q % STAGES) * STAGE_BYTES;
+            float e[D], r[D], go[D];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const float4 v = *reinterpret_cast<const float4*>(st + sw_off(lane, c));
+                r[4 * c] = v.x; r[4 * c + 1] = v.y; r[4 * c + 2] = v.z; r[4 * c + 3] = v.w;
+            }
+            if (has_gemb) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const float4 v = *reinterpret_cast<const float4*>(st + TW * D * 4 + sw_off(lane, c));
+                    go[4 * c] = v.x - G[4 * c]; go[4 * c + 1] = v.y - G[4 * c + 1];
+                    go[4 * c + 2] = v.z - G[4 * c + 2]; go[4 * c + 3] = v.w - G[4 * c + 3];
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < D; ++j) go[j] = -G[j];
+            }
+            __syncwarp();                                    // the stage is now free: it doubles as the staging tile
+            uint8_t* scratch = st;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) *reinterpret_cast<float4*>(scratch + co_off(i)) = gnext[i];
+            __syncwarp();
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const float4 v = *reinterpret_cast<const float4*>(scratch + sw_off(lane, c));
+                e[4 * c] = v.x; e[4 * c + 1] = v.y; e[4 * c + 2] = v.z; e[4 * c + 3] = v.w;
+            }
+            __syncwarp();
+            // next item's codewords go out now (next level of this tile, or the first level of the next tile)
+            if (l > 0) gather(l - 1, pick(ids, l - 1), gnext);
+            else if (ti + 1 < my_tiles) gather(p.L - 1, pick(ids_n, p.L - 1), gnext);
+            float cg, cr, ce;
+            if (MODE == RQ_MODE_ROTATION_TRICK) {
+                float rr = 0.f, ee = 0.f, re = 0.f, gr = 0.f, ge = 0.f;
+#pragma unroll
+                for (int j = 0; j < D; ++j) {
+                    rr = fmaf(r[j], r[j], rr); ee = fmaf(e[j], e[j], ee); re = fmaf(r[j], e[j], re);
+                    gr = fmaf(go[j], r[j], gr); ge = fmaf(go[j], e[j], ge);
+                }
+                const float nx = fast_sqrt(rr), ne = fast_sqrt(ee);
+                const float iu = fast_rcp(nx + 1e-8f), iq = fast_rcp(ne + 1e-8f);
+                const float lam = ne * fast_rcp(nx + 1e-6f);
+                float ns = fmaf(iu * iu, rr, fmaf(2.f * iu * iq, re, iq * iq * ee));
+                if (ns < 0.0625f) {
+                    ns = 0.f;
+#pragma unroll
+                    for (int j = 0; j < D; ++j) {
+                        const float w = fmaf(r[j], iu, e[j] * iq);
+                        ns = fmaf(w, w, ns);
+                    }
+                }
+                const float iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f));
+                const float gw = lam * iw * fmaf(iu, gr, iq * ge);
+                const float gq = lam * iq * ge;
+                cg = lam;
+                cr = 2.f * iu * (gq - gw * iw) + b2;
+                ce = -2.f * gw * iw * iq - b2;
+            } else if (MODE == RQ_MODE_STE) {
+                cg = 1.f; cr = b2; ce = -b2;
+            } else {
+                cg = 0.f; cr = b2; ce = -b2;
+            }
+            // this row's codebook gradient 2 (e - r) g_loss (+ go when the output is the codeword itself):
+            // staged, then reduced into g_cb by the coalesced pattern (4 codeword rows per REDG.128 instruction)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float4 v = make_float4(g2 * (e[4 * c] - r[4 * c]), g2 * (e[4 * c + 1] - r[4 * c + 1]),
+                                       g2 * (e[4 * c + 2] - r[4 * c + 2]), g2 * (e[4 * c + 3] - r[4 * c + 3]));
+                if (MODE == RQ_MODE_EVAL) { v.x += go[4 * c]; v.y += go[4 * c + 1]; v.z += go[4 * c + 2]; v.w += go[4 * c + 3]; }
+                *reinterpret_cast<float4*>(scratch + sw_off(lane, c)) = v;
+            }
+            __syncwarp();
+            {
+                float* gbase = p.g_cb + (int64_t)l * p.K * D + chunk * 4;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k = __shfl_sync(0xffffffffu, id, 4 * i + (lane >> 3));
+                    const float4 v = *reinterpret_cast<const float4*>(scratch + co_off(i));
+                    if (row0 + (lane >> 3) + 4 * i < p.B && !(dbg & 1)) red_add_v4(gbase + (int64_t)k * D, v.x, v.y, v.z, v.w);
+                }
+            }
+            if (p.g_res && valid) {
+                const float* tg = p.g_res + ((int64_t)l * p.B + row) * D;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const float4 v = ldg_stream4(tg + 4 * c);
+                    G[4 * c] += v.x; G[4 * c + 1] += v.y; G[4 * c + 2] += v.z; G[4 * c + 3] += v.w;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < D; ++j) G[j] += fmaf(cg, go[j], fmaf(cr, r[j], ce * e[j]));
+            if (l == 0) {
+                // g_x: staged in the same tile and written out coalesced
+                __syncwarp();
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    *reinterpret_cast<float4*>(scratch + sw_off(lane, c)) =
+                        make_float4(G[4 * c], G[4 * c + 1], G[4 * c + 2], G[4 * c + 3]);
+                __syncwarp();
+                float* dst = p.g_x + (row0 + (lane >> 3)) * D + chunk * 4;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 v = *reinterpret_cast<const float4*>(scratch + co_off(i));
+                    if (row0 + (lane >> 3) + 4 * i < p.B) *reinterpret_cast<float4*>(dst + i * 4 * D) = v;
+                }
+            }
+            __syncwarp();                                    // staging reads done before the stage is refilled
         }
     }
-    (void)timed_out;
+    asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
+static int launch_bwd_row(const BwdParams& p, cudaStream_t st, bool* served) {
+    using namespace bwdrow;
+    *served = false;
+    if (p.L > kBwdMaxL || getenv("RQ_BWD_NO_ROW")) return 0;
+    if ((((uintptr_t)p.res | (uintptr_t)p.g_emb | (uintptr_t)p.cb | (uintptr_t)p.g_x | (uintptr_t)p.g_cb) & 15) != 0) return 0;
+    const size_t smem = (size_t)WARPS * STAGES * STAGE_BYTES;  // 96 KB: two CTAs per SM
+    const int n_tiles = (int)((p.B + TW - 1) / TW);
+    const int ctas_needed = (n_tiles + WARPS - 1) / WARPS;
+    const int grid = ctas_needed < 2 * sm_count() ? ctas_needed : 2 * sm_count();
+    const int dbg = getenv("RQ_BWD_DBG") ? atoi(getenv("RQ_BWD_DBG")) : 0;
+    auto launch = [&](auto kern) -> int {
+        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, THREADS, smem, st>>>(p, n_tiles, dbg);
+        return 0;
+    };
+    int rc;
+    if (p.mode == RQ_MODE_ROTATION_TRICK) rc = launch(rq_bwd_row_kernel<RQ_MODE_ROTATION_TRICK>);
+    else if (p.mode == RQ_MODE_STE) rc = launch(rq_bwd_row_kernel<RQ_MODE_STE>);
+    else rc = launch(rq_bwd_row_kernel<RQ_MODE_EVAL>);
+    if (rc) return rc;
+    RQ_LAUNCHED();
+    *served = true;
+    return 0;
 }
 
 template <int D>
@@ -357,27 +669,32 @@ static int launch_bwd_tma(const BwdParams& p, cudaStream_t st, bool* served) {
         // prefer 64-row tiles with the codebooks resident; shrink the tile before giving the codebooks up
         const int64_t stage = (int64_t)p.L * 2 * cand * D * 4;
         if (cand > 64 && cand > ROWS_PER_PASS) continue;
-        if (STAGES * stage + cb_all + 64 <= kSmemBudget && cb_all <= 96 * 1024) { T = cand; cfg.cb_smem = 1; cfg.cb_bytes = (int)cb_all; break; }
+        if (STAGES * (stage + (int64_t)p.L * cand * 8 + cand * 4) + cb_all + 64 <= kSmemBudget && cb_all <= 96 * 1024) { T = cand; cfg.cb_smem = 1; cfg.cb_bytes = (int)cb_all; break; }
     }
     if (!T) {
         for (int cand = 4 * ROWS_PER_PASS; cand >= ROWS_PER_PASS; cand /= 2) {
             const int64_t stage = (int64_t)p.L * 2 * cand * D * 4;
             if (cand > 128 && cand > ROWS_PER_PASS) continue;
-            if (STAGES * stage + 64 <= kSmemBudget) { T = cand; break; }
+            if (STAGES * (stage + (int64_t)p.L * cand * 8 + cand * 4) + 64 <= kSmemBudget) { T = cand; break; }
         }
     }
     if (!T) return 0;
     cfg.T = T;
+    cfg.dbg = getenv("RQ_BWD_DBG") ? atoi(getenv("RQ_BWD_DBG")) : 0;
     cfg.stage_bytes = p.L * 2 * T * D * 4;
     cfg.n_tiles = (int)((p.B + T - 1) / T);
-    const size_t smem = (size_t)STAGES * cfg.stage_bytes + cfg.cb_bytes + 64;
-    static bool attr_set = false;
-    if (!attr_set) {
-        RQ_CUDA(cudaFuncSetAttribute(rq_bwd_tma_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
+    const size_t smem = (size_t)STAGES * (cfg.stage_bytes + p.L * T * 8 + T * 4) + cfg.cb_bytes + 64;
     const int grid = cfg.n_tiles < sm_count() ? cfg.n_tiles : sm_count();
-    rq_bwd_tma_kernel<D><<<grid, THREADS, smem, st>>>(p, cfg);
+    auto launch = [&](auto kern) -> int {
+        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        kern<<<grid, THREADS, smem, st>>>(p, cfg);
+        return 0;
+    };
+    int rc;
+    if (p.mode == RQ_MODE_ROTATION_TRICK) rc = launch(rq_bwd_tma_kernel<D, RQ_MODE_ROTATION_TRICK>);
+    else if (p.mode == RQ_MODE_STE) rc = launch(rq_bwd_tma_kernel<D, RQ_MODE_STE>);
+    else rc = launch(rq_bwd_tma_kernel<D, RQ_MODE_EVAL>);
+    if (rc) return rc;
     RQ_LAUNCHED();
     *served = true;
     return 0;
@@ -403,7 +720,8 @@ int quantize_backward_simt(const BwdParams& p, int D, cudaStream_t st) {
     {
         bool served = false;
         int rc = 0;
-        if (D == 32) rc = launch_bwd_tma<32>(p, st, &served);
+        if (D == 32) rc = launch_bwd_row(p, st, &served);
+        if (!rc && !served && D == 32) rc = launch_bwd_tma<32>(p, st, &served);
         else if (D == 64) rc = launch_bwd_tma<64>(p, st, &served);
         else if (D == 16) rc = launch_bwd_tma<16>(p, st, &served);
         if (rc || served) return rc;
