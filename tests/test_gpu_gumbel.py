@@ -1,0 +1,102 @@
+"""GPU: Gumbel-softmax backward (rq_quantize_backward, mode 1) against the reference's autograd
+(golden fixtures) and the CPU oracle on seeded shapes; Philox-noise mode against finite differences."""
+import pytest
+import torch
+
+import rq_oracle as O
+from rq_vae_recommender_b200 import functional as RF
+from conftest import load_golden
+from parity_utils import assert_close, synthetic_codebooks
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.mark.parametrize("name", ["rq_stack_d32_k256_l3.npz", "rq_stack_d64_k256_l3.npz", "rq_stack_d64_k1024_l4.npz"])
+def test_golden_gumbel_backward(name):
+    """Gradients the unmodified reference produced (autograd through rand->log->softmax->GEMM)."""
+    z = load_golden(name)
+    if "gumbel_gx" not in z:
+        pytest.skip("fixture has no Gumbel gradients")
+    x = torch.from_numpy(z["x"]).to(DEV).requires_grad_(True)
+    cbs = torch.from_numpy(z["codebooks"]).to(DEV).requires_grad_(True)
+    gu = torch.from_numpy(z["gumbel_uniform"]).to(DEV)
+    g_emb, g_loss = torch.from_numpy(z["g_emb"]).to(DEV), torch.from_numpy(z["g_loss"]).to(DEV)
+    emb, res, ids, loss = RF.residual_quantize(x, cbs, RF.MODE_GUMBEL_SOFTMAX, 0.25, 0.2, RF.DIST_L2, gu)
+    ((emb * g_emb).sum() + (loss * g_loss).sum()).backward()
+    assert_close(x.grad.cpu(), torch.from_numpy(z["gumbel_gx"]), "gumbel grad x")
+    assert_close(cbs.grad.cpu(), torch.from_numpy(z["gumbel_gcb"]), "gumbel grad codebooks")
+
+
+@pytest.mark.parametrize("B,D,K,L,with_gres", [(1, 32, 256, 3, False), (130, 32, 100, 2, True), (257, 16, 64, 3, False),
+                                               (300, 64, 1024, 2, True), (64, 8, 20, 4, False)])
+def test_gumbel_backward_vs_oracle(B, D, K, L, with_gres):
+    g = torch.Generator().manual_seed(B + D + K)
+    x = torch.randn(B, D, generator=g)
+    cbs = synthetic_codebooks(torch.randn(max(4 * K, 512), D, generator=g), L, K, seed=3)
+    u = torch.rand(L, B, K, generator=g)
+    g_emb = torch.randn(L, B, D, generator=g)
+    g_loss = torch.rand(B, generator=g)
+    g_res = torch.randn(L, B, D, generator=g) if with_gres else None
+    T, beta = 0.7, 0.25
+    ref, gx_ref, gcb_ref = O.rq_forward_backward(x, cbs, O.MODE_GUMBEL_SOFTMAX, beta, T, g_emb, g_loss,
+                                                 uniforms=u, g_res=g_res)
+    xd = x.to(DEV).requires_grad_(True)
+    cd = torch.stack(cbs).to(DEV).requires_grad_(True)
+    emb, res, ids, loss = RF.residual_quantize(xd, cd, RF.MODE_GUMBEL_SOFTMAX, beta, T, RF.DIST_L2, u.to(DEV))
+    obj = (emb * g_emb.to(DEV)).sum() + (loss * g_loss.to(DEV)).sum()
+    if g_res is not None:
+        obj = obj + (res * g_res.to(DEV)).sum()
+    obj.backward()
+    assert_close(emb.detach().cpu(), ref.embeddings.detach(), "emb")
+    assert_close(xd.grad.cpu(), gx_ref, "grad x")
+    assert_close(cd.grad.cpu(), gcb_ref, "grad codebooks")
+
+
+def _philox_uniforms(L, B, K, seed, offset):
+    """Host replica of the kernels' noise: Philox4x32-10, counter (row_lo, row_hi, code >> 2, level),
+    key (seed ^ offset) split in two words, 24-bit uniforms (csrc/rq_common.cuh)."""
+    import numpy as np
+    M0, M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)
+    key = (seed ^ offset) & 0xFFFFFFFFFFFFFFFF
+    k0 = np.uint64(key & 0xFFFFFFFF)
+    k1 = np.uint64(key >> 32)
+    rows = np.arange(B, dtype=np.uint64)
+    out = np.zeros((L, B, K), dtype=np.float32)
+    mask = np.uint64(0xFFFFFFFF)
+    for l in range(L):
+        for grp in range((K + 3) // 4):
+            c = [rows & mask, rows >> np.uint64(32), np.full(B, grp, np.uint64), np.full(B, l, np.uint64)]
+            ka, kb = k0, k1
+            for _ in range(10):
+                p0, p1 = M0 * c[0], M1 * c[2]
+                hi0, lo0, hi1, lo1 = p0 >> np.uint64(32), p0 & mask, p1 >> np.uint64(32), p1 & mask
+                c = [hi1 ^ c[1] ^ ka, lo1, hi0 ^ c[3] ^ kb, lo0]
+                ka = (ka + np.uint64(0x9E3779B9)) & mask
+                kb = (kb + np.uint64(0xBB67AE85)) & mask
+            for q in range(4):
+                if grp * 4 + q < K:
+                    out[l, :, grp * 4 + q] = (c[q] >> np.uint64(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)
+    return torch.from_numpy(out)
+
+
+def test_gumbel_philox_noise_is_reproduced_by_the_backward():
+    """In-kernel Philox noise: forward and backward with (seed, offset) must equal forward and backward fed
+    the same uniforms explicitly (computed on the host)."""
+    B, D, K, L = 70, 32, 50, 2
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(B, D, generator=g).to(DEV)
+    cbs = torch.stack(synthetic_codebooks(torch.randn(512, D, generator=g), L, K, seed=1)).to(DEV)
+    g_emb = torch.randn(L, B, D, generator=g).to(DEV)
+    g_loss = torch.rand(B, generator=g).to(DEV)
+    seed, offset, T = 1234567891011, 7, 0.5
+    u = _philox_uniforms(L, B, K, seed, offset).to(DEV)
+    e1, r1, i1, l1 = RF.quantize_forward(x, cbs, RF.MODE_GUMBEL_SOFTMAX, 0.25, T, seed=seed, offset=offset)
+    e2, r2, i2, l2 = RF.quantize_forward(x, cbs, RF.MODE_GUMBEL_SOFTMAX, 0.25, T, gumbel_uniform=u)
+    assert_close(e1.cpu(), e2.cpu(), "philox forward emb", tol=1e-5)
+    assert_close(l1.cpu(), l2.cpu(), "philox forward loss", tol=1e-5)
+    gx1, gc1 = RF.quantize_backward(g_emb, None, g_loss, r1, i1, cbs, RF.MODE_GUMBEL_SOFTMAX, 0.25, T,
+                                    seed=seed, offset=offset)
+    gx2, gc2 = RF.quantize_backward(g_emb, None, g_loss, r2, i2, cbs, RF.MODE_GUMBEL_SOFTMAX, 0.25, T, gumbel_uniform=u)
+    assert_close(gx1.cpu(), gx2.cpu(), "philox backward g_x", tol=1e-4)
+    assert_close(gc1.cpu(), gc2.cpu(), "philox backward g_codebooks", tol=1e-4)
