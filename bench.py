@@ -55,6 +55,22 @@ def peaks():
     return 6650.0, "fallback"
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` extract under profiles/ (None when no capture of that kernel is committed)."""
+    name = {"rq_fwd": "r1_ncu_full_fwd_tc_v3.csv", "rq_bwd": "r1_ncu_full_bwd_row_v3.csv"}.get(kernel)
+    path = os.path.join(ROOT, "profiles", name) if name else None
+    if not path or not os.path.exists(path):
+        return None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    for line in open(path):
+        f = line.strip().split(",")
+        if len(f) == 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and f[1] in unit:
+            tot += float(f[2]) * unit[f[1]]
+    return tot or None
+
+
 def make_inputs(torch, device, n_slots, seed):
     """Synthetic latents with trained-looking codebooks: level l = K residual rows of the data."""
     g = torch.Generator(device="cpu").manual_seed(seed)
@@ -374,7 +390,7 @@ def run_engine(args):
                     "h2d_bytes_per_step": B_PER_GPU * D * 4, "d2h_bytes_per_step": B_PER_GPU * 4 + L * B_PER_GPU * 8},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",
-                         "frac": achieved / hbm, "traffic": None, "peak_source": which + " (burst copy)",
+                         "frac": achieved / hbm, "traffic": ncu_traffic(dom), "peak_source": which + " (burst copy)",
                          "algorithmic_bytes_per_launch": B_PER_GPU * BYTES_FWD, "launch_ms": dom_ms},
             "clocks": clk.summary(),
             "extra": {"fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "ids_only_ms": ids_only_ms,

@@ -103,10 +103,18 @@ extern "C" int rq_kmeans_assign_accumulate(const float* x, const float* centroid
     RQ_CHECK_ARG(pow2_dim(D), RQ_ERR_UNSUPPORTED_SHAPE, "rq_kmeans_assign_accumulate: unsupported D=%d", D);
     RQ_CHECK_ARG(sums && counts && n_changed && centroids, RQ_ERR_NULL_POINTER, "rq_kmeans_assign_accumulate: null pointer");
     RQ_CHECK_ARG(B == 0 || (x && assign), RQ_ERR_NULL_POINTER, "rq_kmeans_assign_accumulate: null pointer");
-    (void)impl;
     KmeansParams p;
     p.x = x; p.centroids = centroids; p.B = B; p.K = K; p.assign = assign; p.has_prev = has_prev;
     p.sums = sums; p.counts = (unsigned long long*)counts; p.n_changed = (unsigned long long*)n_changed; p.KC = 0;
+    // AUTO: the tcgen05 distance kernel when it serves the shape (it computes the expanded form ||c||^2 - 2x.c
+    // with fp32 re-scoring; assignments can differ from the direct form only inside the fp32 tie band)
+    const bool tc_ok = tc_supported(D, K, 1, RQ_MODE_EVAL, RQ_DIST_L2) && (((uintptr_t)centroids & 15) == 0) &&
+                       (((uintptr_t)x & 31) == 0);
+    if (impl == RQ_IMPL_TCGEN05) {
+        RQ_CHECK_ARG(tc_ok, RQ_ERR_UNSUPPORTED_SHAPE, "rq_kmeans_assign_accumulate: (D=%d,K=%d) is not served by the tcgen05 family", D, K);
+        return kmeans_assign_accumulate_tc(p, D, (cudaStream_t)stream);
+    }
+    if (impl == RQ_IMPL_AUTO && tc_ok && B >= 4096) return kmeans_assign_accumulate_tc(p, D, (cudaStream_t)stream);
     return kmeans_assign_accumulate_simt(p, D, (cudaStream_t)stream);
 }
 

@@ -18,6 +18,10 @@ struct FwdParams {
     int64_t* ids;
     float* loss;
     int KC;  // codes per shared-memory chunk (multiple of 4)
+    // k-means use of the forward (L = 1, ids = assignment): count rows whose id differs from the value already
+    // stored at ids[] (all rows when !has_prev).  nullptr = off.
+    unsigned long long* n_changed = nullptr;
+    int has_prev = 0;
 };
 
 struct BwdParams {
@@ -53,6 +57,7 @@ int quantize_backward_simt(const BwdParams& p, int D, cudaStream_t st);
 int quantize_backward_gumbel(const BwdParams& p, int D, float temperature, const float* gu, uint64_t seed,
                              uint64_t offset, cudaStream_t st);
 int kmeans_assign_accumulate_simt(const KmeansParams& p, int D, cudaStream_t st);
+int kmeans_assign_accumulate_tc(const KmeansParams& p, int D, cudaStream_t st);
 int kmeans_update(const float* sums, const int64_t* counts, float* centroids, int D, int K, float* max_shift,
                   int64_t* n_empty, int64_t* empty_ids, cudaStream_t st);
 

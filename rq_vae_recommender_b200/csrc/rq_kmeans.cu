@@ -92,6 +92,53 @@ int kmeans_assign_accumulate_simt(const KmeansParams& p, int D, cudaStream_t st)
     }
 }
 
+// ---- tensor-core assignment + coalesced accumulation --------------------------------------------------------
+// The assignment IS the fused quantiser's forward with L = 1 in ids-only mode (rq_quantize_tc.cu: TMA-staged
+// centroids, tcgen05 distances, fp32 re-scoring of near ties), writing straight into `assign` and counting
+// changed rows.  The accumulation is a second HBM-streaming kernel in the coalesced pattern: D/4 lanes per
+// point, one 16-byte L2 reduction (REDG.128) per lane into sums[assign], one count atomic per point.
+template <int D>
+__global__ void __launch_bounds__(256) rq_kmeans_accumulate_kernel(const float* __restrict__ x,
+                                                                   const int64_t* __restrict__ assign, int64_t B,
+                                                                   float* __restrict__ sums,
+                                                                   unsigned long long* __restrict__ counts) {
+    constexpr int LPR = D / 4;
+    const int64_t n_chunks = B * LPR;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_chunks; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / LPR;
+        const int sub = (int)(i - row * LPR);
+        const int64_t k = __ldg(assign + row);
+        float4 v;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "l"(x + i * 4));
+        red_add_v4(sums + k * D + sub * 4, v.x, v.y, v.z, v.w);
+        if (sub == 0) atomicAdd(counts + k, 1ull);
+    }
+}
+
+int kmeans_assign_accumulate_tc(const KmeansParams& p, int D, cudaStream_t st) {
+    RQ_CUDA(cudaMemsetAsync(p.sums, 0, (size_t)p.K * D * sizeof(float), st));
+    RQ_CUDA(cudaMemsetAsync(p.counts, 0, (size_t)p.K * sizeof(unsigned long long), st));
+    RQ_CUDA(cudaMemsetAsync(p.n_changed, 0, sizeof(unsigned long long), st));
+    if (p.B == 0) return 0;
+    FwdParams f;
+    f.x = p.x; f.cb = p.centroids; f.B = p.B; f.K = p.K; f.L = 1; f.mode = RQ_MODE_EVAL; f.dist = RQ_DIST_L2;
+    f.beta = 0.f; f.temp = 1.f; f.gu = nullptr; f.seed = 0; f.offset = 0;
+    f.emb = nullptr; f.res = nullptr; f.ids = p.assign; f.loss = nullptr; f.KC = 0;
+    f.n_changed = p.n_changed; f.has_prev = p.has_prev;
+    int rc = quantize_forward_tc(f, D, st);
+    if (rc) return rc;
+    const int64_t n_chunks = p.B * (D / 4);
+    int64_t blocks = (n_chunks + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (D == 32) rq_kmeans_accumulate_kernel<32><<<(unsigned)blocks, 256, 0, st>>>(p.x, p.assign, p.B, p.sums, p.counts);
+    else { set_error("kmeans tensor-core path: D=%d not served", D); return RQ_ERR_UNSUPPORTED_SHAPE; }
+    RQ_LAUNCHED();
+    return 0;
+}
+
 // One CTA; thread k owns cluster k (strided).  c_new = sums/count (kmeans.py:57) or unchanged
 // for an empty cluster; shift_k = ||c_new - c_old||_2 (kmeans.py:67).
 __global__ void rq_kmeans_update_kernel(const float* __restrict__ sums, const int64_t* __restrict__ counts,

@@ -347,6 +347,15 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
         }
         __syncwarp();
     };
+    auto store_id = [&](int l, int64_t row, bool active, int bi) {
+        int64_t* dst = p.ids + (int64_t)l * p.B + row;
+        if (p.n_changed) {                                  // k-means: count changed assignments (warp-aggregated)
+            const bool ch = active && (!p.has_prev || *dst != (int64_t)bi);
+            const unsigned m = __ballot_sync(0xffffffffu, ch);
+            if (lane == 0 && m) atomicAdd(p.n_changed, (unsigned long long)__popc(m));
+        }
+        if (active) *dst = bi;
+    };
     const int n_partner_uses = n_partner * p.L;
     const bool is_hi = SHARE && (wg >= 2);
     int use = 0;                                   // this warpgroup's running (tile, level) count
@@ -567,13 +576,13 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
                     park_copy_out(p.emb + ((int64_t)l * p.B + trow0) * D, trow0);
                     __syncwarp();                   // copied out before the next level parks its residual
                 }
-                if (active) p.ids[(int64_t)l * p.B + row] = bi;
-            } else if (active) {
-                if (p.emb) {
+                store_id(l, row, active, bi);
+            } else {
+                if (active && p.emb) {
 #pragma unroll
                     for (int j = 0; j < D; j += 8) ptx::st_global_v8(p.emb + off + j, &o[j]);
                 }
-                p.ids[(int64_t)l * p.B + row] = bi;
+                store_id(l, row, active, bi);
             }
 #pragma unroll
             for (int j = 0; j < D; ++j) r[j] = r[j] - o[j];                     // rqvae.py:129

@@ -81,6 +81,38 @@ def test_kmeans_step_vs_oracle(B, D, K):
     assert_close(sums.cpu(), want, "sums", tol=1e-5)
 
 
+@pytest.mark.parametrize("B,K", [(4096, 256), (100003, 256), (50000, 77)])
+def test_kmeans_tensor_core_assignment(B, K):
+    """impl=TCGEN05 (the fused quantiser's distance kernel with L = 1) against the exact SIMT k-means kernel:
+    assignments may differ only at fp32-rounding ties; sums / counts / n_changed follow the assignment."""
+    D = 32
+    g = torch.Generator().manual_seed(B + K)
+    x = (torch.randn(B, D, generator=g) + 2.0 * torch.randn(8, D, generator=g)[torch.randint(0, 8, (B,), generator=g)]).to(DEV)
+    c = x[torch.randperm(B, generator=g)[:K].to(DEV)].clone()
+    a_s, sums_s, counts_s, _ = RF.kmeans_assign_accumulate(x, c, impl=RF.IMPL_SIMT)
+    a_t, sums_t, counts_t, nch = RF.kmeans_assign_accumulate(x, c, impl=RF.IMPL_TCGEN05)
+    assert int(nch) == B
+    mism = a_s != a_t
+    assert float(mism.float().mean()) < 1e-4
+    if bool(mism.any()):                       # a differing row must be a genuine near-tie
+        xm = x[mism].double()
+        d = ((xm[:, None, :] - c.double()[None]) ** 2).sum(-1)
+        ds, dt = d.gather(1, a_s[mism][:, None]), d.gather(1, a_t[mism][:, None])
+        assert bool(((dt - ds).abs() <= 1e-5 * (xm ** 2).sum(1, keepdim=True).clamp_min(1.0)).all())
+    assert int(counts_t.sum()) == B
+    want = torch.zeros(K, D, dtype=torch.float64, device=DEV).index_add_(0, a_t, x.double())
+    assert_close(sums_t.cpu(), want.cpu(), "sums", tol=1e-5)
+    assert torch.equal(counts_t, torch.bincount(a_t, minlength=K))
+    # second pass from the stored assignment: nothing changes; perturbing a few entries is counted exactly
+    a2 = a_t.clone()
+    _, _, _, n0 = RF.kmeans_assign_accumulate(x, c, a2, impl=RF.IMPL_TCGEN05)
+    assert int(n0) == 0
+    a3 = a_t.clone()
+    a3[:5] = (a3[:5] + 1) % K
+    _, _, _, n5 = RF.kmeans_assign_accumulate(x, c, a3, impl=RF.IMPL_TCGEN05)
+    assert int(n5) == 5 and torch.equal(a3, a_t)
+
+
 def test_tokenizer_golden_end_to_end():
     z = load_golden("tokenizer_small.npz")
     sd = {k[4:]: torch.from_numpy(z[k]) for k in z.keys() if k.startswith("sd::")}
