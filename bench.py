@@ -230,13 +230,28 @@ def run_engine(args):
     cbs = cbs_h.to(dev)
     mode = RF.MODE_ROTATION_TRICK
 
-    def step(i):
-        s = i % N_SLOTS
+    def step_compute(s):
         emb, res, ids, loss = RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP)
         g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP)
-        if world > 1:
-            dist.all_reduce(g_cb)            # codebook-gradient all-reduce (98,304 B), the path's one exchange
         return loss, g_x, g_cb
+
+    # N > 1: the codebook-gradient all-reduce (98,304 B, the path's one exchange) runs on its own stream so
+    # that step i's reduction overlaps step i+1's kernels (each ring slot has its own gradient buffer) — what
+    # DDP's bucketed all-reduce does for the reference (train_rqvae.py:115-117,153).
+    comm_stream = torch.cuda.Stream() if world > 1 else None
+
+    def allreduce_async(g_cb):
+        ev = torch.cuda.Event()
+        ev.record()
+        comm_stream.wait_event(ev)
+        with torch.cuda.stream(comm_stream):
+            dist.all_reduce(g_cb)
+
+    def step(i):
+        out = step_compute(i % N_SLOTS)
+        if world > 1:
+            allreduce_async(out[2])
+        return out
 
     def fence():
         if world > 1:
@@ -268,12 +283,15 @@ def run_engine(args):
     try:
         if not use_graphs:
             raise RuntimeError("eager requested")
-        step_graphs, _keep1, launches_per_step = capture(step)
+        step_graphs, _keep1, launches_per_step = capture(step_compute)
         fwd_graphs, _keep2, _ = capture(lambda s: RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP))
         _fwd_out = [RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP) for s in range(N_SLOTS)]
         bwd_graphs, _keep3, _ = capture(lambda s: RF.quantize_backward(g_embs[s], None, g_loss, _fwd_out[s][1],
                                                                        _fwd_out[s][2], cbs, mode, BETA, TEMP))
-        run_step = lambda i: step_graphs[i % N_SLOTS].replay()
+        def run_step(i):
+            step_graphs[i % N_SLOTS].replay()
+            if world > 1:
+                allreduce_async(_keep1[i % N_SLOTS][2])
         run_fwd = lambda i: fwd_graphs[i % N_SLOTS].replay()
         run_bwd = lambda i: bwd_graphs[i % N_SLOTS].replay()
         launch_mode = "cuda-graph replay (one graph per ring slot)"
@@ -294,6 +312,8 @@ def run_engine(args):
         a.record()
         for i in range(n):
             fn(args.warmup + i)
+        if comm_stream is not None:
+            torch.cuda.current_stream().wait_stream(comm_stream)   # the last reductions are part of the K steps
         b.record()
         return a, b
 
@@ -405,8 +425,14 @@ def run_engine(args):
                                              f"(torch CPU ATen fp32, {cores} threads)"}
         print(json.dumps(out))
     if world > 1:
+        # Captured NCCL all-reduces live inside the step graphs; tearing the communicator down under them
+        # was seen to hang (2 ranks, NCCL 2.28.9).  Everything is measured and printed by now: drop the
+        # graphs, meet at a barrier and leave without the destructor dance.
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
