@@ -220,6 +220,8 @@ def run_engine(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"          # NCCL prints its version banner on stdout otherwise
         dist.init_process_group("nccl", device_id=dev)
     R.lib()
 

@@ -81,17 +81,27 @@ class SemanticIdTokenizer(nn.Module):
 
     @torch.no_grad()
     @eval_mode
-    def precompute_corpus_ids(self, movie_dataset) -> Tensor:
+    def precompute_corpus_ids(self, movie_dataset, group=None) -> Tensor:
         """`movie_dataset[list_of_idx]` must return a SeqBatch whose `.x` is [n, input_dim]
-        (data/processed.py:74-84 of the reference)."""
+        (data/processed.py:74-84 of the reference).
+
+        With torch.distributed initialised (world size G > 1) every rank tokenises only its contiguous
+        row shard (N/G items; no data-path collective), the [N/G, L] ids are all-gathered once, and each
+        rank builds the identical [N, L+1] table — the dedup column needs the global corpus order."""
+        from ... import parallel
         n = len(movie_dataset)
         device = self.rq_vae.device
+        lo, hi = 0, n
+        if parallel.is_distributed(group):
+            import torch.distributed as dist
+            lo, hi = parallel.shard_range(n, dist.get_rank(group), dist.get_world_size(group))
         chunks = []
-        for s in range(0, n, self.corpus_batch_size):
-            idx = list(range(s, min(n, s + self.corpus_batch_size)))
+        for s in range(lo, hi, self.corpus_batch_size):
+            idx = list(range(s, min(hi, s + self.corpus_batch_size)))
             batch = batch_to(movie_dataset[idx], device)
             chunks.append(self.semantic_ids(batch.x))
         ids = torch.cat(chunks, dim=0) if chunks else torch.zeros((0, self.n_layers), dtype=torch.int64, device=device)
+        ids = parallel.gather_row_shards(ids.contiguous(), n, group)
         self.cached_ids = RF.corpus_table(ids, self.codebook_size)
         self._prefix_index = {}
         return self.cached_ids

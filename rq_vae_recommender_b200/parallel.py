@@ -30,3 +30,31 @@ def allreduce_codebook_grads(model, group=None, average: bool = True) -> None:
     for g in grads:
         g.copy_(flat[o:o + g.numel()].view_as(g))
         o += g.numel()
+
+
+def is_distributed(group=None) -> bool:
+    import torch.distributed as dist
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+
+
+def gather_row_shards(local: torch.Tensor, n: int, group=None) -> torch.Tensor:
+    """All-gather of contiguous row shards laid out by `shard_range`: every rank passes its [n_local, ...]
+    block and receives the full [n, ...] tensor.  Shards differ by at most one row, so they are padded to
+    ceil(n / world) rows for one equal-size all_gather and the padding is dropped afterwards.  The only
+    collective of corpus tokenisation: [N/G, L] ids in, [N, L] out."""
+    import torch.distributed as dist
+    if not is_distributed(group):
+        return local
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    lo, hi = shard_range(n, rank, world)
+    assert local.shape[0] == hi - lo, f"rank {rank} holds {local.shape[0]} rows, its shard has {hi - lo}"
+    per = (n + world - 1) // world
+    pad = torch.zeros((per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    pad[:hi - lo] = local
+    out = torch.empty((world * per,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, pad.contiguous(), group=group)
+    parts = []
+    for r in range(world):
+        a, b = shard_range(n, r, world)
+        parts.append(out[r * per:r * per + (b - a)])
+    return torch.cat(parts, dim=0)

@@ -96,7 +96,12 @@ def _gloo_worker(rank, world, port, q):
         rows = km._global_rows(x, [0, 5, 10, 6], off)
         np.random.seed(123 + rank)               # ranks disagree on purpose: rank 0's draw must win
         km._init_centroids(x)
-        q.put((rank, off, n, torch.equal(rows, full[[0, 5, 10, 6]]), km.centroids.clone()))
+        # corpus tokenisation's one collective: [N/G, L] id shards -> the full [N, L] table on every rank
+        from rq_vae_recommender_b200.parallel import gather_row_shards
+        ids_full = torch.arange(11 * 3, dtype=torch.int64).reshape(11, 3)
+        gathered = gather_row_shards(ids_full[lo:hi].contiguous(), 11)
+        q.put((rank, off, n, torch.equal(rows, full[[0, 5, 10, 6]]), km.centroids.clone(),
+               torch.equal(gathered, ids_full)))
     finally:
         dist.destroy_process_group()
 
@@ -113,3 +118,4 @@ def test_kmeans_sharding_helpers_gloo_world2():
     assert res[0][1] == 0 and res[1][1] == 6 and res[0][2] == res[1][2] == 11
     assert res[0][3] and res[1][3]
     assert torch.equal(res[0][4], res[1][4])     # identical initial centroids on both ranks
+    assert res[0][5] and res[1][5]               # row-shard all-gather reassembles the global order

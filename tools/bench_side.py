@@ -1,0 +1,83 @@
+"""Side numbers for the other BASELINE configs (single GPU, CUDA events, inputs resident in HBM):
+ C4-like  ids-only tokenisation throughput on a 4M-item latent chunk (d=32 tcgen05 family; d=64 SIMT family)
+ C3-like  one k-means level-iteration (assign + accumulate + update) over 10M x 32 latents, K = 256
+ C5-like  Gumbel-softmax / rotation-trick forward+backward at 4 x 1024, d = 64 (SIMT family)
+Prints one JSON object; `python tools/bench_side.py > profiles/r1_side_numbers.json` on a B200."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+import rq_vae_recommender_b200 as R
+from rq_vae_recommender_b200 import functional as RF
+
+dev = torch.device("cuda:0")
+HBM = 6551.0
+if os.path.exists("MEASURED_PEAKS.json"):
+    HBM = float(json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"])
+
+
+def timed(fn, iters, warm=2):
+    for _ in range(warm):
+        fn()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+
+def codebooks(L, K, D, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return torch.stack([torch.randn(K, D, generator=g) * (0.6 ** l) for l in range(L)]).to(dev)
+
+
+out = {}
+# ---- C4-like: ids-only over a resident chunk -----------------------------------------------------------
+for D, n in ((32, 4 << 20), (64, 1 << 20)):
+    x = torch.randn(n, D, device=dev)
+    cb = codebooks(3, 256, D)
+    ms = timed(lambda: RF.quantize_forward(x, cb, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
+                                           want_loss=False), 5)
+    byts = n * (4 * D + 8 * 3)
+    out[f"tokenize_ids_only_d{D}_3x256"] = {
+        "items": n, "ms": ms, "items_per_s": n / (ms * 1e-3), "algorithmic_GBps": byts / (ms * 1e-3) / 1e9,
+        "tcgen05": bool(R.lib().rq_tcgen05_supported(D, 256, 3, RF.MODE_EVAL, 1))}
+    del x
+# ---- C3-like: one k-means level-iteration ------------------------------------------------------------------
+n = 10_000_000
+x = torch.randn(n, 32, device=dev)
+c = x[torch.randperm(n, device=dev)[:256]].clone()
+assign = torch.empty(n, dtype=torch.int64, device=dev)
+RF.kmeans_assign_accumulate(x, c, assign)
+
+
+def km_iter():
+    a, sums, counts, nch = RF.kmeans_assign_accumulate(x, c, assign)
+    RF.kmeans_update(sums, counts, c)
+
+
+ms = timed(km_iter, 5)
+out["kmeans_level_iteration_10M_d32_k256"] = {
+    "points": n, "ms": ms, "points_per_s": n / (ms * 1e-3), "algorithmic_GBps": n * 128 / (ms * 1e-3) / 1e9,
+    "frac_of_hbm_roofline": (n * 128 / (ms * 1e-3) / 1e9) / HBM}
+ms_simt = timed(lambda: RF.kmeans_assign_accumulate(x, c, assign, impl=RF.IMPL_SIMT), 2, warm=1)
+out["kmeans_level_iteration_10M_d32_k256"]["simt_family_ms"] = ms_simt
+del x, assign
+# ---- C5-like: 4 x 1024, d = 64 training step (SIMT family) ---------------------------------------------------
+B, D, K, L = 16384, 64, 1024, 4
+x = torch.randn(B, D, device=dev)
+cb = codebooks(L, K, D)
+g_emb = torch.randn(L, B, D, device=dev) * 0.01
+g_loss = torch.full((B,), 1.0 / B, device=dev)
+for name, mode in (("rotation", RF.MODE_ROTATION_TRICK), ("gumbel", RF.MODE_GUMBEL_SOFTMAX)):
+    def step():
+        emb, res, ids, loss = RF.quantize_forward(x, cb, mode, 0.25, 0.2, seed=1, offset=2)
+        RF.quantize_backward(g_emb, None, g_loss, res, ids, cb, mode, 0.25, 0.2, seed=1, offset=2)
+    ms = timed(step, 3, warm=1)
+    out[f"train_step_{name}_4x1024_d64"] = {"items": B, "ms": ms, "items_per_s": B / (ms * 1e-3)}
+print(json.dumps(out, indent=1))
