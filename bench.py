@@ -348,13 +348,17 @@ def run_engine(args):
     loss_pin = torch.empty(B_PER_GPU, dtype=torch.float32).pin_memory()
     ids_pin = torch.empty((L, B_PER_GPU), dtype=torch.int64).pin_memory()
 
+    # batches arrive through the package's DevicePrefetcher (data/utils.py): the H2D copy of step i+1
+    # runs on its own stream while step i is quantised; both are inside the timed region.
+    feed = R.data.utils.DevicePrefetcher(R.data.utils.cycle(xs_pin), dev)
+    g_embs_bdl = [g.permute(1, 2, 0) for g in g_embs]                           # views, [B,D,L] like the output
+
     def e2e_step(i):
         s = i % N_SLOTS
-        lat = xs_pin[s].to(dev, non_blocking=True).requires_grad_(True)         # H2D, 8 MiB
+        lat = next(feed).requires_grad_(True)                                   # H2D, 8 MiB (prefetched)
         out = model.quantize_latents(lat, TEMP)
-        obj = (out.embeddings.permute(2, 0, 1) * g_embs[s]).sum() + (out.quantize_loss * g_loss).sum()
         model.zero_grad(set_to_none=True)
-        obj.backward()
+        torch.autograd.backward([out.embeddings, out.quantize_loss], [g_embs_bdl[s], g_loss])
         if world > 1:
             R.parallel.allreduce_codebook_grads(model)
         loss_pin.copy_(out.quantize_loss.detach(), non_blocking=True)           # D2H

@@ -156,8 +156,10 @@ int rq_gather_tokens(const int64_t* table, int64_t n_rows, int W, const int64_t*
 /*
  * Host-buffer convenience entry (the call a non-torch integrator makes): copies `x_host`
  * (pageable or pinned) to the device, runs rq_quantize_forward in RQ_MODE_EVAL, copies the ids
- * (and loss when non-NULL) back and synchronises `stream`.  Device scratch comes from the
- * stream-ordered allocator (cudaMallocAsync).  `codebooks` is a DEVICE pointer.
+ * [L,B] (and loss [B] when non-NULL) back and returns when they are complete.  Rows are processed
+ * in chunks (262,144 rows; env RQ_HOST_CHUNK_ROWS) as a three-stage pipeline -- H2D of chunk i+1,
+ * compute of chunk i on `stream`, D2H of chunk i-1 -- so device scratch is two chunk-sized buffer
+ * pairs from the stream-ordered allocator whatever B is.  `codebooks` is a DEVICE pointer.
  */
 int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B, int D, int K, int L,
                          int distance, int64_t* ids_host, float* loss_host, int impl,

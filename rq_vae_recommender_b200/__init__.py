@@ -12,5 +12,7 @@ from .modules.quantize import (GumbelNoise, Quantize, QuantizeDistance, Quantize
 from .modules.rqvae import RqVae, RqVaeComputedLosses, RqVaeOutput  # noqa: F401
 from .modules.tokenizer.semids import SemanticIdTokenizer  # noqa: F401
 from .data.schemas import SeqBatch, TokenizedSeqBatch, batch_to  # noqa: F401
+from .data import utils as _data_utils  # noqa: F401  (rq.data.utils.DevicePrefetcher)
+from . import data  # noqa: F401
 
 __version__ = "0.1.0"

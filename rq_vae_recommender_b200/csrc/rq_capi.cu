@@ -1,6 +1,8 @@
 // extern "C" entry points of librqengine.so (see include/rq_engine.h for the contract).
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
+#include <initializer_list>
 
 #include "rq_common.cuh"
 #include "rq_kernels.h"
@@ -126,6 +128,16 @@ extern "C" int rq_kmeans_update(const float* sums, const int64_t* counts, float*
     return kmeans_update(sums, counts, centroids, D, K, max_shift, n_empty, empty_ids, (cudaStream_t)stream);
 }
 
+// Host-buffer tokenisation as a three-stage pipeline over row chunks: H2D of chunk i+1, the fused
+// forward of chunk i and the D2H of chunk i-1 run on three streams (PCIe is full duplex), device
+// memory is two chunk-sized buffer pairs regardless of B.  `stream` carries the compute stage and
+// orders the call after the caller's earlier work; the call returns when ids_host is complete.
+static int64_t host_chunk_rows() {
+    const char* e = getenv("RQ_HOST_CHUNK_ROWS");
+    const int64_t rows = e ? atoll(e) : 0;
+    return rows > 0 ? rows : 262144;
+}
+
 extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B, int D, int K, int L,
                                     int distance, int64_t* ids_host, float* loss_host, int impl,
                                     rq_stream_t stream) {
@@ -133,25 +145,80 @@ extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks,
     RQ_CHECK_ARG(B >= 0, RQ_ERR_INVALID_ARGUMENT, "rq_semantic_ids_host: B < 0");
     if (B == 0) return 0;
     RQ_CHECK_ARG(x_host && codebooks && ids_host, RQ_ERR_NULL_POINTER, "rq_semantic_ids_host: null pointer");
-    float* dx = nullptr;
-    int64_t* dids = nullptr;
-    float* dloss = nullptr;
-    RQ_CUDA(cudaMallocAsync((void**)&dx, (size_t)B * D * sizeof(float), st));
-    RQ_CUDA(cudaMallocAsync((void**)&dids, (size_t)L * B * sizeof(int64_t), st));
-    if (loss_host) RQ_CUDA(cudaMallocAsync((void**)&dloss, (size_t)B * sizeof(float), st));
-    RQ_CUDA(cudaMemcpyAsync(dx, x_host, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, st));
-    int rc = rq_quantize_forward(dx, codebooks, B, D, K, L, RQ_MODE_EVAL, distance, 0.25f, 1.0f, nullptr, 0, 0,
-                                 nullptr, nullptr, dids, dloss, impl, stream);
-    if (rc == 0) {
-        cudaError_t e = cudaMemcpyAsync(ids_host, dids, (size_t)L * B * sizeof(int64_t), cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess && loss_host)
-            e = cudaMemcpyAsync(loss_host, dloss, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st);
-        if (e != cudaSuccess) { set_error("rq_semantic_ids_host: D2H copy failed: %s", cudaGetErrorString(e)); rc = (int)e; }
+    RQ_CHECK_ARG(L >= 1 && D >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_semantic_ids_host: need L >= 1, D >= 1");
+    const int64_t chunk = host_chunk_rows();
+    const int64_t C = B < chunk ? B : chunk;
+    const int64_t n_chunks = (B + C - 1) / C;
+    const int NB = n_chunks > 1 ? 2 : 1;
+    float* dx[2] = {nullptr, nullptr};
+    int64_t* dids[2] = {nullptr, nullptr};
+    float* dloss[2] = {nullptr, nullptr};
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[2] = {}, ev_comp[2] = {}, ev_out[2] = {}, ev_start = nullptr;
+    int rc = 0;
+    cudaError_t e = cudaSuccess;
+#define HOST_TRY(call)                                                                        \
+    do { if (rc == 0 && e == cudaSuccess) { e = (call); } } while (0)
+    HOST_TRY(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+    HOST_TRY(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+    HOST_TRY(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
+    for (int b = 0; b < NB; ++b) {
+        HOST_TRY(cudaEventCreateWithFlags(&ev_in[b], cudaEventDisableTiming));
+        HOST_TRY(cudaEventCreateWithFlags(&ev_comp[b], cudaEventDisableTiming));
+        HOST_TRY(cudaEventCreateWithFlags(&ev_out[b], cudaEventDisableTiming));
+        HOST_TRY(cudaMallocAsync((void**)&dx[b], (size_t)C * D * sizeof(float), st));
+        HOST_TRY(cudaMallocAsync((void**)&dids[b], (size_t)L * C * sizeof(int64_t), st));
+        if (loss_host) HOST_TRY(cudaMallocAsync((void**)&dloss[b], (size_t)C * sizeof(float), st));
     }
-    cudaFreeAsync(dx, st);
-    cudaFreeAsync(dids, st);
-    if (dloss) cudaFreeAsync(dloss, st);
-    cudaError_t e = cudaStreamSynchronize(st);
-    if (rc == 0 && e != cudaSuccess) { set_error("rq_semantic_ids_host: %s", cudaGetErrorString(e)); rc = (int)e; }
-    return rc;
+    // the side streams start after the allocations (and whatever the caller queued before us)
+    HOST_TRY(cudaEventRecord(ev_start, st));
+    HOST_TRY(cudaStreamWaitEvent(s_in, ev_start, 0));
+    HOST_TRY(cudaStreamWaitEvent(s_out, ev_start, 0));
+    for (int64_t i = 0; i < n_chunks && rc == 0 && e == cudaSuccess; ++i) {
+        const int b = (int)(i & 1);
+        const int64_t lo = i * C, n = (B - lo) < C ? (B - lo) : C;
+        if (i >= 2) HOST_TRY(cudaStreamWaitEvent(s_in, ev_comp[b], 0));     // x buffer b consumed
+        HOST_TRY(cudaMemcpyAsync(dx[b], x_host + (size_t)lo * D, (size_t)n * D * sizeof(float),
+                                 cudaMemcpyHostToDevice, s_in));
+        HOST_TRY(cudaEventRecord(ev_in[b], s_in));
+        HOST_TRY(cudaStreamWaitEvent(st, ev_in[b], 0));
+        if (i >= 2) HOST_TRY(cudaStreamWaitEvent(st, ev_out[b], 0));        // ids buffer b drained
+        if (rc == 0 && e == cudaSuccess)
+            rc = rq_quantize_forward(dx[b], codebooks, n, D, K, L, RQ_MODE_EVAL, distance, 0.25f, 1.0f, nullptr, 0,
+                                     0, nullptr, nullptr, dids[b], dloss[b], impl, stream);
+        HOST_TRY(cudaEventRecord(ev_comp[b], st));
+        HOST_TRY(cudaStreamWaitEvent(s_out, ev_comp[b], 0));
+        // device ids are [L, n] for this chunk; the host table is [L, B]
+        HOST_TRY(cudaMemcpy2DAsync(ids_host + lo, (size_t)B * sizeof(int64_t), dids[b], (size_t)n * sizeof(int64_t),
+                                   (size_t)n * sizeof(int64_t), (size_t)L, cudaMemcpyDeviceToHost, s_out));
+        if (loss_host)
+            HOST_TRY(cudaMemcpyAsync(loss_host + lo, dloss[b], (size_t)n * sizeof(float), cudaMemcpyDeviceToHost,
+                                     s_out));
+        HOST_TRY(cudaEventRecord(ev_out[b], s_out));
+    }
+#undef HOST_TRY
+    // drain every stage before the buffers go back to the pool, whatever happened above
+    cudaError_t e1 = s_in ? cudaStreamSynchronize(s_in) : cudaSuccess;
+    cudaError_t e2 = s_out ? cudaStreamSynchronize(s_out) : cudaSuccess;
+    for (int b = 0; b < NB; ++b) {
+        if (dx[b]) cudaFreeAsync(dx[b], st);
+        if (dids[b]) cudaFreeAsync(dids[b], st);
+        if (dloss[b]) cudaFreeAsync(dloss[b], st);
+    }
+    cudaError_t e3 = cudaStreamSynchronize(st);
+    for (int b = 0; b < NB; ++b) {
+        if (ev_in[b]) cudaEventDestroy(ev_in[b]);
+        if (ev_comp[b]) cudaEventDestroy(ev_comp[b]);
+        if (ev_out[b]) cudaEventDestroy(ev_out[b]);
+    }
+    if (ev_start) cudaEventDestroy(ev_start);
+    if (s_in) cudaStreamDestroy(s_in);
+    if (s_out) cudaStreamDestroy(s_out);
+    if (rc != 0) return rc;
+    for (cudaError_t x : {e, e1, e2, e3})
+        if (x != cudaSuccess) {
+            set_error("rq_semantic_ids_host: %s", cudaGetErrorString(x));
+            return (int)x;
+        }
+    return 0;
 }

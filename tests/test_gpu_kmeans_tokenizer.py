@@ -187,3 +187,37 @@ def test_c_abi_host_entry_point():
     assert (torch.from_numpy(ids) == ref.sem_ids).float().mean() > 0.999
     ok = (torch.from_numpy(ids) == ref.sem_ids).all(0)
     assert_close(torch.from_numpy(loss)[ok], ref.quantize_loss[ok], "loss")
+
+
+def test_c_abi_host_entry_point_chunked_pipeline(monkeypatch):
+    """The host entry pipelines row chunks over three streams; a ragged chunking (7 chunks, short
+    tail, pinned and pageable sources) must give exactly the ids and loss of the one-shot device call."""
+    from rq_vae_recommender_b200 import _lib
+    B, D, K, L = 6500, 32, 256, 3
+    g = torch.Generator().manual_seed(15)
+    x = torch.randn(B, D, generator=g)
+    cb_dev = torch.randn(L, K, D, generator=g).to(DEV)
+    _, _, ids_ref, loss_ref = RF.quantize_forward(x.to(DEV), cb_dev, RF.MODE_EVAL)
+    monkeypatch.setenv("RQ_HOST_CHUNK_ROWS", "1000")
+    for src in (x, x.pin_memory()):
+        ids = torch.full((L, B), -1, dtype=torch.int64).pin_memory()
+        loss = torch.full((B,), -1.0).pin_memory()
+        rc = _lib.lib().rq_semantic_ids_host(src.data_ptr(), cb_dev.data_ptr(), B, D, K, L, 1, ids.data_ptr(),
+                                             loss.data_ptr(), 0, None)
+        _lib.check(rc)
+        assert torch.equal(ids, ids_ref.cpu())
+        assert torch.equal(loss, loss_ref.cpu())
+
+
+def test_device_prefetcher_orders_and_completes():
+    """DevicePrefetcher (data/utils.py) returns the batches in order, complete when the consumer
+    stream reads them, and stops with the source."""
+    from rq_vae_recommender_b200.data import utils as U
+    host = [torch.full((1 << 20,), float(i)).pin_memory() for i in range(5)]
+    got = []
+    for t in U.DevicePrefetcher(host, DEV, depth=2):
+        assert t.is_cuda
+        got.append(float(t.sum().item()) / (1 << 20))
+    assert got == [0.0, 1.0, 2.0, 3.0, 4.0]
+    it = U.DevicePrefetcher(U.cycle(host[:2]), DEV)
+    assert [int(next(it)[0].item()) for _ in range(5)] == [0, 1, 0, 1, 0]

@@ -119,3 +119,21 @@ def test_kmeans_sharding_helpers_gloo_world2():
     assert res[0][3] and res[1][3]
     assert torch.equal(res[0][4], res[1][4])     # identical initial centroids on both ranks
     assert res[0][5] and res[1][5]               # row-shard all-gather reassembles the global order
+
+
+def test_data_utils_batch_to_and_cycle():
+    """data/utils.py:4-17 of the reference: cycle restarts the loader, batch_to keeps the batch type."""
+    from rq_vae_recommender_b200.data import utils as U
+    from rq_vae_recommender_b200.data.schemas import SeqBatch
+    it = U.cycle([1, 2, 3])
+    assert [next(it) for _ in range(7)] == [1, 2, 3, 1, 2, 3, 1]
+    b = SeqBatch(*[torch.arange(4) + i for i in range(len(SeqBatch._fields))])
+    out = U.batch_to(b, "cpu")
+    assert type(out) is SeqBatch and all(torch.equal(a, c) for a, c in zip(out, b))
+    assert torch.equal(U.batch_to(torch.ones(3), "cpu"), torch.ones(3))
+    d = U.batch_to({"a": torch.zeros(2), "n": 5}, "cpu")
+    assert d["n"] == 5 and torch.equal(d["a"], torch.zeros(2))
+    with pytest.raises(TypeError):
+        U.batch_to(3.5, "cpu")
+    with pytest.raises(RuntimeError):
+        U.DevicePrefetcher([torch.ones(1)], "cpu")

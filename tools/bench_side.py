@@ -48,6 +48,29 @@ for D, n in ((32, 4 << 20), (64, 1 << 20)):
         "items": n, "ms": ms, "items_per_s": n / (ms * 1e-3), "algorithmic_GBps": byts / (ms * 1e-3) / 1e9,
         "tcgen05": bool(R.lib().rq_tcgen05_supported(D, 256, 3, RF.MODE_EVAL, 1))}
     del x
+# ---- C4-like, host buffers: pinned latents -> ids through the C-ABI host entry (chunked 3-stream pipeline) ----
+import time
+n = 4 << 20
+xh = torch.randn(n, 32).pin_memory()
+cb = codebooks(3, 256, 32)
+idh = torch.empty((3, n), dtype=torch.int64).pin_memory()
+
+
+def host_call():
+    rc = R.lib().rq_semantic_ids_host(xh.data_ptr(), cb.data_ptr(), n, 32, 256, 3, 1, idh.data_ptr(), None, 0, None)
+    assert rc == 0
+
+
+host_call()
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for _ in range(3):
+    host_call()
+dt = (time.perf_counter() - t0) / 3
+out["tokenize_host_buffers_d32_3x256"] = {
+    "items": n, "ms": dt * 1e3, "items_per_s": n / dt, "h2d_GBps": n * 128 / dt / 1e9, "d2h_GBps": n * 24 / dt / 1e9,
+    "note": "wall clock around rq_semantic_ids_host, pinned host buffers, copies inside"}
+del xh, idh
 # ---- C3-like: one k-means level-iteration ------------------------------------------------------------------
 n = 10_000_000
 x = torch.randn(n, 32, device=dev)
