@@ -61,8 +61,14 @@ int kmeans_assign_accumulate_tc(const KmeansParams& p, int D, cudaStream_t st);
 int kmeans_update(const float* sums, const int64_t* counts, float* centroids, int D, int K, float* max_shift,
                   int64_t* n_empty, int64_t* empty_ids, cudaStream_t st);
 
-// tcgen05 family (rq_quantize_tc.cu)
+// tcgen05 family: D = 32 in rq_quantize_tc.cu (bf16 x3 split), D = 64 in rq_quantize_tc64.cu (scaled fp16).
+// tc_supported / quantize_forward_tc route by D.
 bool tc_supported(int D, int K, int L, int mode, int distance);
 int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st);
+bool tc32_supported(int D, int K, int L, int mode, int distance);
+int quantize_forward_tc32(const FwdParams& p, cudaStream_t st);
+bool tc64_supported(int D, int K, int L, int mode, int distance);
+int quantize_forward_tc64(const FwdParams& p, cudaStream_t st);
+int tc64_timeout_flag();
 
 }  // namespace rq

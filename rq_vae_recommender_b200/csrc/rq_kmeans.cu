@@ -134,6 +134,7 @@ int kmeans_assign_accumulate_tc(const KmeansParams& p, int D, cudaStream_t st) {
     const int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
     if (D == 32) rq_kmeans_accumulate_kernel<32><<<(unsigned)blocks, 256, 0, st>>>(p.x, p.assign, p.B, p.sums, p.counts);
+    else if (D == 64) rq_kmeans_accumulate_kernel<64><<<(unsigned)blocks, 256, 0, st>>>(p.x, p.assign, p.B, p.sums, p.counts);
     else { set_error("kmeans tensor-core path: D=%d not served", D); return RQ_ERR_UNSUPPORTED_SHAPE; }
     RQ_LAUNCHED();
     return 0;

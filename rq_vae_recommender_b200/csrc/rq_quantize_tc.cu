@@ -613,7 +613,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     if (warp == 1) ptx::tmem_dealloc(tmem_base, 512);
 }
 
-bool tc_supported(int D, int K, int L, int mode, int distance) {
+bool tc32_supported(int D, int K, int L, int mode, int distance) {
     if (getenv("RQ_DISABLE_TCGEN05")) return false;
     return D == tc::D && K >= 1 && K <= tc::KC && L >= 1 && L <= tc::MAX_L && distance == RQ_DIST_L2 &&
            (mode == RQ_MODE_EVAL || mode == RQ_MODE_STE || mode == RQ_MODE_ROTATION_TRICK);
@@ -638,8 +638,14 @@ static int launch_tc(const TcParams& P, cudaStream_t st) {
     return 0;
 }
 
+bool tc_supported(int D, int K, int L, int mode, int distance) {
+    return tc32_supported(D, K, L, mode, distance) || tc64_supported(D, K, L, mode, distance);
+}
 int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st) {
-    (void)D;
+    return D == 64 ? quantize_forward_tc64(p, st) : quantize_forward_tc32(p, st);
+}
+
+int quantize_forward_tc32(const FwdParams& p, cudaStream_t st) {
     if (p.B == 0) return 0;
     if (!d_err) {
         RQ_CUDA(cudaMalloc((void**)&d_err, sizeof(int)));
@@ -663,7 +669,7 @@ int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st) {
 extern "C" int rq_debug_tc_timeout_flag(void) {
     int v = 0;
     if (rq::d_err) cudaMemcpy(&v, rq::d_err, sizeof(int), cudaMemcpyDeviceToHost);
-    return v;
+    return v | rq::tc64_timeout_flag();
 }
 extern "C" int rq_debug_tc_set_accumulator_dump(float* device_buf_128x256) {
     rq::g_dbg_acc = device_buf_128x256;

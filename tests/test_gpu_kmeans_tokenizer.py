@@ -81,11 +81,10 @@ def test_kmeans_step_vs_oracle(B, D, K):
     assert_close(sums.cpu(), want, "sums", tol=1e-5)
 
 
-@pytest.mark.parametrize("B,K", [(4096, 256), (100003, 256), (50000, 77)])
-def test_kmeans_tensor_core_assignment(B, K):
+@pytest.mark.parametrize("B,K,D", [(4096, 256, 32), (100003, 256, 32), (50000, 77, 32), (60001, 256, 64), (9000, 100, 64)])
+def test_kmeans_tensor_core_assignment(B, K, D):
     """impl=TCGEN05 (the fused quantiser's distance kernel with L = 1) against the exact SIMT k-means kernel:
     assignments may differ only at fp32-rounding ties; sums / counts / n_changed follow the assignment."""
-    D = 32
     g = torch.Generator().manual_seed(B + K)
     x = (torch.randn(B, D, generator=g) + 2.0 * torch.randn(8, D, generator=g)[torch.randint(0, 8, (B,), generator=g)]).to(DEV)
     c = x[torch.randperm(B, generator=g)[:K].to(DEV)].clone()

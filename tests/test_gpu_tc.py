@@ -12,16 +12,18 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _inputs(B, K, L, seed, scale=1.0):
+def _inputs(B, K, L, seed, scale=1.0, D=32):
     g = torch.Generator().manual_seed(seed)
-    x = torch.randn(B, 32, generator=g) * scale
-    cbs = synthetic_codebooks(torch.randn(max(4 * K, 2048), 32, generator=g) * scale, L, K, seed=seed + 1)
+    x = torch.randn(B, D, generator=g) * scale
+    cbs = synthetic_codebooks(torch.randn(max(4 * K, 2048), D, generator=g) * scale, L, K, seed=seed + 1)
     return x, cbs
 
 
 def test_tc_is_selected_for_the_headline_shape():
     assert _lib.lib().rq_tcgen05_supported(32, 256, 3, RF.MODE_ROTATION_TRICK, RF.DIST_L2) == 1
-    assert _lib.lib().rq_tcgen05_supported(64, 256, 3, RF.MODE_EVAL, RF.DIST_L2) in (0, 1)
+    assert _lib.lib().rq_tcgen05_supported(64, 256, 3, RF.MODE_EVAL, RF.DIST_L2) == 1      # ml32m shape
+    assert _lib.lib().rq_tcgen05_supported(64, 256, 4, RF.MODE_EVAL, RF.DIST_L2) == 0      # operand tiles do not fit
+    assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_ROTATION_TRICK, RF.DIST_L2) == 0
     assert _lib.lib().rq_tcgen05_supported(32, 256, 3, RF.MODE_EVAL, RF.DIST_COSINE) == 0
 
 
@@ -90,3 +92,70 @@ def test_tc_vs_oracle_scales_and_near_ties(scale):
     assert_close(loss.cpu()[ok], ref.quantize_loss[ok], "loss")
     _, _, ids_s, _ = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), RF.MODE_EVAL, impl=RF.IMPL_SIMT)
     assert torch.equal(ids, ids_s)
+
+
+# ---- D = 64 (ml32m shape): scaled-fp16 operands, rq_quantize_tc64.cu ------------------------------------------
+@pytest.mark.parametrize("B,K,L", [(128, 256, 1), (1, 256, 3), (300, 256, 3), (4097, 200, 2), (40000, 256, 3),
+                                    (1000, 16, 3), (19073, 255, 1)])
+def test_tc64_ids_bit_identical_to_simt(B, K, L):
+    x, cbs = _inputs(B, K, L, seed=B % 1000 + K + 64, D=64)
+    xd, cd = x.to(DEV), torch.stack(cbs).to(DEV)
+    for mode in (RF.MODE_EVAL, RF.MODE_ROTATION_TRICK, RF.MODE_STE):
+        e1, r1, i1, l1 = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_SIMT)
+        e2, r2, i2, l2 = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_TCGEN05)
+        torch.cuda.synchronize()
+        assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+        n_bad = int((i1 != i2).sum())
+        assert n_bad == 0, f"mode {mode}: {n_bad} ids differ between tcgen05 (d=64) and SIMT families"
+        assert_close(e2, e1, "emb", tol=1e-6)
+        assert_close(r2, r1, "res", tol=1e-6)
+        assert_close(l2, l1, "loss", tol=1e-6)
+    _, _, i3, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
+                                      want_loss=False, impl=RF.IMPL_TCGEN05)
+    _, _, i1, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_SIMT)
+    assert torch.equal(i1, i3)
+
+
+@pytest.mark.parametrize("scale", [1e-4, 1.0, 300.0])
+def test_tc64_vs_oracle_scales_ties_and_outliers(scale):
+    """fp16 operands carry a per-level power-of-two scale: magnitudes far from 1, exact duplicate
+    codewords, rows on a bisector, rows that dwarf the codebook (skip the tensor-core score and are
+    re-scored against all codes) and all-zero rows must all give the SIMT / oracle ids."""
+    B, K, L, D = 6000, 256, 3, 64
+    x, cbs = _inputs(B, K, L, seed=5, scale=scale, D=D)
+    cbs[0][17] = cbs[0][5]
+    g2 = torch.Generator().manual_seed(78)
+    x[:200] = 0.5 * (cbs[0][torch.arange(200) % K] + cbs[0][(torch.arange(200) + 1) % K]) \
+        + 1e-7 * scale * torch.randn(200, D, generator=g2)
+    x[200:260] = cbs[0][5] + 1e-4 * scale * torch.randn(60, D, generator=g2)
+    x[300:340] *= 3e5                                # |t r| > 2^14: the fp16 overflow guard
+    x[340:350] *= 1e-6                               # far below the codebook scale
+    x[350:360] = 0.0
+    xd, cd = x.to(DEV), torch.stack(cbs).to(DEV)
+    _, _, ids_s, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_SIMT)
+    emb, res, ids, loss = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_TCGEN05)
+    assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+    assert torch.equal(ids, ids_s)
+    assert int((ids[0] == 17).sum()) == 0
+    keep = torch.ones(B, dtype=torch.bool)
+    keep[300:340] = False                            # the oracle's own fp32 cancellation differs at 3e5x
+    ref = O.rq_forward(x[keep], cbs, O.MODE_EVAL)
+    check_ids(ids[:, keep.to(DEV)], ref, cbs, f"d64 scale {scale}")
+    ok = matching_rows(ids[:, keep.to(DEV)], ref)
+    assert_close(emb.cpu()[:, keep][:, ok], ref.embeddings[:, ok], "emb")
+    assert_close(loss.cpu()[keep][ok], ref.quantize_loss[ok], "loss")
+
+
+def test_tc64_codebook_scale_extremes():
+    """Level scales span 2^-100..2^100 in the kernel; codebooks of very different magnitude per level
+    (and an all-zero level) keep ids identical to the SIMT family."""
+    B, K, D = 3000, 256, 64
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(B, D, generator=g)
+    cbs = torch.stack([torch.randn(K, D, generator=g) * 1e3, torch.randn(K, D, generator=g) * 1e-5,
+                       torch.zeros(K, D)])
+    xd, cd = x.to(DEV), cbs.to(DEV)
+    _, _, i1, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_SIMT)
+    _, _, i2, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_TCGEN05)
+    assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+    assert torch.equal(i1, i2)

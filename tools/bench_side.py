@@ -38,7 +38,7 @@ def codebooks(L, K, D, seed=0):
 
 out = {}
 # ---- C4-like: ids-only over a resident chunk -----------------------------------------------------------
-for D, n in ((32, 4 << 20), (64, 1 << 20)):
+for D, n in ((32, 4 << 20), (64, 4 << 20)):
     x = torch.randn(n, D, device=dev)
     cb = codebooks(3, 256, D)
     ms = timed(lambda: RF.quantize_forward(x, cb, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
