@@ -117,6 +117,92 @@ __global__ void __launch_bounds__(256) rq_kmeans_accumulate_kernel(const float* 
     }
 }
 
+// Accumulation with CTA-private partial sums: K*D fp32 sums + K counts live in shared memory, rows stream
+// through in the coalesced pattern (D/4 lanes per row, one 16-byte load each) and are added with shared-memory
+// atomics; each CTA flushes its partials once with 16-byte L2 reductions.  The global-reduction kernel above sends
+// B*D*4 bytes of REDG traffic at K hot lines (39k row-adds per line at 10M x 256); here it is (#CTAs * K * D * 4).
+// Component order is rotated by lane/8 so that the 32 lanes of one atomic hit 32 different banks whatever the ids.
+template <int D>
+__global__ void __launch_bounds__(512) rq_kmeans_accumulate_smem_kernel(const float* __restrict__ x,
+                                                                        const int64_t* __restrict__ assign, int64_t B,
+                                                                        int K, float* __restrict__ sums,
+                                                                        unsigned long long* __restrict__ counts) {
+    extern __shared__ __align__(16) float s_sums[];
+    unsigned* s_cnt = reinterpret_cast<unsigned*>(s_sums + (size_t)K * D);
+    for (int i = threadIdx.x; i < K * D + K; i += blockDim.x) s_sums[i] = 0.f;       // +0.0f == 0u bitwise
+    __syncthreads();
+    constexpr int LPR = D / 4;
+    constexpr int U = 4;
+    const int64_t n_chunks = B * LPR;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int rot = (threadIdx.x >> 3) & 3;
+    for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n_chunks; i0 += U * stride) {
+        float4 v[U];
+        int k[U];
+        int sub[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t i = i0 + u * stride;
+            k[u] = -1;
+            if (i < n_chunks) {
+                const int64_t row = i / LPR;
+                sub[u] = (int)(i - row * LPR);
+                k[u] = (int)__ldg(assign + row);
+                asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                             : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w)
+                             : "l"(x + i * 4));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (k[u] < 0) continue;
+            float* dst = s_sums + (size_t)k[u] * D + sub[u] * 4;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int j = (t + rot) & 3;
+                const float val = (j == 0) ? v[u].x : (j == 1) ? v[u].y : (j == 2) ? v[u].z : v[u].w;
+                atomicAdd(dst + j, val);
+            }
+            if (sub[u] == 0) atomicAdd(s_cnt + k[u], 1u);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < K * D / 4; i += blockDim.x) {
+        const float4 t = reinterpret_cast<const float4*>(s_sums)[i];
+        if (t.x != 0.f || t.y != 0.f || t.z != 0.f || t.w != 0.f) red_add_v4(sums + 4 * i, t.x, t.y, t.z, t.w);
+    }
+    for (int kk = threadIdx.x; kk < K; kk += blockDim.x)
+        if (s_cnt[kk]) atomicAdd(counts + kk, (unsigned long long)s_cnt[kk]);
+}
+
+// sums / counts must be zeroed by the caller.  Picks the shared-memory kernel when K*D partials fit.
+template <int D>
+static int launch_kmeans_accumulate(const KmeansParams& p, cudaStream_t st) {
+    const size_t smem = (size_t)p.K * D * 4 + (size_t)p.K * 4;
+    const int64_t n_chunks = p.B * (D / 4);
+    if (smem <= 100 * 1024 && !getenv("RQ_KMEANS_GLOBAL_RED")) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            RQ_CUDA(cudaFuncSetAttribute(rq_kmeans_accumulate_smem_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         100 * 1024));
+            attr_set = true;
+        }
+        int per_sm = (int)((220 * 1024) / (smem + 1024));
+        if (per_sm > 4) per_sm = 4;
+        int64_t blocks = (n_chunks + 512 * 4 - 1) / (512 * 4);
+        const int64_t cap = (int64_t)sm_count() * per_sm;
+        if (blocks > cap) blocks = cap;
+        rq_kmeans_accumulate_smem_kernel<D><<<(unsigned)blocks, 512, smem, st>>>(p.x, p.assign, p.B, p.K, p.sums, p.counts);
+    } else {
+        int64_t blocks = (n_chunks + 255) / 256;
+        const int64_t cap = (int64_t)sm_count() * 16;
+        if (blocks > cap) blocks = cap;
+        rq_kmeans_accumulate_kernel<D><<<(unsigned)blocks, 256, 0, st>>>(p.x, p.assign, p.B, p.sums, p.counts);
+    }
+    RQ_LAUNCHED();
+    return 0;
+}
+
 int kmeans_assign_accumulate_tc(const KmeansParams& p, int D, cudaStream_t st) {
     RQ_CUDA(cudaMemsetAsync(p.sums, 0, (size_t)p.K * D * sizeof(float), st));
     RQ_CUDA(cudaMemsetAsync(p.counts, 0, (size_t)p.K * sizeof(unsigned long long), st));
@@ -129,15 +215,10 @@ int kmeans_assign_accumulate_tc(const KmeansParams& p, int D, cudaStream_t st) {
     f.n_changed = p.n_changed; f.has_prev = p.has_prev;
     int rc = quantize_forward_tc(f, D, st);
     if (rc) return rc;
-    const int64_t n_chunks = p.B * (D / 4);
-    int64_t blocks = (n_chunks + 255) / 256;
-    const int64_t cap = (int64_t)sm_count() * 16;
-    if (blocks > cap) blocks = cap;
-    if (D == 32) rq_kmeans_accumulate_kernel<32><<<(unsigned)blocks, 256, 0, st>>>(p.x, p.assign, p.B, p.sums, p.counts);
-    else if (D == 64) rq_kmeans_accumulate_kernel<64><<<(unsigned)blocks, 256, 0, st>>>(p.x, p.assign, p.B, p.sums, p.counts);
-    else { set_error("kmeans tensor-core path: D=%d not served", D); return RQ_ERR_UNSUPPORTED_SHAPE; }
-    RQ_LAUNCHED();
-    return 0;
+    if (D == 32) return launch_kmeans_accumulate<32>(p, st);
+    if (D == 64) return launch_kmeans_accumulate<64>(p, st);
+    set_error("kmeans tensor-core path: D=%d not served", D);
+    return RQ_ERR_UNSUPPORTED_SHAPE;
 }
 
 // One CTA; thread k owns cluster k (strided).  c_new = sums/count (kmeans.py:57) or unchanged

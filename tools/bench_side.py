@@ -88,6 +88,9 @@ ms = timed(km_iter, 5)
 out["kmeans_level_iteration_10M_d32_k256"] = {
     "points": n, "ms": ms, "points_per_s": n / (ms * 1e-3), "algorithmic_GBps": n * 128 / (ms * 1e-3) / 1e9,
     "frac_of_hbm_roofline": (n * 128 / (ms * 1e-3) / 1e9) / HBM}
+ms_assign = timed(lambda: RF.quantize_forward(x, c[None], RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
+                                              want_loss=False), 5)
+out["kmeans_level_iteration_10M_d32_k256"]["assign_only_ms"] = ms_assign
 ms_simt = timed(lambda: RF.kmeans_assign_accumulate(x, c, assign, impl=RF.IMPL_SIMT), 2, warm=1)
 out["kmeans_level_iteration_10M_d32_k256"]["simt_family_ms"] = ms_simt
 del x, assign
