@@ -353,16 +353,38 @@ def run_engine(args):
     feed = R.data.utils.DevicePrefetcher(R.data.utils.cycle(xs_pin), dev)
     g_embs_bdl = [g.permute(1, 2, 0) for g in g_embs]                           # views, [B,D,L] like the output
 
+    class QuantizeLatents(torch.nn.Module):
+        """The quantiser part of RqVae.forward (rqvae.py:121-138) as a module, so that PyTorch's own
+        torch.cuda.make_graphed_callables can replay its forward and backward as CUDA graphs."""
+
+        def __init__(self, rqvae, temp):
+            super().__init__()
+            self.rqvae, self.temp = rqvae, temp
+
+        def forward(self, lat):
+            out = self.rqvae.quantize_latents(lat, self.temp)
+            return out.embeddings, out.sem_ids, out.quantize_loss
+
+    quantizer = QuantizeLatents(model, TEMP)
+    e2e_mode = "eager module call"
+    if use_graphs:
+        try:
+            quantizer = torch.cuda.make_graphed_callables(quantizer, (xs[0].clone().requires_grad_(True),),
+                                                           allow_unused_input=True)
+            e2e_mode = "torch.cuda.make_graphed_callables(module)"
+        except Exception as ex:                                               # keep the number, say how it was made
+            e2e_mode = f"eager module call (graph capture failed: {type(ex).__name__}: {str(ex)[:300]})"
+
     def e2e_step(i):
         s = i % N_SLOTS
         lat = next(feed).requires_grad_(True)                                   # H2D, 8 MiB (prefetched)
-        out = model.quantize_latents(lat, TEMP)
+        emb, sem_ids, qloss = quantizer(lat)
         model.zero_grad(set_to_none=True)
-        torch.autograd.backward([out.embeddings, out.quantize_loss], [g_embs_bdl[s], g_loss])
+        torch.autograd.backward([emb, qloss], [g_embs_bdl[s], g_loss])
         if world > 1:
             R.parallel.allreduce_codebook_grads(model)
-        loss_pin.copy_(out.quantize_loss.detach(), non_blocking=True)           # D2H
-        ids_pin.copy_(out.sem_ids.detach().t(), non_blocking=True)              # D2H
+        loss_pin.copy_(qloss.detach(), non_blocking=True)                       # D2H
+        ids_pin.copy_(sem_ids.detach().t(), non_blocking=True)                  # D2H
         torch.cuda.current_stream().synchronize()                               # the caller reads the result
 
     for i in range(max(3, args.warmup)):
@@ -422,7 +444,7 @@ def run_engine(args):
             "extra": {"fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "ids_only_ms": ids_only_ms,
                       "ids_only_items_per_s": B_PER_GPU / (ids_only_ms * 1e-3),
                       "fwd_items_per_s": B_PER_GPU / (fwd_ms * 1e-3),
-                      "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode},
+                      "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode},
         }
         if not args.no_cpu_baseline and world == 1:
             ips, ms, cores = cpu_reference_run(args.cpu_sample_items, 3, 1)

@@ -89,6 +89,9 @@ class ResidualQuantizeFn(torch.autograd.Function):
         ctx.save_for_backward(res, ids, codebooks, gumbel_uniform if gumbel_uniform is not None else x.new_empty(0))
         ctx.cfg = (mode, beta, temperature, gumbel_uniform is not None, seed, offset)
         ctx.mark_non_differentiable(ids)
+        # an output nobody differentiated (normally the residuals) reaches backward as None, not as a
+        # zero tensor the kernel would have to stream
+        ctx.set_materialize_grads(False)
         return emb, res, ids, loss
 
     @staticmethod

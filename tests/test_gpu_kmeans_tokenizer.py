@@ -220,3 +220,55 @@ def test_device_prefetcher_orders_and_completes():
     assert got == [0.0, 1.0, 2.0, 3.0, 4.0]
     it = U.DevicePrefetcher(U.cycle(host[:2]), DEV)
     assert [int(next(it)[0].item()) for _ in range(5)] == [0, 1, 0, 1, 0]
+
+
+def test_full_size_properties_c3_kmeans_10m():
+    """BASELINE config 3 size on one GPU (10M x 32 latents, 256 centroids): size-independent invariants of
+    one assignment + accumulation pass and its update (no oracle run at this size)."""
+    n, D, K = 10_000_000, 32, 256
+    g = torch.Generator(device=DEV).manual_seed(3)
+    x = torch.randn(n, D, device=DEV, generator=g)
+    c = x[:K].clone()
+    assign, sums, counts, nch = RF.kmeans_assign_accumulate(x, c)
+    assert int(nch) == n and int(counts.sum()) == n
+    assert int(assign.min()) >= 0 and int(assign.max()) < K
+    assert torch.equal(counts, torch.bincount(assign, minlength=K))
+    want = torch.zeros(K, D, dtype=torch.float64, device=DEV).index_add_(0, assign, x.double())
+    assert_close(sums, want.float(), "sums", tol=2e-5)
+    # the chosen centroid is the nearest one (direct form, float64) on a 64k-row sample, up to fp32 ties
+    idx = torch.arange(0, n, n // 65536, device=DEV)[:65536]
+    d = torch.cdist(x[idx].double(), c.double()) ** 2
+    excess = d.gather(1, assign[idx][:, None]).squeeze(1) - d.min(1).values
+    assert bool((excess <= 1e-5 * ((x[idx].double() ** 2).sum(1) + 1.0)).all())
+    # idempotence: a second pass from the stored assignment changes nothing
+    _, sums2, counts2, n0 = RF.kmeans_assign_accumulate(x, c, assign)
+    assert int(n0) == 0 and torch.equal(counts2, counts)
+    assert_close(sums2, sums, "sums (second pass)", tol=2e-5)
+    # update: centroid = mean of its points; total mass is conserved
+    c2 = c.clone()
+    RF.kmeans_update(sums, counts, c2)
+    nz = counts > 0
+    assert_close(c2[nz], (want[nz] / counts[nz][:, None]).float(), "centroids", tol=2e-5)
+
+
+def test_full_size_properties_c4_tokenize_d64():
+    """BASELINE config 4 shape (ml32m: d=64, 3x256), one 4M-item chunk of the 100M corpus: ids-only
+    tokenisation is deterministic, in range, equal to the exact SIMT family on a slice, and every id is
+    the nearest code of the residual it was chosen for (float64) up to the tie band."""
+    n, D, K, L = 4 << 20, 64, 256, 3
+    g = torch.Generator(device=DEV).manual_seed(4)
+    x = torch.randn(n, D, device=DEV, generator=g)
+    cb = torch.stack([x[l * K:(l + 1) * K] * (0.6 ** l) for l in range(L)]).contiguous()
+    _, _, ids, _ = RF.quantize_forward(x, cb, RF.MODE_EVAL, want_embeddings=False, want_residuals=False, want_loss=False)
+    _, _, ids2, _ = RF.quantize_forward(x, cb, RF.MODE_EVAL, want_embeddings=False, want_residuals=False, want_loss=False)
+    assert torch.equal(ids, ids2)
+    assert int(ids.min()) >= 0 and int(ids.max()) < K
+    sl = slice(1_000_000, 1_000_000 + 50_000)
+    _, res_s, ids_s, _ = RF.quantize_forward(x[sl].contiguous(), cb, RF.MODE_EVAL, impl=RF.IMPL_SIMT)
+    assert torch.equal(ids[:, sl], ids_s)
+    for l in range(L):
+        r = res_s[l][:8192].double()
+        d = torch.cdist(r, cb[l].double()) ** 2
+        excess = d.gather(1, ids_s[l][:8192, None]).squeeze(1) - d.min(1).values
+        scale = (r ** 2).sum(1) + (cb[l].double() ** 2).sum(1).max()
+        assert bool((excess <= 1e-6 * scale).all())
