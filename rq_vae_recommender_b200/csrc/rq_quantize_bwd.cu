@@ -667,6 +667,12 @@ __global__ void __launch_bounds__(bwdrow2::THREADS, 2) rq_bwd_row2_kernel(BwdPar
     };
     auto pick = [&](const int (&a)[kBwdMaxL], int l) { return (l == 3) ? a[3] : (l == 2) ? a[2] : (l == 1) ? a[1] : a[0]; };
     load_ids(wglobal);
+    // experiment: phase offset between the CTAs sharing an SM (dbg >> 8 = delay in units of 256 ns for odd CTAs)
+    if ((dbg >> 8) && (blockIdx.x & 1)) {
+        const long long t0 = clock64();
+        const long long wait = (long long)(dbg >> 8) * 256 * 2;      // ~2 cycles per ns
+        while (clock64() - t0 < wait) __nanosleep(64);
+    }
 
     for (int tile = wglobal; tile < n_tiles; tile += nwarps) {
         const int64_t row0 = (int64_t)tile * TW;
@@ -827,6 +833,221 @@ static int launch_bwd_row2(const BwdParams& p, cudaStream_t st, bool* served) {
     return 0;
 }
 
+// ---- D = 32, two lanes per row, double-buffered ---------------------------------------------------------------
+// Per warp the work is one serial chain (load -> dot products -> update -> scatter, level after level), so the
+// launch takes as long as the slowest warp's chain (tools/time_bwd.py: the phases add up instead of overlapping).
+// Here a warp's item is 16 rows x 1 level with TWO lanes per row (16 dims each): the per-item chain is half as
+// long, a 6 KB item fits twice in the warp's 12 KB, and the next item (next level, or the next tile's first
+// level) is in flight while the current one is computed.
+namespace bwdrow3 {
+constexpr int D = 32, TW = 16, WARPS = 8, THREADS = 32 * WARPS;
+constexpr int TILE_BYTES = TW * D * 4;           // 2 KB
+constexpr int ITEM_BYTES = 3 * TILE_BYTES;       // residual rows | gradient rows | codeword rows
+constexpr int WARP_BYTES = 2 * ITEM_BYTES;
+}  // namespace bwdrow3
+
+template <int MODE>
+__global__ void __launch_bounds__(bwdrow3::THREADS, 2) rq_bwd_row3_kernel(BwdParams p, int n_tiles) {
+    using namespace bwdrow3;
+    using bwdrow::sw_off;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* wbuf = smem + warp * WARP_BYTES;
+    const uint32_t wbuf_u32 = (uint32_t)__cvta_generic_to_shared(wbuf);
+    const bool has_gemb = p.g_emb != nullptr;
+    const int chunk = lane & 7, sub = lane >> 3;            // coalesced side: 8 lanes per row, 4 rows per instruction
+    const int ri = lane >> 1, half = lane & 1;              // compute side: 2 lanes per row, 16 dims each
+    const int wglobal = blockIdx.x * WARPS + warp, nwarps = gridDim.x * WARPS;
+    uint32_t co[4], ro[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        co[i] = sw_off(4 * i + sub, chunk);
+        ro[i] = sw_off(ri, 4 * half + i);
+    }
+
+    int ids_c[kBwdMaxL], ids_n[kBwdMaxL];
+    float gl_c = 0.f, gl_n = 0.f;
+    auto load_ids = [&](int tile, int (&ids)[kBwdMaxL], float& gl) {
+        const int64_t row = (int64_t)tile * TW + ri;
+        const bool ok = tile < n_tiles && row < p.B;
+#pragma unroll
+        for (int l = 0; l < kBwdMaxL; ++l) ids[l] = (ok && l < p.L) ? (int)__ldg(p.ids + (int64_t)l * p.B + row) : 0;
+        gl = (ok && p.g_loss) ? __ldg(p.g_loss + row) : 0.f;
+    };
+    auto pick = [&](const int (&a)[kBwdMaxL], int l) { return (l == 3) ? a[3] : (l == 2) ? a[2] : (l == 1) ? a[1] : a[0]; };
+    // fill buffer `b` with (tile, level l); `id` = this lane's row id at that level
+    auto issue = [&](int b, int tile, int l, int id) {
+        const int64_t row0 = (int64_t)tile * TW;
+        const uint32_t dst = wbuf_u32 + b * ITEM_BYTES;
+        const float* src_r = p.res + ((int64_t)l * p.B + row0 + sub) * D + chunk * 4;
+        const float* src_g = has_gemb ? p.g_emb + ((int64_t)l * p.B + row0 + sub) * D + chunk * 4 : nullptr;
+        const float* cbl = p.cb + (int64_t)l * p.K * D + chunk * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int k = __shfl_sync(0xffffffffu, id, 2 * (4 * i + sub));
+            if (row0 + sub + 4 * i < p.B) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + co[i]), "l"(src_r + i * 4 * D) : "memory");
+                if (has_gemb)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + TILE_BYTES + co[i]), "l"(src_g + i * 4 * D)
+                                 : "memory");
+            }
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 2 * TILE_BYTES + co[i]), "l"(cbl + (int64_t)k * D)
+                         : "memory");
+        }
+    };
+
+    int cur = wglobal;
+    load_ids(cur, ids_c, gl_c);
+    if (cur < n_tiles) issue(0, cur, p.L - 1, pick(ids_c, p.L - 1));
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    int buf = 0;
+    while (cur < n_tiles) {
+        const int nxt = cur + nwarps;
+        load_ids(nxt, ids_n, gl_n);
+        const int64_t row0 = (int64_t)cur * TW;
+        const float g2 = 2.f * gl_c, b2 = g2 * p.beta;
+        float G[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) G[j] = 0.f;
+#pragma unroll 1
+        for (int l = p.L - 1; l >= 0; --l) {
+            const int id = pick(ids_c, l);
+            if (l > 0) issue(buf ^ 1, cur, l - 1, pick(ids_c, l - 1));
+            else if (nxt < n_tiles) issue(buf ^ 1, nxt, p.L - 1, pick(ids_n, p.L - 1));
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+            __syncwarp();
+            uint8_t* tR = wbuf + buf * ITEM_BYTES;
+            uint8_t* tG = tR + TILE_BYTES;
+            uint8_t* tE = tG + TILE_BYTES;
+            float cg, cr, ce;
+            if (MODE == RQ_MODE_ROTATION_TRICK) {
+                float rr = 0.f, ee = 0.f, re = 0.f, gr = 0.f, ge = 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float4 r4 = *reinterpret_cast<const float4*>(tR + ro[c]);
+                    const float4 e4 = *reinterpret_cast<const float4*>(tE + ro[c]);
+                    float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (has_gemb) g4 = *reinterpret_cast<const float4*>(tG + ro[c]);
+                    const float rv[4] = {r4.x, r4.y, r4.z, r4.w}, ev[4] = {e4.x, e4.y, e4.z, e4.w};
+                    const float gv[4] = {g4.x - G[4 * c], g4.y - G[4 * c + 1], g4.z - G[4 * c + 2], g4.w - G[4 * c + 3]};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        rr = fmaf(rv[j], rv[j], rr); ee = fmaf(ev[j], ev[j], ee); re = fmaf(rv[j], ev[j], re);
+                        gr = fmaf(gv[j], rv[j], gr); ge = fmaf(gv[j], ev[j], ge);
+                    }
+                }
+                rr += __shfl_xor_sync(0xffffffffu, rr, 1); ee += __shfl_xor_sync(0xffffffffu, ee, 1);
+                re += __shfl_xor_sync(0xffffffffu, re, 1); gr += __shfl_xor_sync(0xffffffffu, gr, 1);
+                ge += __shfl_xor_sync(0xffffffffu, ge, 1);
+                const float nx = fast_sqrt(rr), ne = fast_sqrt(ee);
+                const float iu = fast_rcp(nx + 1e-8f), iq = fast_rcp(ne + 1e-8f);
+                const float lam = ne * fast_rcp(nx + 1e-6f);
+                float ns = fmaf(iu * iu, rr, fmaf(2.f * iu * iq, re, iq * iq * ee));
+                // |u+q| < 1/4 (codeword antipodal to the residual): recompute without cancellation; both lanes of a
+                // row see the same ns, so the branch is uniform per row and the shuffle is taken by whole pairs
+                const bool redo = ns < 0.0625f;
+                if (__any_sync(0xffffffffu, redo)) {
+                    float n2 = 0.f;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const float4 r4 = *reinterpret_cast<const float4*>(tR + ro[c]);
+                        const float4 e4 = *reinterpret_cast<const float4*>(tE + ro[c]);
+                        float w;
+                        w = fmaf(r4.x, iu, e4.x * iq); n2 = fmaf(w, w, n2);
+                        w = fmaf(r4.y, iu, e4.y * iq); n2 = fmaf(w, w, n2);
+                        w = fmaf(r4.z, iu, e4.z * iq); n2 = fmaf(w, w, n2);
+                        w = fmaf(r4.w, iu, e4.w * iq); n2 = fmaf(w, w, n2);
+                    }
+                    n2 += __shfl_xor_sync(0xffffffffu, n2, 1);
+                    if (redo) ns = n2;
+                }
+                const float iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f));
+                const float gw = lam * iw * fmaf(iu, gr, iq * ge);
+                const float gq = lam * iq * ge;
+                cg = lam;
+                cr = 2.f * iu * (gq - gw * iw) + b2;
+                ce = -2.f * gw * iw * iq - b2;
+            } else if (MODE == RQ_MODE_STE) {
+                cg = 1.f; cr = b2; ce = -b2;
+            } else {
+                cg = 0.f; cr = b2; ce = -b2;
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float4 r4 = *reinterpret_cast<const float4*>(tR + ro[c]);
+                const float4 e4 = *reinterpret_cast<const float4*>(tE + ro[c]);
+                float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (has_gemb) g4 = *reinterpret_cast<const float4*>(tG + ro[c]);
+                const float rv[4] = {r4.x, r4.y, r4.z, r4.w}, ev[4] = {e4.x, e4.y, e4.z, e4.w};
+                const float gv[4] = {g4.x - G[4 * c], g4.y - G[4 * c + 1], g4.z - G[4 * c + 2], g4.w - G[4 * c + 3]};
+                float v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    v[j] = g2 * (ev[j] - rv[j]);
+                    if (MODE == RQ_MODE_EVAL) v[j] += gv[j];
+                    G[4 * c + j] += fmaf(cg, gv[j], fmaf(cr, rv[j], ce * ev[j]));
+                }
+                *reinterpret_cast<float4*>(tG + ro[c]) = make_float4(v[0], v[1], v[2], v[3]);
+            }
+            __syncwarp();
+            {
+                float* gbase = p.g_cb + (int64_t)l * p.K * D + chunk * 4;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int k = __shfl_sync(0xffffffffu, id, 2 * (4 * i + sub));
+                    const float4 v = *reinterpret_cast<const float4*>(tG + co[i]);
+                    if (row0 + sub + 4 * i < p.B) red_add_v4(gbase + (int64_t)k * D, v.x, v.y, v.z, v.w);
+                }
+            }
+            if (l == 0) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    *reinterpret_cast<float4*>(tR + ro[c]) = make_float4(G[4 * c], G[4 * c + 1], G[4 * c + 2], G[4 * c + 3]);
+                __syncwarp();
+                float* dst = p.g_x + (row0 + sub) * D + chunk * 4;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float4 v = *reinterpret_cast<const float4*>(tR + co[i]);
+                    if (row0 + sub + 4 * i < p.B) *reinterpret_cast<float4*>(dst + i * 4 * D) = v;
+                }
+            }
+            __syncwarp();                                    // reads of this buffer done before it is refilled
+            buf ^= 1;
+        }
+        cur = nxt;
+#pragma unroll
+        for (int l = 0; l < kBwdMaxL; ++l) ids_c[l] = ids_n[l];
+        gl_c = gl_n;
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
+static int launch_bwd_row3(const BwdParams& p, cudaStream_t st, bool* served) {
+    using namespace bwdrow3;
+    *served = false;
+    if (p.L > kBwdMaxL || getenv("RQ_BWD_NO_ROW3")) return 0;
+    if (p.g_res) return 0;                                    // residual-output gradients: ring-buffered kernel
+    if ((((uintptr_t)p.res | (uintptr_t)p.g_emb | (uintptr_t)p.cb | (uintptr_t)p.g_x | (uintptr_t)p.g_cb) & 15) != 0) return 0;
+    const size_t smem = (size_t)WARPS * WARP_BYTES;            // 96 KB: two CTAs (16 warps) per SM
+    const int n_tiles = (int)((p.B + TW - 1) / TW);
+    const int ctas_needed = (n_tiles + WARPS - 1) / WARPS;
+    const int grid = ctas_needed < 2 * sm_count() ? ctas_needed : 2 * sm_count();
+    auto launch = [&](auto kern) -> int {
+        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, THREADS, smem, st>>>(p, n_tiles);
+        return 0;
+    };
+    int rc;
+    if (p.mode == RQ_MODE_ROTATION_TRICK) rc = launch(rq_bwd_row3_kernel<RQ_MODE_ROTATION_TRICK>);
+    else if (p.mode == RQ_MODE_STE) rc = launch(rq_bwd_row3_kernel<RQ_MODE_STE>);
+    else rc = launch(rq_bwd_row3_kernel<RQ_MODE_EVAL>);
+    if (rc) return rc;
+    RQ_LAUNCHED();
+    *served = true;
+    return 0;
+}
+
 static int launch_bwd_row(const BwdParams& p, cudaStream_t st, bool* served) {
     using namespace bwdrow;
     *served = false;
@@ -920,7 +1141,8 @@ int quantize_backward_simt(const BwdParams& p, int D, cudaStream_t st) {
     {
         bool served = false;
         int rc = 0;
-        if (D == 32) rc = launch_bwd_row2(p, st, &served);
+        if (D == 32) rc = launch_bwd_row3(p, st, &served);
+        if (!rc && !served && D == 32) rc = launch_bwd_row2(p, st, &served);
         if (!rc && !served && D == 32) rc = launch_bwd_row(p, st, &served);
         if (!rc && !served && D == 32) rc = launch_bwd_tma<32>(p, st, &served);
         else if (D == 64) rc = launch_bwd_tma<64>(p, st, &served);

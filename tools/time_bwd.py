@@ -16,7 +16,7 @@ fw = [RF.quantize_forward(xs[i], cbs, mode, 0.25, 0.2) for i in range(N)]
 
 
 def run(label, env):
-    for k in ("RQ_BWD_DBG", "RQ_BWD_NO_ROW2", "RQ_BWD_NO_ROW"):
+    for k in ("RQ_BWD_DBG", "RQ_BWD_NO_ROW3", "RQ_BWD_NO_ROW2", "RQ_BWD_NO_ROW"):
         os.environ.pop(k, None)
     os.environ.update(env)
     def go(i):
@@ -40,12 +40,12 @@ def run(label, env):
     print(f"{label:40s} {a.elapsed_time(b) / (5 * N) * 1e3:8.1f} us per backward (graph replay, memset + kernel)")
 
 
-run("row2 full", {})
-run("row2 no REDG", {"RQ_BWD_DBG": "1"})
-run("row2 no g_x store", {"RQ_BWD_DBG": "2"})
-run("row2 no math", {"RQ_BWD_DBG": "4"})
-run("row2 no loads", {"RQ_BWD_DBG": "8"})
-run("row2 no loads no REDG no store", {"RQ_BWD_DBG": "11"})
-run("row2 nothing", {"RQ_BWD_DBG": "15"})
-run("row (ring) full", {"RQ_BWD_NO_ROW2": "1"})
-run("row (ring) no REDG", {"RQ_BWD_NO_ROW2": "1", "RQ_BWD_DBG": "1"})
+run("row3 (2 lanes/row, double-buffered)", {})
+R2 = {"RQ_BWD_NO_ROW3": "1"}
+run("row2 full", dict(R2))
+run("row2 no REDG", dict(R2, RQ_BWD_DBG="1"))
+run("row2 no g_x store", dict(R2, RQ_BWD_DBG="2"))
+run("row2 no math", dict(R2, RQ_BWD_DBG="4"))
+run("row2 no loads", dict(R2, RQ_BWD_DBG="8"))
+run("row2 nothing", dict(R2, RQ_BWD_DBG="15"))
+run("row (ring) full", {"RQ_BWD_NO_ROW3": "1", "RQ_BWD_NO_ROW2": "1"})
