@@ -25,6 +25,11 @@ int sm_count() {
         int dev = 0;
         if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
         if (cached <= 0) cached = 148;
+        // SMs left free for concurrently running collectives (NCCL kernels need a few CTAs' worth of SM
+        // resources; a persistent grid that fills every SM would make one of the two wait for the other)
+        const char* e = getenv("RQ_SM_RESERVE");
+        const int reserve = e ? atoi(e) : 0;
+        if (reserve > 0 && reserve < cached) cached -= reserve;
     }
     return cached;
 }

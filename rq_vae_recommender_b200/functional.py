@@ -54,8 +54,10 @@ def quantize_forward(x: torch.Tensor, codebooks: torch.Tensor, mode: int = MODE_
 
 
 def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, beta, temperature,
-                      gumbel_uniform=None, seed: int = 0, offset: int = 0) -> Tuple[torch.Tensor, torch.Tensor]:
-    """rq_quantize_backward: returns (g_x [B,D], g_codebooks [L,K,D])."""
+                      gumbel_uniform=None, seed: int = 0, offset: int = 0,
+                      g_codebooks_out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """rq_quantize_backward: returns (g_x [B,D], g_codebooks [L,K,D]).  `g_codebooks_out` (contiguous fp32
+    [L,K,D]) receives the codebook gradient in place — e.g. a persistent all-reduce bucket."""
     residuals = _f32c(residuals, "residuals")
     codebooks = _f32c(codebooks, "codebooks")
     L.require_cuda(ids, "ids", torch.int64)
@@ -69,7 +71,12 @@ def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, bet
     dev = residuals.device
     with torch.cuda.device(dev):
         g_x = torch.empty((B, D), device=dev, dtype=torch.float32)
-        g_cb = torch.empty((Lv, K, D), device=dev, dtype=torch.float32)
+        if g_codebooks_out is None:
+            g_cb = torch.empty((Lv, K, D), device=dev, dtype=torch.float32)
+        else:
+            g_cb = L.require_cuda(g_codebooks_out, "g_codebooks_out", torch.float32)
+            if tuple(g_cb.shape) != (Lv, K, D) or not g_cb.is_contiguous():
+                raise L.RqEngineError(f"g_codebooks_out must be contiguous [L,K,D]={Lv, K, D}")
         rc = L.lib().rq_quantize_backward(L.ptr(g_emb), L.ptr(g_res), L.ptr(g_loss), L.ptr(residuals), L.ptr(ids),
                                           L.ptr(codebooks), B, D, K, Lv, int(mode), float(beta), float(temperature),
                                           L.ptr(gumbel_uniform), int(seed), int(offset), L.ptr(g_x), L.ptr(g_cb),

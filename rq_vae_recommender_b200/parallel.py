@@ -6,6 +6,15 @@ from typing import Tuple
 import torch
 
 
+def reserve_sms_for_collectives(n_sms: int = 8) -> None:
+    """Leave `n_sms` SMs out of the engine's persistent grids so that an NCCL kernel on another stream
+    (codebook-gradient / k-means all-reduce) and the quantiser kernels never wait for each other's SM
+    resources.  Must be called before the first kernel launch of the process (the library reads
+    RQ_SM_RESERVE once)."""
+    import os
+    os.environ["RQ_SM_RESERVE"] = str(int(n_sms))
+
+
 def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
     """Contiguous block [lo, hi) of `n` rows owned by `rank`; the first n % world ranks get one extra."""
     base, rem = divmod(n, world)
