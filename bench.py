@@ -244,16 +244,20 @@ def run_engine(args):
     # DDP's bucketed all-reduce does for the reference (train_rqvae.py:115-117,153).  The reduction is launched
     # eagerly beside the replayed graphs: captured as a branch of the step graph it has to join before the graph
     # ends, which serialises it with the kernels (measured at N = 4: 107-133 us/step in-graph vs 60 us beside).
-    comm_stream = torch.cuda.Stream() if world > 1 else None
+    pending = []                                        # async NCCL work handles of the last steps
 
     def allreduce_async(g_cb):
-        ev = torch.cuda.Event()
-        ev.record()
-        comm_stream.wait_event(ev)
-        with torch.cuda.stream(comm_stream):
-            dist.all_reduce(g_cb)
+        # async_op: NCCL's own stream waits for the launching stream's work so far; the launching stream moves on
+        pending.append(dist.all_reduce(g_cb, async_op=True))
+
+    def before_slot_reuse():
+        # the step about to run overwrites the gradient buffer reduced N_SLOTS steps ago: order it after that
+        # reduction (long finished in practice, so the wait costs nothing)
+        if len(pending) >= N_SLOTS:
+            pending.pop(0).wait()
 
     def step(i):
+        before_slot_reuse()
         out = step_compute(i % N_SLOTS)
         if world > 1:
             allreduce_async(out[2])
@@ -295,6 +299,7 @@ def run_engine(args):
         bwd_graphs, _keep3, _ = capture(lambda s: RF.quantize_backward(g_embs[s], None, g_loss, _fwd_out[s][1],
                                                                        _fwd_out[s][2], cbs, mode, BETA, TEMP))
         def run_step(i):
+            before_slot_reuse()
             step_graphs[i % N_SLOTS].replay()
             if world > 1:
                 allreduce_async(_keep1[i % N_SLOTS][2])
@@ -318,8 +323,8 @@ def run_engine(args):
         a.record()
         for i in range(n):
             fn(args.warmup + i)
-        if comm_stream is not None:
-            torch.cuda.current_stream().wait_stream(comm_stream)   # the last reductions are part of the K steps
+        while pending:
+            pending.pop(0).wait()                       # the last reductions are part of the K steps
         b.record()
         return a, b
 
