@@ -143,6 +143,31 @@ static int64_t host_chunk_rows() {
     return rows > 0 ? rows : 262144;
 }
 
+// Scratch of the host entry comes from a library-owned stream-ordered pool that keeps freed blocks (the default
+// pool's release threshold is 0: it would return the chunk buffers to the driver at every synchronisation and
+// re-map them on the next call, which costs milliseconds).
+static cudaMemPool_t host_entry_pool() {
+    static cudaMemPool_t pools[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!pools[dev]) {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        uint64_t keep = 1ull << 30;                     // up to 1 GiB stays cached between calls
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        pools[dev] = pool;
+    }
+    return pools[dev];
+}
+static cudaError_t host_entry_alloc(void** p, size_t bytes, cudaStream_t st) {
+    cudaMemPool_t pool = host_entry_pool();
+    return pool ? cudaMallocFromPoolAsync(p, bytes, pool, st) : cudaMallocAsync(p, bytes, st);
+}
+
 extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B, int D, int K, int L,
                                     int distance, int64_t* ids_host, float* loss_host, int impl,
                                     rq_stream_t stream) {
@@ -171,9 +196,9 @@ extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks,
         HOST_TRY(cudaEventCreateWithFlags(&ev_in[b], cudaEventDisableTiming));
         HOST_TRY(cudaEventCreateWithFlags(&ev_comp[b], cudaEventDisableTiming));
         HOST_TRY(cudaEventCreateWithFlags(&ev_out[b], cudaEventDisableTiming));
-        HOST_TRY(cudaMallocAsync((void**)&dx[b], (size_t)C * D * sizeof(float), st));
-        HOST_TRY(cudaMallocAsync((void**)&dids[b], (size_t)L * C * sizeof(int64_t), st));
-        if (loss_host) HOST_TRY(cudaMallocAsync((void**)&dloss[b], (size_t)C * sizeof(float), st));
+        HOST_TRY(host_entry_alloc((void**)&dx[b], (size_t)C * D * sizeof(float), st));
+        HOST_TRY(host_entry_alloc((void**)&dids[b], (size_t)L * C * sizeof(int64_t), st));
+        if (loss_host) HOST_TRY(host_entry_alloc((void**)&dloss[b], (size_t)C * sizeof(float), st));
     }
     // the side streams start after the allocations (and whatever the caller queued before us)
     HOST_TRY(cudaEventRecord(ev_start, st));

@@ -154,8 +154,7 @@ __global__ void __launch_bounds__(kSimtThreads) rq_fwd_simt_kernel(FwdParams p) 
             if (p.res) store_row<D>(p.res + off, r);
             if (p.emb) store_row<D>(p.emb + off, o);
             p.ids[(int64_t)l * p.B + row] = bi;
-#pragma unroll
-            for (int j = 0; j < D; ++j) r[j] = r[j] - o[j];                 // rqvae.py:129
+            residual_update<D>(r, o);                                      // rqvae.py:129
         }
     }
     if (active && p.loss) p.loss[row] = loss_acc;

@@ -584,8 +584,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
                 }
                 store_id(l, row, active, bi);
             }
-#pragma unroll
-            for (int j = 0; j < D; ++j) r[j] = r[j] - o[j];                     // rqvae.py:129
+            residual_update<D>(r, o);                                      // rqvae.py:129
             xx = dot_self<D>(r);
             RQ_TL_DEP(12 + 8 * l, xx);
         }

@@ -393,8 +393,7 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
                 }
                 if (active) *dst = bi;
             }
-#pragma unroll
-            for (int j = 0; j < D; ++j) r[j] = r[j] - e[j];                     // rqvae.py:129
+            residual_update<D>(r, e);                                      // rqvae.py:129
             xx = dot_self<D>(r);
         }
         if (active && p.loss) p.loss[row] = loss_acc;

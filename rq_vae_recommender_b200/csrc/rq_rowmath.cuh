@@ -19,12 +19,18 @@ __device__ __forceinline__ void store_row(float* __restrict__ dst, const float (
 #pragma unroll
     for (int j = 0; j < D / 4; ++j) d4[j] = make_float4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
 }
+// ||r||^2: even and odd elements accumulate in the two lanes of one FFMA2 chain, then the lanes are added.
+// (Both kernel families and the re-scoring path use this one definition, so they agree bit for bit.)
 template <int D>
 __device__ __forceinline__ float dot_self(const float (&r)[D]) {
-    float s = 0.f;
+    if (D < 2) return r[0] * r[0];
+    f32x2 s = pack2(0.f, 0.f);
 #pragma unroll
-    for (int j = 0; j < D; ++j) s = fmaf(r[j], r[j], s);
-    return s;
+    for (int j = 0; j + 1 < D; j += 2) {
+        const f32x2 v = pack2(r[j], r[j + 1]);
+        s = fma2(v, v, s);
+    }
+    return hsum2(s);
 }
 
 // Canonical ||c||^2 of a codeword, bit-identical in both kernel families: sequential fmaf over
@@ -67,26 +73,37 @@ __device__ __forceinline__ float code_sqnorm(const float* __restrict__ c) {
 template <int D>
 __device__ __forceinline__ float level_epilogue(int mode, float beta, const float (&r)[D], const float (&e)[D],
                                                 float xx, float (&o)[D]) {
-    float dsq = 0.f;
-    if (mode == RQ_MODE_ROTATION_TRICK) {
-        float ee = 0.f, re = 0.f;
+    static_assert(D % 2 == 0, "rows are processed as fp32 pairs");
+    f32x2 rp[D / 2], ep[D / 2];
 #pragma unroll
-        for (int j = 0; j < D; ++j) {
-            float t = r[j] - e[j];
-            dsq = fmaf(t, t, dsq);
-            ee = fmaf(e[j], e[j], ee);
-            re = fmaf(r[j], e[j], re);
+    for (int j = 0; j < D / 2; ++j) {
+        rp[j] = pack2(r[2 * j], r[2 * j + 1]);
+        ep[j] = pack2(e[2 * j], e[2 * j + 1]);
+    }
+    float dsq;
+    if (mode == RQ_MODE_ROTATION_TRICK) {
+        f32x2 d2 = pack2(0.f, 0.f), e2 = d2, re2 = d2;
+#pragma unroll
+        for (int j = 0; j < D / 2; ++j) {
+            const f32x2 t = sub2(rp[j], ep[j]);
+            d2 = fma2(t, t, d2);
+            e2 = fma2(ep[j], ep[j], e2);
+            re2 = fma2(rp[j], ep[j], re2);
         }
+        dsq = hsum2(d2);
+        const float ee = hsum2(e2), re = hsum2(re2);
         const float nx = fast_sqrt(xx), ne = fast_sqrt(ee);
         const float iu = fast_rcp(nx + 1e-8f), iq = fast_rcp(ne + 1e-8f);
         float ns = fmaf(iu * iu, xx, fmaf(2.f * iu * iq, re, iq * iq * ee));
         if (ns < 0.0625f) {                                   // |u+q| < 1/4: recompute without cancellation
-            ns = 0.f;
+            f32x2 n2 = pack2(0.f, 0.f);
+            const f32x2 iu2 = pack2(iu, iu), iq2 = pack2(iq, iq);
 #pragma unroll
-            for (int j = 0; j < D; ++j) {
-                float sj = fmaf(r[j], iu, e[j] * iq);
-                ns = fmaf(sj, sj, ns);
+            for (int j = 0; j < D / 2; ++j) {
+                const f32x2 sj = fma2(rp[j], iu2, mul2(ep[j], iq2));
+                n2 = fma2(sj, sj, n2);
             }
+            ns = hsum2(n2);
         }
         const float iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f)); // F.normalize(eps=1e-6)
         const float rs = fmaf(iu, xx, iq * re);               // r.(u+q)
@@ -94,23 +111,35 @@ __device__ __forceinline__ float level_epilogue(int mode, float beta, const floa
         const float lam = ne * fast_rcp(nx + 1e-6f);
         const float ca = lam * (1.f - 2.f * rsw * iu);
         const float ce = 2.f * lam * iq * (iu * xx - rsw);
+        const f32x2 ca2 = pack2(ca, ca), ce2 = pack2(ce, ce);
 #pragma unroll
-        for (int j = 0; j < D; ++j) o[j] = fmaf(ca, r[j], ce * e[j]);
+        for (int j = 0; j < D / 2; ++j) unpack2(fma2(ca2, rp[j], mul2(ce2, ep[j])), o[2 * j], o[2 * j + 1]);
     } else {
+        f32x2 d2 = pack2(0.f, 0.f);
 #pragma unroll
-        for (int j = 0; j < D; ++j) {
-            float t = r[j] - e[j];
-            dsq = fmaf(t, t, dsq);
+        for (int j = 0; j < D / 2; ++j) {
+            const f32x2 t = sub2(rp[j], ep[j]);
+            d2 = fma2(t, t, d2);
         }
+        dsq = hsum2(d2);
         if (mode == RQ_MODE_STE) {
 #pragma unroll
-            for (int j = 0; j < D; ++j) o[j] = r[j] + (e[j] - r[j]);       // quantize.py:132
+            for (int j = 0; j < D / 2; ++j)                                // quantize.py:132: x + (emb - x)
+                unpack2(add2(rp[j], sub2(ep[j], rp[j])), o[2 * j], o[2 * j + 1]);
         } else {                                                           // EVAL: quantize.py:149
 #pragma unroll
             for (int j = 0; j < D; ++j) o[j] = e[j];
         }
     }
     return dsq + beta * dsq;                                               // loss.py:40-42
+}
+
+// r -= o (rqvae.py:129), pairwise
+template <int D>
+__device__ __forceinline__ void residual_update(float (&r)[D], const float (&o)[D]) {
+#pragma unroll
+    for (int j = 0; j + 1 < D; j += 2)
+        unpack2(sub2(pack2(r[j], r[j + 1]), pack2(o[j], o[j + 1])), r[j], r[j + 1]);
 }
 
 }  // namespace rq

@@ -216,7 +216,14 @@ __device__ __forceinline__ uint32_t pack_hi16(uint32_t a, uint32_t b) { return _
 __device__ __forceinline__ void split_pair(float a, float b, uint32_t& hi, uint32_t& lo) {
     uint32_t ah = bf16_hi_bits(a), bh = bf16_hi_bits(b);
     hi = pack_hi16(ah, bh);
-    lo = pack_hi16(__float_as_uint(a - __uint_as_float(ah)), __float_as_uint(b - __uint_as_float(bh)));
+    // both subtractions in one FADD2 (exact: a - hi(a) is representable)
+    unsigned long long ab, hh, dd;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ab) : "f"(a), "f"(b));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(hh) : "r"(ah), "r"(bh));
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dd) : "l"(ab), "l"(hh));
+    uint32_t la, lb;
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(la), "=r"(lb) : "l"(dd));
+    lo = pack_hi16(la, lb);
 }
 
 }  // namespace ptx

@@ -62,14 +62,18 @@ def host_call():
 
 
 host_call()
+host_call()
 torch.cuda.synchronize()
-t0 = time.perf_counter()
-for _ in range(3):
+times = []
+for _ in range(7):
+    t0 = time.perf_counter()
     host_call()
-dt = (time.perf_counter() - t0) / 3
+    times.append(time.perf_counter() - t0)
+dt = sorted(times)[len(times) // 2]                     # median of 7 calls
 out["tokenize_host_buffers_d32_3x256"] = {
     "items": n, "ms": dt * 1e3, "items_per_s": n / dt, "h2d_GBps": n * 128 / dt / 1e9, "d2h_GBps": n * 24 / dt / 1e9,
-    "note": "wall clock around rq_semantic_ids_host, pinned host buffers, copies inside"}
+    "note": "wall clock around rq_semantic_ids_host (median of 7), pinned host buffers, copies inside",
+    "ms_min_max": [min(times) * 1e3, max(times) * 1e3]}
 del xh, idh
 # ---- C3-like: one k-means level-iteration ------------------------------------------------------------------
 n = 10_000_000
