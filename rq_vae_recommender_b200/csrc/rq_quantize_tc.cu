@@ -546,6 +546,11 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
             if (bi >= p.K) bi = p.K - 1;        // unreachable unless inputs are NaN; keeps the gather in range
 
             // ---- gather, estimator, loss, outputs, residual update ---------------------------------------
+            // ids-only launches (tokenisation, k-means assignment) need nothing past the id at the last level
+            if (l == p.L - 1 && !p.emb && !p.loss) {
+                store_id(l, row, active, bi);
+                continue;
+            }
             float e[D], o[D];
             if (SHARE) {
                 // cooperative gather: 8 lanes fetch the 8 chunks of one row's codeword (4 rows per instruction)

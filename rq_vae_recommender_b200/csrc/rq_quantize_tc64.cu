@@ -375,15 +375,7 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
             }
             if (bi >= p.K) bi = p.K - 1;        // unreachable unless inputs are NaN; keeps the gather in range
 
-            // ---- gather, estimator, loss, outputs, residual update ---------------------------------------
-            float e[D];
-#pragma unroll
-            for (int j = 0; j < D; j += 8) ptx::ld_global_v8(cbl + (int64_t)bi * D + j, &e[j]);
-            loss_acc += level_epilogue<D>(p.mode, p.beta, r, e, xx, e);          // estimator value in place
-            if (active && p.emb) {
-#pragma unroll
-                for (int j = 0; j < D; j += 8) ptx::st_global_v8(p.emb + off + j, &e[j]);
-            }
+            // ---- id out; then gather, estimator, loss, outputs, residual update ---------------------------------
             {
                 int64_t* dst = p.ids + (int64_t)l * p.B + row;
                 if (p.n_changed) {
@@ -392,6 +384,16 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
                     if (lane == 0 && m) atomicAdd(p.n_changed, (unsigned long long)__popc(m));
                 }
                 if (active) *dst = bi;
+            }
+            // ids-only launches (tokenisation, k-means assignment) need nothing past the id at the last level
+            if (l == p.L - 1 && !p.emb && !p.loss) continue;
+            float e[D];
+#pragma unroll
+            for (int j = 0; j < D; j += 8) ptx::ld_global_v8(cbl + (int64_t)bi * D + j, &e[j]);
+            loss_acc += level_epilogue<D>(p.mode, p.beta, r, e, xx, e);          // estimator value in place
+            if (active && p.emb) {
+#pragma unroll
+                for (int j = 0; j < D; j += 8) ptx::st_global_v8(p.emb + off + j, &e[j]);
             }
             residual_update<D>(r, e);                                      // rqvae.py:129
             xx = dot_self<D>(r);
