@@ -95,11 +95,14 @@ class SemanticIdTokenizer(nn.Module):
         if parallel.is_distributed(group):
             import torch.distributed as dist
             lo, hi = parallel.shard_range(n, dist.get_rank(group), dist.get_world_size(group))
-        chunks = []
-        for s in range(lo, hi, self.corpus_batch_size):
-            idx = list(range(s, min(hi, s + self.corpus_batch_size)))
-            batch = batch_to(movie_dataset[idx], device)
-            chunks.append(self.semantic_ids(batch.x))
+        def host_batches():
+            for s in range(lo, hi, self.corpus_batch_size):
+                yield movie_dataset[list(range(s, min(hi, s + self.corpus_batch_size)))]
+
+        # the copy of chunk i+1 (768-d inputs: the bulk of the bytes on this path) runs on its own stream while
+        # chunk i is encoded and quantised
+        from ...data.utils import DevicePrefetcher
+        chunks = [self.semantic_ids(batch.x) for batch in DevicePrefetcher(host_batches(), device)]
         ids = torch.cat(chunks, dim=0) if chunks else torch.zeros((0, self.n_layers), dtype=torch.int64, device=device)
         ids = parallel.gather_row_shards(ids.contiguous(), n, group)
         self.cached_ids = RF.corpus_table(ids, self.codebook_size)

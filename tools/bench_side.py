@@ -75,6 +75,44 @@ out["tokenize_host_buffers_d32_3x256"] = {
     "note": "wall clock around rq_semantic_ids_host (median of 7), pinned host buffers, copies inside",
     "ms_min_max": [min(times) * 1e3, max(times) * 1e3]}
 del xh, idh
+# ---- C4-like, module level: SemanticIdTokenizer.precompute_corpus_ids over 1M pinned 768-d items (ml32m dims) ------
+from rq_vae_recommender_b200.data.schemas import SeqBatch
+
+
+class _Corpus(torch.utils.data.Dataset):
+    def __init__(self, n, dim):
+        self.x = torch.randn(n, dim).pin_memory()
+
+    def __len__(self):
+        return self.x.shape[0]
+
+    def __getitem__(self, idx):
+        lo, hi = idx[0], idx[-1] + 1                      # the tokenizer asks for contiguous ranges
+        ids = torch.arange(lo, hi)
+        m1 = -torch.ones(hi - lo, dtype=torch.int64)
+        return SeqBatch(user_ids=m1, ids=ids, ids_fut=m1, x=self.x[lo:hi], x_fut=m1, seq_mask=torch.ones(hi - lo, dtype=torch.bool))
+
+
+n_items = 1 << 20
+corpus = _Corpus(n_items, 768)
+tok = R.SemanticIdTokenizer(input_dim=768, output_dim=64, hidden_dims=[512, 256, 128], codebook_size=256, n_layers=3,
+                            n_cat_feats=0).to(dev)
+with torch.no_grad():
+    lat = tok.rq_vae.encode(corpus.x[:65536].to(dev))
+    for l, layer in enumerate(tok.rq_vae.layers):        # trained-looking codebooks: residual rows of the data
+        layer.embedding.weight.copy_(lat[l * 256:(l + 1) * 256] * (0.6 ** l))
+        layer.kmeans_initted = True
+tok.precompute_corpus_ids(corpus)
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+table = tok.precompute_corpus_ids(corpus)
+torch.cuda.synchronize()
+dt = time.perf_counter() - t0
+out["corpus_tokenisation_module_api_1M_x_768_to_d64_3x256"] = {
+    "items": n_items, "ms": dt * 1e3, "items_per_s": n_items / dt, "h2d_GBps": n_items * 768 * 4 / dt / 1e9,
+    "table_shape": list(table.shape),
+    "note": "pinned 768-d inputs -> encoder MLP (torch) -> fused quantiser -> dedup table; wall clock, H2D inside"}
+del corpus, tok, table
 # ---- C3-like: one k-means level-iteration ------------------------------------------------------------------
 n = 10_000_000
 x = torch.randn(n, 32, device=dev)
