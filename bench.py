@@ -384,11 +384,14 @@ def run_engine(args):
         except Exception as ex:                                               # keep the number, say how it was made
             e2e_mode = f"eager module call (graph capture failed: {type(ex).__name__}: {str(ex)[:300]})"
 
+    q_params = [prm for prm in model.parameters() if prm.requires_grad]
+
     def e2e_step(i):
         s = i % N_SLOTS
         lat = next(feed).requires_grad_(True)                                   # H2D, 8 MiB (prefetched)
         emb, sem_ids, qloss = quantizer(lat)
-        model.zero_grad(set_to_none=True)
+        for prm in q_params:                                                    # zero_grad(set_to_none=True)
+            prm.grad = None
         torch.autograd.backward([emb, qloss], [g_embs_bdl[s], g_loss])
         if world > 1:
             R.parallel.allreduce_codebook_grads(model)

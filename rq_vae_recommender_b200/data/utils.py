@@ -64,6 +64,7 @@ class DevicePrefetcher:
         self._it: Iterator = iter(source)
         self._stream = torch.cuda.Stream(device=self.device)
         self._queue = []
+        self._free_events = []
         self._depth = depth
         for _ in range(depth):
             self._issue()
@@ -73,9 +74,10 @@ class DevicePrefetcher:
             host = next(self._it)
         except StopIteration:
             return
+        # events are recycled (creating one costs more than recording it)
+        ev = self._free_events.pop() if self._free_events else torch.cuda.Event()
         with torch.cuda.stream(self._stream):
             dev = batch_to(host, self.device, non_blocking=True)
-            ev = torch.cuda.Event()
             ev.record(self._stream)
         self._queue.append((dev, ev))
 
@@ -88,6 +90,7 @@ class DevicePrefetcher:
         dev, ev = self._queue.pop(0)
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(ev)
+        self._free_events.append(ev)
         _record_stream(dev, cur)
         self._issue()
         return dev
