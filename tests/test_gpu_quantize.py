@@ -191,3 +191,35 @@ def test_full_size_properties_c2():
         # determinism / idempotence of the launch
         emb2, res2, ids2, loss2 = RF.quantize_forward(xd, cbs, mode, beta=0.25)
         assert torch.equal(ids, ids2) and torch.equal(emb, emb2) and torch.equal(loss, loss2)
+
+
+@pytest.mark.parametrize("mode", [O.MODE_ROTATION_TRICK, O.MODE_STE])
+@pytest.mark.parametrize("which", ["loss_only", "emb_only", "res_only", "emb_res_loss"])
+def test_backward_with_partial_upstream_gradients(which, mode):
+    """Outputs nobody differentiated reach the autograd Function as None (no zero tensors are
+    materialised); every subset of {embeddings, residuals, loss} must give the oracle's gradients —
+    the residuals case goes through the ring-buffered kernel, the others through the default one."""
+    B, D, K, L = 3000, 32, 256, 3
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(B, D, generator=g)
+    cbs = synthetic_codebooks(torch.randn(4 * K, D, generator=g), L, K, seed=3)
+    g_emb = torch.randn(L, B, D, generator=g) if "emb" in which else None
+    g_res = torch.randn(L, B, D, generator=g) * 0.1 if "res" in which else None
+    g_loss = torch.rand(B, generator=g) if "loss" in which else None
+    z = torch.zeros(L, B, D)
+    ref, gx_ref, gcb_ref = O.rq_forward_backward(x, cbs, mode, 0.25, 0.2, g_emb if g_emb is not None else z,
+                                                 g_loss if g_loss is not None else torch.zeros(B), g_res=g_res)
+    xin = x.to(DEV).requires_grad_(True)
+    cin = torch.stack(cbs).to(DEV).requires_grad_(True)
+    emb, res, ids, loss = RF.residual_quantize(xin, cin, mode, 0.25, 0.2)
+    outs, grads = [], []
+    for o, go in ((emb, g_emb), (res, g_res), (loss, g_loss)):
+        if go is not None:
+            outs.append(o)
+            grads.append(go.to(DEV))
+    torch.autograd.backward(outs, grads)
+    ok = matching_rows(ids, ref)
+    assert ok.float().mean() > 0.995
+    assert_close(xin.grad.cpu()[ok], gx_ref[ok], f"{which} grad x")
+    if bool(ok.all()):
+        assert_close(cin.grad.cpu(), gcb_ref, f"{which} grad codebooks")
