@@ -350,27 +350,49 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
                     cm |= (accB[i] <= thr) ? (1u << i) : 0u;
                 }
                 if (wild) { gm = 0xFFFFu; cm = 0xFFFFu; }
-                if (ambiguous) {
-                    float best = INFINITY;
-#pragma unroll 1
-                    for (uint32_t g = gm; g; g &= g - 1) {
-                        const int gi = __ffs(g) - 1;
-#pragma unroll 1
-                        for (uint32_t c = cm; c; c &= c - 1) {
-                            const int k = gi * 16 + (__ffs(c) - 1);
-                            if (k >= p.K) continue;
-                            const float4* c4 = reinterpret_cast<const float4*>(cbl + (int64_t)k * D);
-                            float a = 0.f;
+                // The warp re-scores one ambiguous row at a time, its candidate pairs spread over the 32 lanes
+                // (a lane-serial loop would hold the other 31 rows — and through the warpgroup barrier the other
+                // three warps — for one 64-long FMA chain per candidate).  The row is parked in the warp's own,
+                // currently idle, A-tile rows; every lane runs the same sequential fmaf chain as the SIMT family
+                // on its candidate, then a lexicographic (distance, index) minimum picks the lowest index among
+                // equals — the result of the serial ascending scan.
+                float* scratch = reinterpret_cast<float*>(sAw + (warp & 3) * 32 * 128);
+                for (unsigned todo = __ballot_sync(0xffffffffu, ambiguous); todo; todo &= todo - 1) {
+                    const int src = __ffs(todo) - 1;
+                    if (lane == src) {
 #pragma unroll
-                            for (int j = 0; j < D / 4; ++j) {
-                                const float4 cv = __ldg(c4 + j);
-                                a = fmaf(r[4 * j], cv.x, a); a = fmaf(r[4 * j + 1], cv.y, a);
-                                a = fmaf(r[4 * j + 2], cv.z, a); a = fmaf(r[4 * j + 3], cv.w, a);
-                            }
-                            float d = (xx + sCC[l * KC + k]) - 2.f * a;
-                            if (d < best) { best = d; bi = k; }
-                        }
+                        for (int j = 0; j < D; j += 4)
+                            *reinterpret_cast<float4*>(scratch + j) = make_float4(r[j], r[j + 1], r[j + 2], r[j + 3]);
                     }
+                    __syncwarp();
+                    const uint32_t g = __shfl_sync(0xffffffffu, gm, src), c = __shfl_sync(0xffffffffu, cm, src);
+                    const float xs = __shfl_sync(0xffffffffu, xx, src);
+                    const int nc = __popc(c), np = __popc(g) * nc;
+                    float best = INFINITY;
+                    int bk = __shfl_sync(0xffffffffu, bi, src);          // stays if nothing compares below +inf (NaN input)
+                    for (int t = lane; t < np; t += 32) {
+                        const int k = (int)__fns(g, 0, t / nc + 1) * 16 + (int)__fns(c, 0, t % nc + 1);
+                        if (k >= p.K) continue;
+                        const float4* c4 = reinterpret_cast<const float4*>(cbl + (int64_t)k * D);
+                        float a = 0.f;
+#pragma unroll
+                        for (int j = 0; j < D / 4; ++j) {
+                            const float4 cv = __ldg(c4 + j);
+                            const float4 rv = *reinterpret_cast<const float4*>(scratch + 4 * j);
+                            a = fmaf(rv.x, cv.x, a); a = fmaf(rv.y, cv.y, a);
+                            a = fmaf(rv.z, cv.z, a); a = fmaf(rv.w, cv.w, a);
+                        }
+                        const float d = (xs + sCC[l * KC + k]) - 2.f * a;
+                        if (d < best) { best = d; bk = k; }             // a lane's candidates come in ascending index
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const float od = __shfl_xor_sync(0xffffffffu, best, o);
+                        const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
+                        if (od < best || (od == best && ok < bk)) { best = od; bk = ok; }
+                    }
+                    if (lane == src) bi = bk;
+                    __syncwarp();                                       // scratch is reused by the next row
                 }
             }
             if (bi >= p.K) bi = p.K - 1;        // unreachable unless inputs are NaN; keeps the gather in range
