@@ -24,7 +24,8 @@ def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
 
 def allreduce_codebook_grads(model, group=None, average: bool = True) -> None:
     """All-reduce of the [L,K,D] codebook gradients (98,304 B at 3x256x32): what DDP does
-    implicitly in the reference (train_rqvae.py:115-117,153), as ONE flat NCCL call."""
+    implicitly in the reference (train_rqvae.py:115-117,153), as ONE flat NCCL call (three device
+    ops in total: pack, all-reduce with in-collective averaging, unpack)."""
     import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return
@@ -32,13 +33,14 @@ def allreduce_codebook_grads(model, group=None, average: bool = True) -> None:
     if not grads:
         return
     flat = torch.cat([g.reshape(-1) for g in grads])
-    dist.all_reduce(flat, group=group)
-    if average:
-        flat /= dist.get_world_size(group)
-    o = 0
-    for g in grads:
-        g.copy_(flat[o:o + g.numel()].view_as(g))
-        o += g.numel()
+    nccl = dist.get_backend(group) == "nccl"
+    if average and nccl:
+        dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=group)
+    else:
+        dist.all_reduce(flat, group=group)
+        if average:
+            flat /= dist.get_world_size(group)
+    torch._foreach_copy_(grads, [c.view_as(g) for g, c in zip(grads, flat.split([g.numel() for g in grads]))])
 
 
 def is_distributed(group=None) -> bool:

@@ -100,8 +100,21 @@ def _gloo_worker(rank, world, port, q):
         from rq_vae_recommender_b200.parallel import gather_row_shards
         ids_full = torch.arange(11 * 3, dtype=torch.int64).reshape(11, 3)
         gathered = gather_row_shards(ids_full[lo:hi].contiguous(), 11)
+        # codebook-gradient all-reduce (mean over ranks), the training step's one collective
+        from rq_vae_recommender_b200.parallel import allreduce_codebook_grads
+
+        class _Layer:
+            def __init__(self, v):
+                self.embedding = torch.nn.Embedding(5, 4)
+                self.embedding.weight.grad = torch.full((5, 4), float(v))
+
+        class _Model:
+            layers = [_Layer(rank + 1), _Layer(10 * (rank + 1))]
+        allreduce_codebook_grads(_Model)
+        grads_ok = (torch.allclose(_Model.layers[0].embedding.weight.grad, torch.full((5, 4), 1.5))
+                    and torch.allclose(_Model.layers[1].embedding.weight.grad, torch.full((5, 4), 15.0)))
         q.put((rank, off, n, torch.equal(rows, full[[0, 5, 10, 6]]), km.centroids.clone(),
-               torch.equal(gathered, ids_full)))
+               torch.equal(gathered, ids_full), grads_ok))
     finally:
         dist.destroy_process_group()
 
@@ -119,6 +132,7 @@ def test_kmeans_sharding_helpers_gloo_world2():
     assert res[0][3] and res[1][3]
     assert torch.equal(res[0][4], res[1][4])     # identical initial centroids on both ranks
     assert res[0][5] and res[1][5]               # row-shard all-gather reassembles the global order
+    assert res[0][6] and res[1][6]               # codebook gradients averaged over the two ranks
 
 
 def test_data_utils_batch_to_and_cycle():
