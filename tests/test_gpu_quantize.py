@@ -223,3 +223,40 @@ def test_backward_with_partial_upstream_gradients(which, mode):
     assert_close(xin.grad.cpu()[ok], gx_ref[ok], f"{which} grad x")
     if bool(ok.all()):
         assert_close(cin.grad.cpu(), gcb_ref, f"{which} grad codebooks")
+
+
+def test_c1_full_corpus_get_semantic_ids():
+    """BASELINE config 1 at full size: 12,101 items, 768-d, encoder [512,256,128] -> d=32, 3x256, codebooks
+    k-means-initialised on first use (quantize.py:102-103).  `RqVae.get_semantic_ids` on the GPU against the
+    oracle fed with the same latents and codebooks; the torch encoder is checked against its CPU copy."""
+    import copy
+    N = 12101
+    g = torch.Generator().manual_seed(0)
+    x = torch.nn.functional.normalize(torch.randn(N, 768, generator=g), dim=1)
+    torch.manual_seed(0)
+    model = R.RqVae(input_dim=768, embed_dim=32, hidden_dims=[512, 256, 128], codebook_size=256,
+                    codebook_kmeans_init=True, codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, n_layers=3,
+                    n_cat_features=0).to(DEV)
+    model.eval()
+    np.random.seed(0)
+    with torch.no_grad():
+        out = model.get_semantic_ids(x.to(DEV), 0.001)          # first call: per-level k-means init, then quantise
+        assert all(layer.kmeans_initted for layer in model.layers)
+        out2 = model.get_semantic_ids(x.to(DEV), 0.001)         # fused path, same codebooks
+        lat = model.encode(x.to(DEV))
+        cbs = model.effective_codebooks()
+    assert out.sem_ids.shape == (N, 3) and out.embeddings.shape == (N, 32, 3)
+    assert torch.equal(out.sem_ids, out2.sem_ids)
+    ref = O.rq_forward(lat.cpu(), list(cbs.cpu()), O.MODE_EVAL)
+    ids_lb = out2.sem_ids.t().contiguous()
+    n_mis, n_out1 = check_ids(ids_lb, ref, list(cbs.cpu()), "C1")
+    assert n_mis <= 2
+    ok = matching_rows(ids_lb, ref)
+    assert_close(out2.embeddings.permute(2, 0, 1).cpu()[:, ok], ref.embeddings[:, ok], "emb")
+    assert_close(out2.residuals.permute(2, 0, 1).cpu()[:, ok], ref.residuals[:, ok], "residuals")
+    assert_close(out2.quantize_loss.cpu()[ok], ref.quantize_loss[ok], "loss")
+    lat_cpu = copy.deepcopy(model.encoder).cpu()(x)
+    assert_close(lat.cpu(), lat_cpu.detach(), "encoder latents (torch GPU vs torch CPU)", tol=1e-4)
+    # k-means-initialised codebooks are all in use at level 0 and most tuples are distinct
+    assert int(torch.unique(out2.sem_ids[:, 0]).numel()) >= 250
+    assert int(torch.unique(out2.sem_ids, dim=0).shape[0]) > 0.9 * N
