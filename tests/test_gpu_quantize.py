@@ -260,3 +260,46 @@ def test_c1_full_corpus_get_semantic_ids():
     # k-means-initialised codebooks are all in use at level 0 and most tuples are distinct
     assert int(torch.unique(out2.sem_ids[:, 0]).numel()) >= 250
     assert int(torch.unique(out2.sem_ids, dim=0).shape[0]) > 0.9 * N
+
+
+def test_full_size_properties_c5():
+    """BASELINE config 5 shape (4 levels x 1024 codes, d=64, 65,536 items per GPU), ROTATION_TRICK and
+    GUMBEL_SOFTMAX (in-kernel Philox noise): size-independent invariants of forward and backward."""
+    B, D, K, L = 65536, 64, 1024, 4
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(B, D, generator=g)
+    cbs = torch.stack(synthetic_codebooks(x[:20000], L, K, seed=6)).to(DEV)
+    xd = x.to(DEV)
+    g_emb = (torch.randn(L, B, D, generator=g) * 0.01).to(DEV)
+    g_loss = torch.full((B,), 1.0 / B, device=DEV)
+    _, _, ids_eval, _ = RF.quantize_forward(xd, cbs, O.MODE_EVAL)
+    for mode in (O.MODE_ROTATION_TRICK, O.MODE_GUMBEL_SOFTMAX):
+        kw = dict(seed=11, offset=3) if mode == O.MODE_GUMBEL_SOFTMAX else {}
+        emb, res, ids, loss = RF.quantize_forward(xd, cbs, mode, 0.25, 0.2, **kw)
+        assert int(ids.min()) >= 0 and int(ids.max()) < K
+        assert torch.equal(res[0], xd)
+        assert torch.equal(ids[0], ids_eval[0])              # ids are argmin(dist) in every mode (quantize.py:121)
+        for l in range(L - 1):                               # residual chain, rqvae.py:129 — exact
+            assert torch.equal(res[l + 1], res[l] - emb[l])
+        if mode == O.MODE_ROTATION_TRICK:
+            assert torch.equal(ids, ids_eval)
+            e = torch.stack([cbs[l][ids[l]] for l in range(L)])
+            assert_close(emb, e, "rotation value ~ codeword", tol=1e-4)
+        else:
+            e = emb                                          # Gumbel: the loss is taken against the soft embedding
+            # the soft embedding is a convex combination of the level's codewords
+            lo, hi = cbs.min(dim=1).values[:, None, :], cbs.max(dim=1).values[:, None, :]
+            assert bool(((emb >= lo - 1e-4) & (emb <= hi + 1e-4)).all())
+        want = sum(1.25 * ((res[l] - e[l]) ** 2).sum(-1) for l in range(L))
+        assert_close(loss, want, "loss identity", tol=1e-4)
+        emb2, _, ids2, loss2 = RF.quantize_forward(xd, cbs, mode, 0.25, 0.2, **kw)
+        assert torch.equal(ids, ids2) and torch.equal(emb, emb2) and torch.equal(loss, loss2)
+        g_x, g_cb = RF.quantize_backward(g_emb, None, g_loss, res, ids, cbs, mode, 0.25, 0.2, **kw)
+        assert bool(torch.isfinite(g_x).all()) and bool(torch.isfinite(g_cb).all())
+        assert float(g_cb.abs().sum()) > 0 and float(g_x.abs().sum()) > 0
+        if mode == O.MODE_ROTATION_TRICK:
+            # codes nobody selected receive no gradient
+            for l in range(L):
+                unused = torch.ones(K, dtype=torch.bool, device=DEV)
+                unused[ids[l]] = False
+                assert float(g_cb[l][unused].abs().sum()) == 0.0
