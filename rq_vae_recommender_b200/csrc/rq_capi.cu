@@ -45,7 +45,7 @@ extern "C" const char* rq_last_error(void) { return g_err; }
 extern "C" uint64_t rq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int rq_tcgen05_supported(int D, int K, int L, int mode, int distance) {
-    return tc_supported(D, K, L, mode, distance) ? 1 : 0;
+    return (tc_supported(D, K, L, mode, distance) || tc64_bigk_supported(D, K, L, mode, distance)) ? 1 : 0;
 }
 
 extern "C" int rq_quantize_forward(const float* x, const float* codebooks, int64_t B, int D, int K, int L, int mode,
@@ -68,7 +68,10 @@ extern "C" int rq_quantize_forward(const float* x, const float* codebooks, int64
     p.emb = emb_out; p.res = residuals; p.ids = ids; p.loss = loss; p.KC = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // the tcgen05 family stages the codebooks with TMA bulk copies (16-byte aligned source rows)
-    const bool tc_ok = tc_supported(D, K, L, mode, distance) && (((uintptr_t)codebooks & 15) == 0) && (((uintptr_t)x & 31) == 0);
+    const bool aligned = (((uintptr_t)codebooks & 15) == 0) && (((uintptr_t)x & 31) == 0);
+    const bool tc_ok = tc_supported(D, K, L, mode, distance) && aligned;
+    if (tc64_bigk_supported(D, K, L, mode, distance) && aligned && (impl == RQ_IMPL_TCGEN05 || (impl == RQ_IMPL_AUTO && B >= 2048)))
+        return quantize_forward_tc64_bigk(p, st);
     if (impl == RQ_IMPL_TCGEN05) {
         RQ_CHECK_ARG(tc_ok, RQ_ERR_UNSUPPORTED_SHAPE,
                      "rq_quantize_forward: (D=%d,K=%d,L=%d,mode=%d,dist=%d) is not served by the tcgen05 family", D, K, L,
@@ -163,6 +166,16 @@ static cudaMemPool_t host_entry_pool() {
     }
     return pools[dev];
 }
+namespace rq {
+void* engine_pool_alloc(size_t bytes, cudaStream_t st) {
+    void* ptr = nullptr;
+    cudaMemPool_t pool = host_entry_pool();
+    cudaError_t e = pool ? cudaMallocFromPoolAsync(&ptr, bytes, pool, st) : cudaMallocAsync(&ptr, bytes, st);
+    if (e != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return ptr;
+}
+}  // namespace rq
+
 static cudaError_t host_entry_alloc(void** p, size_t bytes, cudaStream_t st) {
     cudaMemPool_t pool = host_entry_pool();
     return pool ? cudaMallocFromPoolAsync(p, bytes, pool, st) : cudaMallocAsync(p, bytes, st);

@@ -22,6 +22,12 @@ struct FwdParams {
     // stored at ids[] (all rows when !has_prev).  nullptr = off.
     unsigned long long* n_changed = nullptr;
     int has_prev = 0;
+    // optional [B]: exact fp32 distance (SIMT arithmetic) of the id chosen at the LAST level — lets a caller merge
+    // the winners of several codebook chunks (rq_quantize_bigk.cu).  nullptr = off.  tcgen05 d=64 family only.
+    float* best_dist = nullptr;
+    // > 1: the launch covers `n_chunks` consecutive 256-code chunks of ONE codebook of `K` codes (L must be 1):
+    // CTA b serves chunk b % n_chunks, ids / best_dist of chunk c are written at offset c * B.
+    int n_chunks = 1;
 };
 
 struct BwdParams {
@@ -70,5 +76,9 @@ int quantize_forward_tc32(const FwdParams& p, cudaStream_t st);
 bool tc64_supported(int D, int K, int L, int mode, int distance);
 int quantize_forward_tc64(const FwdParams& p, cudaStream_t st);
 int tc64_timeout_flag();
+// K > 256 at D = 64: level-major composition of the d=64 kernel over 256-code chunks (rq_quantize_bigk.cu)
+bool tc64_bigk_supported(int D, int K, int L, int mode, int distance);
+int quantize_forward_tc64_bigk(const FwdParams& p, cudaStream_t st);
+void* engine_pool_alloc(size_t bytes, cudaStream_t st);     // library-owned stream-ordered pool (rq_capi.cu)
 
 }  // namespace rq

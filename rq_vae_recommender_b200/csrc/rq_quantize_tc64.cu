@@ -108,10 +108,9 @@ struct Tc64Params {
 
 __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Params P) {
     using namespace tc64;
-    const FwdParams& p = P.f;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
-    const SmemLayout S = smem_layout(p.L);
+    const SmemLayout S = smem_layout(P.f.L);
     uint8_t* sB = smem + S.b_tiles;
     uint8_t* sA = smem + S.a_tiles;
     uint8_t* sCCt = smem + S.cc_tiles;
@@ -124,6 +123,16 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wg = tid >> 7, wtid = tid & 127;
+    // chunked launch (rq_quantize_bigk.cu): this CTA scores every row against ONE 256-code chunk of the codebook
+    const int n_chunks = P.f.n_chunks, chunk = (int)blockIdx.x % n_chunks;
+    const int cta = (int)blockIdx.x / n_chunks, n_cta = (int)gridDim.x / n_chunks;   // position among the chunk's CTAs
+    FwdParams p = P.f;
+    if (n_chunks > 1) {
+        p.cb = P.f.cb + (int64_t)chunk * KC * D;
+        p.K = (P.f.K - chunk * KC < KC) ? (P.f.K - chunk * KC) : KC;
+        p.ids = P.f.ids + (int64_t)chunk * P.f.B;
+        p.best_dist = P.f.best_dist ? P.f.best_dist + (int64_t)chunk * P.f.B : nullptr;
+    }
 
     if (tid == 0) {
         ptx::mbar_init(&mbar_full[0], 1);
@@ -133,11 +142,11 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
     if (warp == 1) ptx::tmem_alloc(tmem_base_s, 512);
 
     // ---- first tile's rows: loads in flight during the prologue ------------------------------------------
-    const int my_tiles = (P.n_tiles > (int)blockIdx.x) ? (P.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    const int my_tiles = (P.n_tiles > cta) ? (P.n_tiles - 1 - cta) / n_cta + 1 : 0;
     const int n_mine = (my_tiles > wg) ? (my_tiles - 1 - wg) / NWG + 1 : 0;
     float r[D];
     {
-        const int64_t row = ((int64_t)blockIdx.x + (int64_t)gridDim.x * wg) * TILE_M + wtid;
+        const int64_t row = ((int64_t)cta + (int64_t)n_cta * wg) * TILE_M + wtid;
         if (n_mine > 0 && row < p.B) {
 #pragma unroll
             for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + row * D + j, &r[j]);
@@ -226,7 +235,7 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
     int use = 0;
 
     for (int it = 0; it < n_mine; ++it) {
-        const int tile = (int)blockIdx.x + (int)gridDim.x * (wg + NWG * it);
+        const int tile = cta + n_cta * (wg + NWG * it);
         const int64_t row = (int64_t)tile * TILE_M + wtid;
         const bool active = row < p.B;
         float xx = dot_self<D>(r);
@@ -407,6 +416,18 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
                 }
                 if (active) *dst = bi;
             }
+            if (p.best_dist && l == p.L - 1) {
+                // exact distance of the winner, the SIMT family's arithmetic (sequential fmaf chain)
+                const float4* c4 = reinterpret_cast<const float4*>(cbl + (int64_t)bi * D);
+                float a = 0.f;
+#pragma unroll
+                for (int j = 0; j < D / 4; ++j) {
+                    const float4 cv = __ldg(c4 + j);
+                    a = fmaf(r[4 * j], cv.x, a); a = fmaf(r[4 * j + 1], cv.y, a);
+                    a = fmaf(r[4 * j + 2], cv.z, a); a = fmaf(r[4 * j + 3], cv.w, a);
+                }
+                if (active) p.best_dist[row] = (xx + sCC[l * KC + bi]) - 2.f * a;
+            }
             // ids-only launches (tokenisation, k-means assignment) need nothing past the id at the last level
             if (l == p.L - 1 && !p.emb && !p.loss) continue;
             float e[D];
@@ -422,7 +443,7 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
         }
         if (active && p.loss) p.loss[row] = loss_acc;
         if (it + 1 < n_mine) {
-            const int64_t nrow = ((int64_t)blockIdx.x + (int64_t)gridDim.x * (wg + NWG * (it + 1))) * TILE_M + wtid;
+            const int64_t nrow = ((int64_t)cta + (int64_t)n_cta * (wg + NWG * (it + 1))) * TILE_M + wtid;
             if (nrow < p.B) {
 #pragma unroll
                 for (int j = 0; j < D; j += 8) ptx::ld_global_v8(p.x + nrow * D + j, &r[j]);
@@ -469,7 +490,14 @@ int quantize_forward_tc64(const FwdParams& p, cudaStream_t st) {
         RQ_CUDA(cudaFuncSetAttribute(rq_fwd_tc64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
-    const int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
+    int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
+    if (p.n_chunks > 1) {
+        // equal share of the SMs per chunk (at least one CTA each)
+        int per = sm_count() / p.n_chunks;
+        if (per < 1) per = 1;
+        if (per > P.n_tiles) per = P.n_tiles;
+        grid = per * p.n_chunks;
+    }
     rq_fwd_tc64_kernel<<<grid, tc64::THREADS, S.total + 1024, st>>>(P);
     RQ_LAUNCHED();
     return 0;

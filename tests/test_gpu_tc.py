@@ -22,8 +22,9 @@ def _inputs(B, K, L, seed, scale=1.0, D=32):
 def test_tc_is_selected_for_the_headline_shape():
     assert _lib.lib().rq_tcgen05_supported(32, 256, 3, RF.MODE_ROTATION_TRICK, RF.DIST_L2) == 1
     assert _lib.lib().rq_tcgen05_supported(64, 256, 3, RF.MODE_EVAL, RF.DIST_L2) == 1      # ml32m shape
-    assert _lib.lib().rq_tcgen05_supported(64, 256, 4, RF.MODE_EVAL, RF.DIST_L2) == 0      # operand tiles do not fit
-    assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_ROTATION_TRICK, RF.DIST_L2) == 0
+    assert _lib.lib().rq_tcgen05_supported(64, 256, 4, RF.MODE_EVAL, RF.DIST_L2) == 1      # level-major composition
+    assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_ROTATION_TRICK, RF.DIST_L2) == 1   # config 5 shape
+    assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_GUMBEL_SOFTMAX, RF.DIST_L2) == 0
     assert _lib.lib().rq_tcgen05_supported(32, 256, 3, RF.MODE_EVAL, RF.DIST_COSINE) == 0
 
 
@@ -159,3 +160,25 @@ def test_tc64_codebook_scale_extremes():
     _, _, i2, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_TCGEN05)
     assert _lib.lib().rq_debug_tc_timeout_flag() == 0
     assert torch.equal(i1, i2)
+
+
+# ---- D = 64, K > 256 or L > 3: level-major composition over 256-code chunks (rq_quantize_bigk.cu) ------------------
+@pytest.mark.parametrize("B,K,L", [(300, 1024, 4), (5000, 1000, 2), (20000, 512, 3), (4097, 256, 4), (1, 1024, 1),
+                                    (65536, 1024, 4)])
+def test_tc64_bigk_ids_bit_identical_to_simt(B, K, L):
+    x, cbs = _inputs(B, K, L, seed=B % 1000 + K + 7, D=64)
+    xd, cd = x.to(DEV), torch.stack(cbs).to(DEV)
+    for mode in (RF.MODE_EVAL, RF.MODE_ROTATION_TRICK, RF.MODE_STE):
+        e1, r1, i1, l1 = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_SIMT)
+        e2, r2, i2, l2 = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_TCGEN05)
+        torch.cuda.synchronize()
+        assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+        n_bad = int((i1 != i2).sum())
+        assert n_bad == 0, f"mode {mode}: {n_bad} ids differ between the chunked tcgen05 path and the SIMT family"
+        assert_close(e2, e1, "emb", tol=1e-6)
+        assert_close(r2, r1, "res", tol=1e-6)
+        assert_close(l2, l1, "loss", tol=1e-6)
+    _, _, i3, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
+                                      want_loss=False, impl=RF.IMPL_TCGEN05)
+    _, _, i1, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_SIMT)
+    assert torch.equal(i1, i3)
