@@ -171,16 +171,17 @@ out["kmeans_level_iteration_10M_d32_k256"]["assign_only_ms"] = ms_assign
 ms_simt = timed(lambda: RF.kmeans_assign_accumulate(x, c, assign, impl=RF.IMPL_SIMT), 2, warm=1)
 out["kmeans_level_iteration_10M_d32_k256"]["simt_family_ms"] = ms_simt
 del x, assign
-# ---- C5-like: 4 x 1024, d = 64 training step (SIMT family) ---------------------------------------------------
-B, D, K, L = 16384, 64, 1024, 4
-x = torch.randn(B, D, device=dev)
+# ---- C5-like: 4 x 1024, d = 64 training step (rotation: chunked tcgen05 forward; Gumbel: SIMT family) ---------------
+D, K, L = 64, 1024, 4
 cb = codebooks(L, K, D)
-g_emb = torch.randn(L, B, D, device=dev) * 0.01
-g_loss = torch.full((B,), 1.0 / B, device=dev)
-for name, mode in (("rotation", RF.MODE_ROTATION_TRICK), ("gumbel", RF.MODE_GUMBEL_SOFTMAX)):
-    def step():
+for B in (16384, 65536):
+    x = torch.randn(B, D, device=dev)
+    g_emb = torch.randn(L, B, D, device=dev) * 0.01
+    g_loss = torch.full((B,), 1.0 / B, device=dev)
+    for name, mode in (("rotation", RF.MODE_ROTATION_TRICK), ("gumbel", RF.MODE_GUMBEL_SOFTMAX)):
         emb, res, ids, loss = RF.quantize_forward(x, cb, mode, 0.25, 0.2, seed=1, offset=2)
-        RF.quantize_backward(g_emb, None, g_loss, res, ids, cb, mode, 0.25, 0.2, seed=1, offset=2)
-    ms = timed(step, 3, warm=1)
-    out[f"train_step_{name}_4x1024_d64"] = {"items": B, "ms": ms, "items_per_s": B / (ms * 1e-3)}
+        f = timed(lambda: RF.quantize_forward(x, cb, mode, 0.25, 0.2, seed=1, offset=2), 3, warm=1)
+        b = timed(lambda: RF.quantize_backward(g_emb, None, g_loss, res, ids, cb, mode, 0.25, 0.2, seed=1, offset=2), 3, warm=1)
+        out[f"train_step_{name}_4x1024_d64_B{B}"] = {"items": B, "fwd_ms": f, "bwd_ms": b, "ms": f + b,
+                                                     "items_per_s": B / ((f + b) * 1e-3)}
 print(json.dumps(out, indent=1))
