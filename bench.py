@@ -12,7 +12,9 @@ Weak scaling: every rank processes its own 65,536-row batch per step.
 
 `value`   : device-resident inputs, CUDA-event timed, max over ranks.
 `e2e`     : the same step through the public module API (`RqVae.quantize_latents` + autograd) with the
-            batch in pinned HOST memory: H2D of the latents and D2H of (loss, sem_ids) every step.
+            batch in pinned HOST memory: H2D of the latents and D2H of (loss, sem_ids) every step; the module's
+            forward + backward are captured once per static input (torch.cuda.graph) and the host reads each
+            step's result one step behind the launch front.
 `roofline`: the dominant kernel's algorithmic bytes / its mean launch duration (CUDA events inside the
             timed region) against MEASURED_PEAKS.json.
 `cpu_baseline` / `--impl reference`: the CPU restatement of the reference's quantiser (oracle/, the same
@@ -354,17 +356,11 @@ def run_engine(args):
             model.layers[l].embedding.weight.copy_(cbs[l])
     model.train()
     xs_pin = [t.pin_memory() for t in xs_h]
-    loss_pin = torch.empty(B_PER_GPU, dtype=torch.float32).pin_memory()
-    ids_pin = torch.empty((L, B_PER_GPU), dtype=torch.int64).pin_memory()
 
-    # batches arrive through the package's DevicePrefetcher (data/utils.py): the H2D copy of step i+1
-    # runs on its own stream while step i is quantised; both are inside the timed region.
-    feed = R.data.utils.DevicePrefetcher(R.data.utils.cycle(xs_pin), dev)
     g_embs_bdl = [g.permute(1, 2, 0) for g in g_embs]                           # views, [B,D,L] like the output
 
     class QuantizeLatents(torch.nn.Module):
-        """The quantiser part of RqVae.forward (rqvae.py:121-138) as a module, so that PyTorch's own
-        torch.cuda.make_graphed_callables can replay its forward and backward as CUDA graphs."""
+        """The quantiser part of RqVae.forward (rqvae.py:121-138) as a module."""
 
         def __init__(self, rqvae, temp):
             super().__init__()
@@ -375,38 +371,91 @@ def run_engine(args):
             return out.embeddings, out.sem_ids, out.quantize_loss
 
     quantizer = QuantizeLatents(model, TEMP)
-    e2e_mode = "eager module call"
-    if use_graphs:
-        try:
-            quantizer = torch.cuda.make_graphed_callables(quantizer, (xs[0].clone().requires_grad_(True),),
-                                                           allow_unused_input=True)
-            e2e_mode = "torch.cuda.make_graphed_callables(module)"
-        except Exception as ex:                                               # keep the number, say how it was made
-            e2e_mode = f"eager module call (graph capture failed: {type(ex).__name__}: {str(ex)[:300]})"
-
     q_params = [prm for prm in model.parameters() if prm.requires_grad]
+    E2E_SLOTS = 2
+    # Batches arrive through the package's DevicePrefetcher (data/utils.py): the H2D copy of step i+1 runs on its
+    # own stream, straight into the static input of the step that will consume it, while step i is quantised.
+    lat_static = [torch.empty(B_PER_GPU, D, device=dev).requires_grad_(True) for _ in range(E2E_SLOTS)]
+    loss_pin = [torch.empty(B_PER_GPU, dtype=torch.float32).pin_memory() for _ in range(E2E_SLOTS)]
+    ids_pin = [torch.empty((L, B_PER_GPU), dtype=torch.int64).pin_memory() for _ in range(E2E_SLOTS)]
+    done = [torch.cuda.Event() for _ in range(E2E_SLOTS)]
 
-    def e2e_step(i):
-        s = i % N_SLOTS
-        lat = next(feed).requires_grad_(True)                                   # H2D, 8 MiB (prefetched)
-        emb, sem_ids, qloss = quantizer(lat)
+    def module_step(s):
+        """forward + backward of the module on slot s's static input (the user's training-step calls)"""
         for prm in q_params:                                                    # zero_grad(set_to_none=True)
             prm.grad = None
+        lat_static[s].grad = None
+        emb, sem_ids, qloss = quantizer(lat_static[s])
         torch.autograd.backward([emb, qloss], [g_embs_bdl[s], g_loss])
+        return sem_ids, qloss, [prm.grad for prm in q_params]
+
+    e2e_mode = "eager module call"
+    e2e_graphs = None
+    if use_graphs:
+        # PyTorch's whole-step capture recipe: warm up on a side stream, then capture forward + backward of the
+        # module once per static input and replay (eager, the ~25 Python-dispatched ops of the step cost ~430 us of
+        # host time for ~55 us of kernels)
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    for s in range(E2E_SLOTS):
+                        module_step(s)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            e2e_graphs, e2e_outs = [], []
+            for s in range(E2E_SLOTS):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    out = module_step(s)
+                e2e_graphs.append(g)
+                e2e_outs.append(out)
+            e2e_mode = "torch.cuda.graph(module forward + autograd backward), one graph per static input"
+        except Exception as ex:                                               # keep the number, say how it was made
+            e2e_graphs = None
+            e2e_mode = f"eager module call (graph capture failed: {type(ex).__name__}: {str(ex)[:300]})"
+            torch.cuda.synchronize()
+
+    feed = R.data.utils.DevicePrefetcher(R.data.utils.cycle(xs_pin), dev, into=lat_static)
+
+    def e2e_step(i):
+        s = i % E2E_SLOTS
+        lat = next(feed)                                                        # H2D, 8 MiB (prefetched)
+        assert lat is lat_static[s]
+        if e2e_graphs is not None:
+            e2e_graphs[s].replay()
+            sem_ids, qloss, grads = e2e_outs[s]
+            for prm, gr in zip(q_params, grads):                                # what the optimizer would read
+                prm.grad = gr
+        else:
+            sem_ids, qloss, grads = module_step(s)
         if world > 1:
             R.parallel.allreduce_codebook_grads(model)
-        loss_pin.copy_(qloss.detach(), non_blocking=True)                       # D2H
-        ids_pin.copy_(sem_ids.detach().t(), non_blocking=True)                  # D2H
-        torch.cuda.current_stream().synchronize()                               # the caller reads the result
+        loss_pin[s].copy_(qloss.detach(), non_blocking=True)                    # D2H
+        ids_pin[s].copy_(sem_ids.detach().t(), non_blocking=True)               # D2H
+        done[s].record()
+        # the caller reads results one step behind the launch front (the usual asynchronous logging of a
+        # training loop): step i-1's loss and ids are complete on the host here, while step i runs
+        if i > 0:
+            done[(i - 1) % E2E_SLOTS].synchronize()
 
     for i in range(max(3, args.warmup)):
         e2e_step(i)
     fence()
+    n_warm = max(3, args.warmup)
     t0 = time.perf_counter()
     for i in range(args.steps):
-        e2e_step(args.warmup + i)
-    fence()
+        e2e_step(n_warm + i)
+    fence()                                                                     # the last step's result has landed
     e2e_s = time.perf_counter() - t0
+    # outside the timed region: the last step's host-side result equals a direct launch on the same batch
+    j_last = n_warm + args.steps - 1
+    _, _, ids_chk, loss_chk = RF.quantize_forward(xs_pin[j_last % len(xs_pin)].to(dev), cbs, mode, BETA, TEMP)
+    e2e_ok = bool(torch.equal(ids_pin[j_last % E2E_SLOTS], ids_chk.cpu()) and
+                  torch.allclose(loss_pin[j_last % E2E_SLOTS], loss_chk.cpu(), rtol=1e-5, atol=1e-7))
+    if not e2e_ok:
+        raise RuntimeError("e2e: the pipelined step's host result differs from a direct launch on the same batch")
 
     # ---- side numbers (outside the timed region): ids-only tokenisation launch -------------------
     ids_fn = lambda s: RF.quantize_forward(xs[s], cbs, RF.MODE_EVAL, want_embeddings=False,  # noqa: E731
@@ -456,7 +505,8 @@ def run_engine(args):
             "extra": {"fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "ids_only_ms": ids_only_ms,
                       "ids_only_items_per_s": B_PER_GPU / (ids_only_ms * 1e-3),
                       "fwd_items_per_s": B_PER_GPU / (fwd_ms * 1e-3),
-                      "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode},
+                      "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode,
+                      "e2e_result_checked": e2e_ok},
         }
         if not args.no_cpu_baseline and world == 1:
             ips, ms, cores = cpu_reference_run(args.cpu_sample_items, 3, 1)

@@ -53,11 +53,18 @@ class DevicePrefetcher:
     works but the copy then blocks the host).  Each `next()` (1) makes the consumer's current
     stream wait for the copy of the batch it returns, (2) starts the copy of the following batch on
     the prefetcher's stream, and returns.  Buffers are handed to the caching allocator with
-    `record_stream`, so a batch's memory is not reused while the consumer stream still reads it."""
+    `record_stream`, so a batch's memory is not reused while the consumer stream still reads it.
 
-    def __init__(self, source: Iterable, device, depth: int = 1):
+    `into` (tensor batches only): a ring of at least depth + 1 preallocated device tensors the batches are
+    copied into, in order — the static inputs of CUDA-graph-captured steps, which must not move.  Before a
+    buffer is overwritten the copy stream waits for everything the consumer stream had been given when the
+    copy was issued, which includes the step that last read that buffer."""
+
+    def __init__(self, source: Iterable, device, depth: int = 1, into=None):
         if depth < 1:
             raise ValueError("depth must be >= 1")
+        if into is not None and len(into) < depth + 1:
+            raise ValueError("into needs at least depth + 1 buffers")
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("DevicePrefetcher feeds the CUDA engine; got device " + str(device))
@@ -66,6 +73,8 @@ class DevicePrefetcher:
         self._queue = []
         self._free_events = []
         self._depth = depth
+        self._into = list(into) if into is not None else None
+        self._n_issued = 0
         for _ in range(depth):
             self._issue()
 
@@ -76,9 +85,18 @@ class DevicePrefetcher:
             return
         # events are recycled (creating one costs more than recording it)
         ev = self._free_events.pop() if self._free_events else torch.cuda.Event()
-        with torch.cuda.stream(self._stream):
-            dev = batch_to(host, self.device, non_blocking=True)
-            ev.record(self._stream)
+        if self._into is not None:
+            dev = self._into[self._n_issued % len(self._into)]
+            self._n_issued += 1
+            # the consumer's earlier reads of this buffer come first
+            self._stream.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self._stream), torch.no_grad():
+                dev.copy_(host, non_blocking=True)
+                ev.record(self._stream)
+        else:
+            with torch.cuda.stream(self._stream):
+                dev = batch_to(host, self.device, non_blocking=True)
+                ev.record(self._stream)
         self._queue.append((dev, ev))
 
     def __iter__(self):
@@ -91,6 +109,7 @@ class DevicePrefetcher:
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(ev)
         self._free_events.append(ev)
-        _record_stream(dev, cur)
+        if self._into is None:
+            _record_stream(dev, cur)
         self._issue()
         return dev

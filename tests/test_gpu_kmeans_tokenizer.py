@@ -220,6 +220,21 @@ def test_device_prefetcher_orders_and_completes():
     assert got == [0.0, 1.0, 2.0, 3.0, 4.0]
     it = U.DevicePrefetcher(U.cycle(host[:2]), DEV)
     assert [int(next(it)[0].item()) for _ in range(5)] == [0, 1, 0, 1, 0]
+    # static ring (`into`): the batches land in the given buffers in turn, and a buffer is not overwritten
+    # before the consumer stream's earlier reads of it (a long-running reduction here) have run
+    bufs = [torch.empty(1 << 20, device=DEV) for _ in range(2)]
+    it = U.DevicePrefetcher(U.cycle(host), DEV, into=bufs)
+    sums = []
+    for i in range(7):
+        t = next(it)
+        assert t is bufs[i % 2]
+        acc = t.double()
+        for _ in range(20):
+            acc = acc * 1.0 + 0.0
+        sums.append(acc.sum())
+    assert [float(v.item()) / (1 << 20) for v in sums] == [float(i % 5) for i in range(7)]
+    with pytest.raises(ValueError):
+        U.DevicePrefetcher(host, DEV, depth=2, into=bufs)
 
 
 def test_full_size_properties_c3_kmeans_10m():
