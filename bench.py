@@ -22,6 +22,8 @@ Weak scaling: every rank processes its own 65,536-row batch per step.
             Python tree that does not travel to the GPU box.
 """
 import argparse
+import contextlib
+import io
 import json
 import os
 import sys
@@ -527,10 +529,24 @@ def run_engine(args):
 
 def main():
     args = parse()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_engine(args)
+    # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner, for one) is
+    # sent to stderr by pointing fd 1 at fd 2 for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(buf):
+            if args.impl == "reference":
+                run_reference(args)
+            else:
+                run_engine(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    sys.stdout.write(buf.getvalue())
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
