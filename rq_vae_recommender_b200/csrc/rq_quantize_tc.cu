@@ -79,7 +79,9 @@ struct TcParams {
     int* err;        // device flag: set when an mbarrier / lock wait timed out
     int n_tiles;
     float* dbg_acc;  // optional [128][256] dump of tile 0 / level 0's accumulator (tests only)
-    int dbg_flags;      // experiments only (RQ_TC_DBG_FLAGS): 1 = skip first x load, 2 = skip codebook TMA
+    int dbg_flags;      // experiments only (RQ_TC_DBG_FLAGS): 1 = skip first x load, 2 = skip codebook TMA,
+                        // 4 = per-CTA %globaltimer stamps at dbg_tl[2048 + 4 * blockIdx.x],
+                        // 8 = never take the re-scoring path, 32 = issue 2 of the 7 MMAs (timing what-ifs, wrong ids)
     long long* dbg_tl;  // optional [32 warps][64 marks] clock64 timeline of CTA 0 (profiling only)
 };
 #define RQ_TL(mark)                                                                           \
@@ -139,7 +141,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     float* sCC = reinterpret_cast<float*>(smem + S.cc_f32);
     uint64_t* mbar_full = reinterpret_cast<uint64_t*>(smem + S.misc);        // [4] accumulator ready (per warpgroup)
     uint64_t* mbar_free = reinterpret_cast<uint64_t*>(smem + S.misc + 32);   // [2] accumulator read out (per slot)
-    uint64_t* mbar_load = reinterpret_cast<uint64_t*>(smem + S.misc + 48);   // [1] codebook bulk copy landed
+    uint64_t* mbar_load = reinterpret_cast<uint64_t*>(smem + S.misc + 128);  // [MAX_L] a level's codebook bulk copy landed
     uint64_t* mbar_x = reinterpret_cast<uint64_t*>(smem + S.misc + 96);     // [4] x tile landed (per warpgroup)
     uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(smem + S.misc + 64);
     int* cmax_bits = reinterpret_cast<int*>(smem + S.misc + 80);             // [MAX_L] max ||c||^2 per level
@@ -148,6 +150,10 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     const int wg = tid >> 7, wtid = tid & 127;
     const int slot = wg & 1;
     RQ_TL(0);
+    if (P.dbg_tl && (P.dbg_flags & 4) && tid == 0) {       // per-CTA wall-clock stamps (profiling only)
+        P.dbg_tl[2048 + 4 * blockIdx.x] = (long long)ptx::globaltimer();
+        P.dbg_tl[2048 + 4 * blockIdx.x + 1] = (long long)ptx::smid();
+    }
 
     // ---- codebooks: one TMA bulk copy per level, fp32 rows straight into that level's B-tile space --------
     if (tid == 0) {
@@ -155,14 +161,17 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
         for (int i = 0; i < 4; ++i) ptx::mbar_init(&mbar_full[i], 1);
         ptx::mbar_init(&mbar_free[0], 4);
         ptx::mbar_init(&mbar_free[1], 4);
-        ptx::mbar_init(mbar_load, 1);
+#pragma unroll
+        for (int i = 0; i < MAX_L; ++i) ptx::mbar_init(&mbar_load[i], 1);
 #pragma unroll
         for (int i = 0; i < 4; ++i) ptx::mbar_init(&mbar_x[i], 1);
         ptx::fence_mbar_init();
         const uint32_t level_bytes = (uint32_t)p.K * D * 4;
-        ptx::mbar_arrive_expect_tx(mbar_load, (P.dbg_flags & 2) ? 0u : level_bytes * p.L);
-        for (int l = 0; l < p.L; ++l)
-            if (!(P.dbg_flags & 2)) ptx::bulk_g2s(sB + l * B_TILE_BYTES, p.cb + (int64_t)l * p.K * D, level_bytes, mbar_load);
+        // one barrier per level: level l is converted while the later levels are still in flight
+        for (int l = 0; l < p.L; ++l) {
+            ptx::mbar_arrive_expect_tx(&mbar_load[l], (P.dbg_flags & 2) ? 0u : level_bytes);
+            if (!(P.dbg_flags & 2)) ptx::bulk_g2s(sB + l * B_TILE_BYTES, p.cb + (int64_t)l * p.K * D, level_bytes, &mbar_load[l]);
+        }
     }
     RQ_TL(45);
     // ---- first tile's rows: HBM loads in flight during the whole prologue ------------------------------
@@ -206,9 +215,6 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     __syncthreads();                                   // barrier inits + cmax zeros visible
     RQ_TL(1);
     if (SHARE && wtid == 0 && n_mine > 0) issue_x_tile(((int64_t)blockIdx.x + (int64_t)gridDim.x * wg) * TILE_M);
-    if (!ptx::mbar_wait(mbar_load, 0)) {
-        if (P.err) atomicExch(P.err, 1);
-    }
     RQ_TL(2);
     // ---- in-place conversion: work item = (level, code, 8-element chunk); the four lanes of a code read
     // its 128-byte fp32 row and rewrite the same 128 bytes as [-2hi | -2lo] bf16 in the swizzled order ------
@@ -216,6 +222,10 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
         const int n_items = p.L * KC * 4;                          // multiple of 2 * THREADS
         constexpr int U = 2;                                       // items in flight per thread
         for (int i0 = tid; i0 < n_items; i0 += U * THREADS) {
+            // items i0 and i0 + THREADS belong to the same level (1024 items per level, U * THREADS divides 1024)
+            if (!ptx::mbar_wait(&mbar_load[i0 >> 10], 0)) {
+                if (P.err) atomicExch(P.err, 1);
+            }
             float cv[U][8];
 #pragma unroll
             for (int u = 0; u < U; ++u) {
@@ -398,7 +408,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
                 const int ak[6] = {0, 32, 64, 96, 0, 32};
                 const int bk[6] = {0, 32, 0, 32, 64, 96};
 #pragma unroll
-                for (int i = 0; i < 6; ++i) {
+                for (int i = 0; i < ((P.dbg_flags & 32) ? 1 : 6); ++i) {
                     uint64_t ad = ptx::make_smem_desc(a0 + ak[i], 16, 1024, ptx::kLayoutSw128);
                     uint64_t bd = ptx::make_smem_desc(b0 + bk[i], 16, 1024, ptx::kLayoutSw128);
                     ptx::umma_bf16(tmem_acc, ad, bd, idesc, i > 0);
@@ -503,7 +513,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
             // packing the index moves a value by < 2^-19 |v|: widen the band by 2^-17 |m1|
             const float m1 = fminf(m1a, m1b);
             const float thr = m1 + (tol + 8e-6f * fabsf(m1));
-            const bool ambiguous = (m2a <= thr) || (m2b <= thr);
+            const bool ambiguous = ((m2a <= thr) || (m2b <= thr)) && !(P.dbg_flags & 8);
             const float* cbl = p.cb + (int64_t)l * p.K * D;
             // the exact residual row comes back from its parking place
             if (SHARE) park_load_row(r);
@@ -615,6 +625,7 @@ __global__ void __launch_bounds__(128 * NWG, 1) rq_fwd_tc_kernel(TcParams P) {
     ptx::tc_fence_before_sync();
     __syncthreads();
     if (warp == 1) ptx::tmem_dealloc(tmem_base, 512);
+    if (P.dbg_tl && (P.dbg_flags & 4) && tid == 0) P.dbg_tl[2048 + 4 * blockIdx.x + 2] = (long long)ptx::globaltimer();
 }
 
 bool tc32_supported(int D, int K, int L, int mode, int distance) {

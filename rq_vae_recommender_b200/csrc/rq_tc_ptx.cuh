@@ -226,5 +226,16 @@ __device__ __forceinline__ void split_pair(float a, float b, uint32_t& hi, uint3
     lo = pack_hi16(la, lb);
 }
 
+__device__ __forceinline__ unsigned long long globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ uint32_t smid() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
+    return r;
+}
+
 }  // namespace ptx
 }  // namespace rq
