@@ -154,6 +154,20 @@ int rq_gather_tokens(const int64_t* table, int64_t n_rows, int W, const int64_t*
                      const uint8_t* seq_mask, int64_t n_tokens, int64_t* out, rq_stream_t stream);
 
 /*
+ * Id-diversity metrics of a finished corpus table.  Replaces the three torch.unique calls of the reference's
+ * eval block (train_rqvae.py:227-237):
+ *   entropy  = -sum_t p_t log p_t over the distinct L-tuples t, p_t = count_t / N      (rqvae_entropy)
+ *   used[l]  = number of distinct ids in column l            (codebook_usage_l = used[l] / codebook_size)
+ *   max_dup  = max of the dedup column                        (max_id_duplicates = max_dup / N)
+ * table [N, L+1] int64 contiguous = [ids | dedup] as written by rq_corpus_table; entropy [1] double, used [L]
+ * int64, max_dup [1] int64 on the device.  One pass, no sort: the entropy telescopes over the dedup column.
+ * workspace: rq_id_diversity_workspace_bytes(L, codebook_size) bytes (a bitmap; zeroed by the call).
+ */
+int64_t rq_id_diversity_workspace_bytes(int L, int64_t codebook_size);
+int rq_id_diversity(const int64_t* table, int64_t N, int L, int64_t codebook_size, double* entropy, int64_t* used,
+                    int64_t* max_dup, void* workspace, int64_t workspace_bytes, rq_stream_t stream);
+
+/*
  * Host-buffer convenience entry (the call a non-torch integrator makes): copies `x_host`
  * (pageable or pinned) to the device, runs rq_quantize_forward in RQ_MODE_EVAL, copies the ids
  * [L,B] (and loss [B] when non-NULL) back and returns when they are complete.  Rows are processed

@@ -267,6 +267,23 @@ def corpus_ids_table(sem_ids: np.ndarray) -> np.ndarray:
     return np.concatenate([sem_ids, corpus_dedup_column(sem_ids)[:, None]], axis=1)
 
 
+def id_diversity(corpus_ids: torch.Tensor, vae_n_layers: int, vae_codebook_size: int) -> dict:
+    """The eval-time id-diversity log, op for op as train_rqvae.py:227-237 computes it (torch.unique over the
+    tuple rows and over each column; float32 arithmetic)."""
+    corpus_ids = torch.as_tensor(corpus_ids)
+    log = {}
+    max_duplicates = corpus_ids[:, -1].max() / corpus_ids.shape[0]                      # :228
+    _, counts = torch.unique(corpus_ids[:, :-1], dim=0, return_counts=True)             # :230
+    p = counts / corpus_ids.shape[0]                                                    # :231
+    rqvae_entropy = -(p * torch.log(p)).sum()                                           # :232
+    for cid in range(vae_n_layers):                                                     # :234-236
+        _, counts = torch.unique(corpus_ids[:, cid], return_counts=True)
+        log[f"codebook_usage_{cid}"] = len(counts) / vae_codebook_size
+    log["rqvae_entropy"] = rqvae_entropy.cpu().item()                                   # :238
+    log["max_id_duplicates"] = max_duplicates.cpu().item()                              # :239
+    return log
+
+
 def exists_prefix(cached_ids: np.ndarray, prefix: np.ndarray, strict_reference_quirk: bool = False) -> np.ndarray:
     """semids.py:103-120.  `strict_reference_quirk=True` reproduces `math.ceil(n // 16)`
     (:114): only full chunks of 16 along dim 0 are evaluated, the remainder stays False."""

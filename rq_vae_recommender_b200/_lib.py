@@ -43,6 +43,9 @@ SIGNATURES = {
                                       c_void_p]),
     "rq_prefix_exists": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p]),
     "rq_gather_tokens": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "rq_id_diversity_workspace_bytes": (c_int64, [c_int, c_int64]),
+    "rq_id_diversity": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                c_void_p]),
     "rq_debug_tc_timeout_flag": (c_int, []),
     "rq_debug_tc_set_accumulator_dump": (c_int, [c_void_p]),
     "rq_debug_tc_set_timeline": (c_int, [c_void_p]),

@@ -7,6 +7,8 @@
 //  * prefix index  — exists_prefix (:103-120): sorted packed prefixes + binary search instead
 //    of a [16, n, N, p] broadcast compare.
 //  * token gather  — _tokenize_seq_batch_from_cached + padding fill (:122-123, :137-141).
+//  * id diversity  — the eval-time metrics train_rqvae.py:227-237 takes from three torch.unique calls
+//    (tuple entropy, per-level codebook usage, max duplicates): one pass over the finished table.
 //
 // The radix sort is cub::DeviceRadixSort (ships with the CUDA toolkit); everything around it
 // is hand-written.
@@ -214,6 +216,112 @@ extern "C" int rq_gather_tokens(const int64_t* table, int64_t n_rows, int W, con
     const int T = 256;
     int64_t total = n_tokens * W;
     gather_tokens_kernel<<<(unsigned)((total + T - 1) / T), T, 0, st>>>(table, n_rows, W, item_ids, seq_mask, n_tokens, out);
+    RQ_LAUNCHED();
+    return 0;
+}
+
+// ---- id diversity ----------------------------------------------------------------------------
+// entropy = -sum_t p_t log p_t over the distinct L-tuples t (p_t = n_t / N) needs no sort once the dedup column
+// exists: the items of a tuple carry dedup = 0 .. n_t - 1, and with f(n) = (n/N) log(n/N), f(0) = 0,
+//   f(n_t) = sum_{d=0}^{n_t-1} [f(d+1) - f(d)]   =>   entropy = -sum_items [f(dedup_i + 1) - f(dedup_i)].
+// usage: one bit per (level, id) in a CTA-private shared-memory bitmap, OR-ed into the global bitmap once per CTA.
+__global__ void id_diversity_kernel(const int64_t* __restrict__ table, int64_t N, int L, int64_t K, int words,
+                                    bool use_smem, double* __restrict__ entropy, unsigned long long* __restrict__ max_dup,
+                                    uint32_t* __restrict__ bitmap) {
+    extern __shared__ uint32_t s_bits[];
+    if (use_smem) {
+        for (int i = threadIdx.x; i < L * words; i += blockDim.x) s_bits[i] = 0u;
+        __syncthreads();
+    }
+    const double invN = 1.0 / (double)N;
+    double acc = 0.0;
+    unsigned long long mx = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t* row = table + i * (L + 1);
+        for (int l = 0; l < L; ++l) {
+            const int64_t v = row[l];
+            if (v >= 0 && v < K) {
+                const uint32_t bit = 1u << (v & 31);
+                uint32_t* w = (use_smem ? s_bits : bitmap) + l * words + (int)(v >> 5);
+                if (!(*w & bit)) atomicOr(w, bit);
+            }
+        }
+        const int64_t d = row[L];
+        const double a = (double)(d + 1) * invN, b = (double)d * invN;
+        acc += a * log(a) - (d > 0 ? b * log(b) : 0.0);
+        mx = (unsigned long long)d > mx ? (unsigned long long)d : mx;
+    }
+    // block reduction (double sum, max)
+    __shared__ double s_acc[32];
+    __shared__ unsigned long long s_mx[32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        const unsigned long long t = __shfl_xor_sync(0xffffffffu, mx, o);
+        mx = t > mx ? t : mx;
+    }
+    if ((threadIdx.x & 31) == 0) { s_acc[threadIdx.x >> 5] = acc; s_mx[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0;
+        unsigned long long m = 0;
+        for (int w = 0; w < (int)(blockDim.x + 31) / 32; ++w) { a += s_acc[w]; m = s_mx[w] > m ? s_mx[w] : m; }
+        atomicAdd(entropy, -a);
+        atomicMax(max_dup, m);
+    }
+    if (use_smem) {
+        for (int i = threadIdx.x; i < L * words; i += blockDim.x)
+            if (s_bits[i]) atomicOr(bitmap + i, s_bits[i]);
+    }
+}
+
+__global__ void id_usage_kernel(const uint32_t* __restrict__ bitmap, int L, int words, int64_t* __restrict__ used) {
+    const int l = blockIdx.x;
+    int c = 0;
+    for (int i = threadIdx.x; i < words; i += blockDim.x) c += __popc(bitmap[l * words + i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    __shared__ int s_c[32];
+    if ((threadIdx.x & 31) == 0) s_c[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < (int)(blockDim.x + 31) / 32; ++w) t += s_c[w];
+        used[l] = t;
+    }
+}
+
+
+extern "C" int64_t rq_id_diversity_workspace_bytes(int L, int64_t codebook_size) {
+    if (L < 1 || codebook_size < 1) return 0;
+    return (int64_t)L * ((codebook_size + 31) / 32) * 4;
+}
+
+extern "C" int rq_id_diversity(const int64_t* table, int64_t N, int L, int64_t codebook_size, double* entropy,
+                               int64_t* used, int64_t* max_dup, void* workspace, int64_t workspace_bytes,
+                               rq_stream_t stream) {
+    using namespace rq;
+    cudaStream_t st = (cudaStream_t)stream;
+    RQ_CHECK_ARG(N >= 1 && L >= 1 && codebook_size >= 1, RQ_ERR_INVALID_ARGUMENT,
+                 "rq_id_diversity: need N >= 1, L >= 1, codebook_size >= 1");
+    RQ_CHECK_ARG(table && entropy && used && max_dup && workspace, RQ_ERR_NULL_POINTER, "rq_id_diversity: null pointer");
+    const int64_t need = rq_id_diversity_workspace_bytes(L, codebook_size);
+    RQ_CHECK_ARG(workspace_bytes >= need, RQ_ERR_INVALID_ARGUMENT, "rq_id_diversity: workspace too small (%lld < %lld)",
+                 (long long)workspace_bytes, (long long)need);
+    const int words = (int)((codebook_size + 31) / 32);
+    RQ_CUDA(cudaMemsetAsync(workspace, 0, (size_t)need, st));
+    RQ_CUDA(cudaMemsetAsync(entropy, 0, sizeof(double), st));
+    RQ_CUDA(cudaMemsetAsync(max_dup, 0, sizeof(int64_t), st));
+    const bool use_smem = need <= 32 * 1024;
+    const int T = 256;
+    int64_t blocks = (N + T - 1) / T;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    id_diversity_kernel<<<(unsigned)blocks, T, use_smem ? (size_t)need : 0, st>>>(
+        table, N, L, codebook_size, words, use_smem, entropy, reinterpret_cast<unsigned long long*>(max_dup),
+        reinterpret_cast<uint32_t*>(workspace));
+    RQ_LAUNCHED();
+    id_usage_kernel<<<L, 256, 0, st>>>(reinterpret_cast<const uint32_t*>(workspace), L, words, used);
     RQ_LAUNCHED();
     return 0;
 }

@@ -175,6 +175,27 @@ def corpus_table(sem_ids: torch.Tensor, codebook_size: int) -> torch.Tensor:
     return table
 
 
+def id_diversity(table: torch.Tensor, codebook_size: int):
+    """[N,L+1] int64 corpus table -> (entropy [] float64, used [L] int64, max_dup [] int64), device tensors
+    (rq_id_diversity; train_rqvae.py:227-237)."""
+    L.require_cuda(table, "table", torch.int64)
+    table = table.contiguous()
+    N, W = table.shape
+    if N < 1 or W < 2:
+        raise L.RqEngineError("id_diversity: table must be [N >= 1, L + 1]")
+    dev = table.device
+    with torch.cuda.device(dev):
+        entropy = torch.empty((), device=dev, dtype=torch.float64)
+        used = torch.empty((W - 1,), device=dev, dtype=torch.int64)
+        max_dup = torch.empty((), device=dev, dtype=torch.int64)
+        nbytes = int(L.lib().rq_id_diversity_workspace_bytes(W - 1, int(codebook_size)))
+        ws = torch.empty((max(nbytes, 4),), device=dev, dtype=torch.uint8)
+        rc = L.lib().rq_id_diversity(L.ptr(table), N, W - 1, int(codebook_size), L.ptr(entropy), L.ptr(used),
+                                     L.ptr(max_dup), L.ptr(ws), nbytes, L.stream_of(table))
+    L.check(rc, "rq_id_diversity")
+    return entropy, used, max_dup
+
+
 def prefix_index(table: torch.Tensor, p: int, radix: int) -> torch.Tensor:
     """Sorted packed keys of table[:, :p] (uint64 stored in an int64 tensor)."""
     L.require_cuda(table, "table", torch.int64)

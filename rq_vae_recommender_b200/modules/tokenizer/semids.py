@@ -109,6 +109,21 @@ class SemanticIdTokenizer(nn.Module):
         self._prefix_index = {}
         return self.cached_ids
 
+    @torch.no_grad()
+    def id_diversity(self) -> dict:
+        """The id-diversity log of the reference's eval block (train_rqvae.py:227-237) from the cached table:
+        `rqvae_entropy`, `max_id_duplicates` and `codebook_usage_{level}` as Python floats.  The reference takes
+        them from three `torch.unique` calls (a sort each); here one pass over the table (rq_id_diversity)."""
+        if self.cached_ids is None:
+            raise Exception("No match can be found in empty cache.")            # as exists_prefix, semids.py:107
+        entropy, used, max_dup = RF.id_diversity(self.cached_ids, self.codebook_size)
+        n = self.cached_ids.shape[0]
+        vals = torch.cat([entropy.reshape(1), max_dup.reshape(1).double(), used.double()]).cpu()   # one host read
+        out = {f"codebook_usage_{cid}": float(vals[2 + cid]) / self.codebook_size for cid in range(self.n_layers)}
+        out["rqvae_entropy"] = float(torch.tensor(float(vals[0]), dtype=torch.float32))
+        out["max_id_duplicates"] = float(torch.tensor(float(vals[1]), dtype=torch.float32) / n)
+        return out
+
     def _index_for(self, p: int):
         if p not in self._prefix_index:
             # the dedup column can exceed codebook_size, so the packing radix covers the whole table

@@ -166,6 +166,38 @@ def test_corpus_table_vs_oracle(N, L, K):
     assert np.array_equal(RF.corpus_table(view, K).cpu().numpy(), table.cpu().numpy())
 
 
+@pytest.mark.parametrize("N,L,K", [(1, 3, 256), (100000, 3, 8), (250000, 4, 1024), (5000, 2, 3), (40000, 3, 100000)])
+def test_id_diversity_vs_oracle(N, L, K):
+    """rq_id_diversity against the torch.unique form of train_rqvae.py:227-237 (oracle.id_diversity): usage counts
+    and max duplicates exact, entropy to float32 rounding of the reference's own sum."""
+    g = torch.Generator().manual_seed(7 * N + L)
+    ids = torch.randint(0, K, (N, L), generator=g)
+    if N > 10:
+        ids[N // 2:N // 2 + 50] = ids[0]          # one heavy tuple
+        ids[:, L - 1] = ids[:, L - 1] % max(K // 2, 1)   # an under-used last level
+    table = RF.corpus_table(ids.to(DEV), K)
+    want = O.id_diversity(table.cpu(), L, K)
+    entropy, used, max_dup = RF.id_diversity(table, K)
+    for cid in range(L):
+        assert int(used[cid]) == round(want[f"codebook_usage_{cid}"] * K)
+    assert int(max_dup) == int(table[:, -1].max())
+    assert abs(float(entropy) - want["rqvae_entropy"]) <= 2e-5 * max(1.0, abs(want["rqvae_entropy"]))
+
+
+def test_tokenizer_id_diversity_log_keys():
+    """SemanticIdTokenizer.id_diversity returns the reference's log keys and values (train_rqvae.py:234-239)."""
+    tok = R.SemanticIdTokenizer(input_dim=24, output_dim=8, hidden_dims=[16], codebook_size=6, n_layers=3, n_cat_feats=0)
+    with pytest.raises(Exception):
+        tok.id_diversity()
+    ids = torch.randint(0, 6, (1300, 3), generator=torch.Generator().manual_seed(5))
+    tok.cached_ids = RF.corpus_table(ids.to(DEV), 6)
+    got = tok.id_diversity()
+    want = O.id_diversity(tok.cached_ids.cpu(), 3, 6)
+    assert set(got) == set(want)
+    for k in want:
+        assert abs(got[k] - want[k]) <= 1e-5 * max(1.0, abs(want[k])), k
+
+
 def test_c_abi_host_entry_point():
     """rq_semantic_ids_host: host buffers in, host buffers out, copies inside."""
     import ctypes

@@ -138,3 +138,17 @@ def test_tokenizer_semantic_ids_from_state_dict():
     lat = O.mlp_forward(torch.from_numpy(z["x"]), [sd["encoder.mlp.0.weight"], sd["encoder.mlp.2.weight"]], False)
     out = O.rq_forward(lat, [sd[f"layers.{l}.embedding.weight"] for l in range(3)], O.MODE_EVAL)
     assert np.array_equal(out.sem_ids.T.numpy(), z["cached_ids"][:, :3])
+
+
+def test_id_diversity_oracle_known_answer():
+    """oracle.id_diversity (train_rqvae.py:227-239) on a table whose answer is known in closed form: tuples with
+    multiplicities 3, 2, 1 out of 6 -> entropy = -(1/2 ln 1/2 + 1/3 ln 1/3 + 1/6 ln 1/6)."""
+    import math
+    ids = np.array([[0, 1], [0, 1], [2, 1], [0, 1], [2, 1], [3, 0]], dtype=np.int64)
+    table = torch.from_numpy(O.corpus_ids_table(ids).reshape(6, 3))
+    log = O.id_diversity(table, 2, 4)
+    want = -(0.5 * math.log(0.5) + (1 / 3) * math.log(1 / 3) + (1 / 6) * math.log(1 / 6))
+    assert abs(log["rqvae_entropy"] - want) < 1e-6
+    assert log["codebook_usage_0"] == 3 / 4 and log["codebook_usage_1"] == 2 / 4
+    assert abs(log["max_id_duplicates"] - 2 / 6) < 1e-7
+
