@@ -62,7 +62,7 @@ def peaks():
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
     `ncu --set full` extract under profiles/ (None when no capture of that kernel is committed)."""
-    name = {"rq_fwd": "r1_ncu_full_fwd_tc_v4.csv", "rq_bwd": "r1_ncu_full_bwd_row2_v5.csv"}.get(kernel)
+    name = {"rq_fwd": "r1_ncu_full_fwd_tc_v7.csv", "rq_bwd": "r1_ncu_full_bwd_row3_v7.csv"}.get(kernel)
     path = os.path.join(ROOT, "profiles", name) if name else None
     if not path or not os.path.exists(path):
         return None
