@@ -22,8 +22,6 @@ Weak scaling: every rank processes its own 65,536-row batch per step.
             Python tree that does not travel to the GPU box.
 """
 import argparse
-import contextlib
-import io
 import json
 import os
 import sys
@@ -192,7 +190,7 @@ def run_reference(args):
     ips, ms, cores = cpu_reference_run(n, steps, warm)
     cb = {"value": ips, "unit": "items/s", "cores": cores, "kind": "port",
           "sample": f"{steps} steps x {n} items fwd+bwd (oracle/rq_oracle.py, torch CPU ATen, fp32)"}
-    print(json.dumps({
+    emit(json.dumps({
         "impl": "reference", "metric": "items/sec semantic-ID quantize (3x256,d=32)", "value": ips,
         "unit": "items/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -515,7 +513,7 @@ def run_engine(args):
             out["cpu_baseline"] = {"value": ips, "unit": "items/s", "cores": cores, "kind": "port",
                                    "sample": f"3 steps x {args.cpu_sample_items} items fwd+bwd, oracle/rq_oracle.py "
                                              f"(torch CPU ATen fp32, {cores} threads)"}
-        print(json.dumps(out))
+        emit(json.dumps(out))
     if world > 1:
         # Captured NCCL all-reduces live inside the step graphs; tearing the communicator down under them
         # was seen to hang (2 ranks, NCCL 2.28.9).  Everything is measured and printed by now: drop the
@@ -527,26 +525,32 @@ def run_engine(args):
         os._exit(0)
 
 
+_REAL_STDOUT_FD = None
+
+
+def emit(line: str) -> None:
+    """The one JSON line goes straight to the process's original stdout (see main)."""
+    data = (line + "\n").encode()
+    if _REAL_STDOUT_FD is None:
+        sys.stdout.write(line + "\n")
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT_FD, data)
+
+
 def main():
+    global _REAL_STDOUT_FD
     args = parse()
     # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner, for one) is
-    # sent to stderr by pointing fd 1 at fd 2 for the duration of the run
+    # sent to stderr by pointing fd 1 at fd 2 for the duration of the run; emit() writes to the saved descriptor
+    # (the multi-rank path leaves through os._exit, so nothing may wait in a buffer)
     sys.stdout.flush()
-    real_stdout = os.dup(1)
+    _REAL_STDOUT_FD = os.dup(1)
     os.dup2(2, 1)
-    buf = io.StringIO()
-    try:
-        with contextlib.redirect_stdout(buf):
-            if args.impl == "reference":
-                run_reference(args)
-            else:
-                run_engine(args)
-    finally:
-        sys.stdout.flush()
-        os.dup2(real_stdout, 1)
-        os.close(real_stdout)
-    sys.stdout.write(buf.getvalue())
-    sys.stdout.flush()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_engine(args)
 
 
 if __name__ == "__main__":
