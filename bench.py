@@ -225,8 +225,17 @@ def run_engine(args):
         if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"          # NCCL prints its version banner on stdout otherwise
         dist.init_process_group("nccl", device_id=dev)
-        if "RQ_SM_RESERVE" not in os.environ:
-            R.parallel.reserve_sms_for_collectives(8)  # the all-reduce kernel runs beside the persistent grids
+    # N > 1: the codebook-gradient exchange is an async NCCL all-reduce beside the replayed graphs.  RQ_BENCH_PEER=1
+    # swaps in the engine's own one-shot all-reduce over peer-mapped memory (parallel.PeerAllReduce) on a side
+    # stream, RQ_BENCH_PEER=inline puts that kernel into the step graph right behind the backward.  Measured
+    # (us/step, N = 2 / 8): NCCL 53.8 / 58.8, peer side stream 57.8 / 62.2, peer inline 66.6 / 70.2 — NCCL stays
+    # the default.
+    peer_mode = os.environ.get("RQ_BENCH_PEER", "")
+    use_peer = world > 1 and bool(peer_mode) and R.parallel.PeerAllReduce.available()
+    peer_inline = use_peer and peer_mode == "inline"
+    if world > 1 and not peer_inline and "RQ_SM_RESERVE" not in os.environ:
+        # the exchange kernel runs beside the persistent grids, which otherwise fill every SM's register file
+        R.parallel.reserve_sms_for_collectives(4 if use_peer else 8)
     R.lib()
 
     xs_h, cbs_h, g_emb_h, g_loss_h = make_inputs(torch, dev, N_SLOTS, seed=100 + rank)
@@ -236,9 +245,18 @@ def run_engine(args):
     cbs = cbs_h.to(dev)
     mode = RF.MODE_ROTATION_TRICK
 
+    peer = R.parallel.PeerAllReduce((L, K, D), slots=N_SLOTS) if use_peer else None
+
     def step_compute(s):
         emb, res, ids, loss = RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP)
-        g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP)
+        if peer is not None:
+            # the backward scatters into slot s of the symmetric buffer; one more launch averages it over the ranks
+            g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP,
+                                             g_codebooks_out=peer.buffer[s])
+            if peer_inline:
+                peer.all_reduce_(s, average=True)
+        else:
+            g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP)
         return loss, g_x, g_cb
 
     # N > 1: the codebook-gradient all-reduce (98,304 B, the path's one exchange) runs on its own stream so
@@ -248,21 +266,41 @@ def run_engine(args):
     # ends, which serialises it with the kernels (measured at N = 4: 107-133 us/step in-graph vs 60 us beside).
     pending = []                                        # async NCCL work handles of the last steps
 
-    def allreduce_async(g_cb):
+    side = torch.cuda.Stream() if (peer is not None and not peer_inline) else None
+    slot_done = [None] * N_SLOTS                        # event of the last exchange launched on each slot
+    fork_ev = [torch.cuda.Event() for _ in range(N_SLOTS)]
+
+    def allreduce_async(g_cb, i=0):
+        if peer is not None:
+            if peer_inline:
+                return                                  # already reduced inside the step (and its graph)
+            s_ = i % N_SLOTS
+            fork_ev[s_].record()                          # the step's backward has been launched
+            side.wait_event(fork_ev[s_])
+            peer.all_reduce_(s_, average=True, stream=side)
+            ev = slot_done[s_] or torch.cuda.Event()
+            ev.record(side)
+            slot_done[s_] = ev
+            return
         # async_op: NCCL's own stream waits for the launching stream's work so far; the launching stream moves on
         pending.append(dist.all_reduce(g_cb, async_op=True))
 
-    def before_slot_reuse():
+    def before_slot_reuse(i=0):
+        if side is not None:
+            ev = slot_done[i % N_SLOTS]
+            if ev is not None:
+                torch.cuda.current_stream().wait_event(ev)   # the backward about to run overwrites that slot
+            return
         # the step about to run overwrites the gradient buffer reduced N_SLOTS steps ago: order it after that
         # reduction (long finished in practice, so the wait costs nothing)
         if len(pending) >= N_SLOTS:
             pending.pop(0).wait()
 
     def step(i):
-        before_slot_reuse()
+        before_slot_reuse(i)
         out = step_compute(i % N_SLOTS)
         if world > 1:
-            allreduce_async(out[2])
+            allreduce_async(out[2], i)
         return out
 
     def fence():
@@ -301,10 +339,10 @@ def run_engine(args):
         bwd_graphs, _keep3, _ = capture(lambda s: RF.quantize_backward(g_embs[s], None, g_loss, _fwd_out[s][1],
                                                                        _fwd_out[s][2], cbs, mode, BETA, TEMP))
         def run_step(i):
-            before_slot_reuse()
+            before_slot_reuse(i)
             step_graphs[i % N_SLOTS].replay()
             if world > 1:
-                allreduce_async(_keep1[i % N_SLOTS][2])
+                allreduce_async(_keep1[i % N_SLOTS][2], i)
         run_fwd = lambda i: fwd_graphs[i % N_SLOTS].replay()
         run_bwd = lambda i: bwd_graphs[i % N_SLOTS].replay()
         launch_mode = "cuda-graph replay (one graph per ring slot)"
@@ -327,6 +365,8 @@ def run_engine(args):
             fn(args.warmup + i)
         while pending:
             pending.pop(0).wait()                       # the last reductions are part of the K steps
+        if side is not None:
+            torch.cuda.current_stream().wait_stream(side)
         b.record()
         return a, b
 
@@ -506,6 +546,8 @@ def run_engine(args):
                       "ids_only_items_per_s": B_PER_GPU / (ids_only_ms * 1e-3),
                       "fwd_items_per_s": B_PER_GPU / (fwd_ms * 1e-3),
                       "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode,
+                      "grad_exchange": (None if world == 1 else ("rq_peer_allreduce_f32 (peer memory, " + ("in the step graph)" if peer_inline else "side stream beside the graphs)"))
+                                        if peer is not None else "NCCL all_reduce, async beside the graphs"),
                       "e2e_result_checked": e2e_ok},
         }
         if not args.no_cpu_baseline and world == 1:

@@ -168,6 +168,30 @@ int rq_id_diversity(const int64_t* table, int64_t N, int L, int64_t codebook_siz
                     int64_t* max_dup, void* workspace, int64_t workspace_bytes, rq_stream_t stream);
 
 /*
+ * One-shot all-reduce (sum * scale) of a small fp32 region over peer-mapped symmetric memory (NVLink loads, no
+ * NCCL): the codebook-gradient exchange of a training step, which the reference leaves to DDP
+ * (train_rqvae.py:115-117,153), and the k-means sums / counts exchange.  Capturable in a CUDA graph; every rank
+ * launches it with the same n_floats in the same order.
+ *   peer_bufs_dev   device array [world] of the ranks' allocation base pointers (rank order)
+ *   peer_pads_dev   device array [world] of the ranks' signal pads (zero-initialised uint32 words, at least
+ *                   rq_peer_allreduce_pad_bytes() each; words from 2048 on are used)
+ *   offset_floats, n_floats   the reduced region inside every allocation (multiples of 4, n_floats <=
+ *                   rq_peer_allreduce_max_floats())
+ *   out             local destination, 16-byte aligned; may be this rank's own region (written after every rank
+ *                   has finished reading)
+ *   epoch_dev       device-local zero-initialised uint32 [rq_peer_allreduce_state_words()], one per allocation
+ * Ranks sum in rank order, so all ranks end with bit-identical values.  torch.distributed._symmetric_memory
+ * provides the pointer tables (rq_vae_recommender_b200/parallel.py::PeerAllReduce).
+ */
+int64_t rq_peer_allreduce_max_floats(void);
+int rq_peer_allreduce_state_words(void);
+int rq_peer_allreduce_pad_bytes(void);
+int rq_peer_allreduce_f32(const void* peer_bufs_dev, const void* peer_pads_dev, int rank, int world,
+                          int64_t offset_floats, int64_t n_floats, float* out, float scale, uint32_t* epoch_dev,
+                          rq_stream_t stream);
+int rq_debug_peer_timeout_flag(void);   /* 1 once a rank failed to arrive at a barrier of the kernel above */
+
+/*
  * Host-buffer convenience entry (the call a non-torch integrator makes): copies `x_host`
  * (pageable or pinned) to the device, runs rq_quantize_forward in RQ_MODE_EVAL, copies the ids
  * [L,B] (and loss [B] when non-NULL) back and returns when they are complete.  Rows are processed

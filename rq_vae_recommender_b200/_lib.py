@@ -43,6 +43,12 @@ SIGNATURES = {
                                       c_void_p]),
     "rq_prefix_exists": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p]),
     "rq_gather_tokens": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "rq_peer_allreduce_max_floats": (c_int64, []),
+    "rq_peer_allreduce_state_words": (c_int, []),
+    "rq_peer_allreduce_pad_bytes": (c_int, []),
+    "rq_peer_allreduce_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int64, c_int64, c_void_p, c_float, c_void_p,
+                                      c_void_p]),
+    "rq_debug_peer_timeout_flag": (c_int, []),
     "rq_id_diversity_workspace_bytes": (c_int64, [c_int, c_int64]),
     "rq_id_diversity": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
                                 c_void_p]),

@@ -1,6 +1,7 @@
 """Row sharding of the item corpus across ranks: one process per GPU, codebooks and
 encoder replicated, items split into contiguous blocks.  Tokenisation needs no data-path
-collective; k-means and the codebook gradient use one all-reduce (torch.distributed / NCCL)."""
+collective; k-means and the codebook gradient use one all-reduce: torch.distributed / NCCL, or the engine's own
+one-shot kernel over peer-mapped memory (`PeerAllReduce`)."""
 from typing import Tuple
 
 import torch
@@ -41,6 +42,67 @@ def allreduce_codebook_grads(model, group=None, average: bool = True) -> None:
         if average:
             flat /= dist.get_world_size(group)
     torch._foreach_copy_(grads, [c.view_as(g) for g, c in zip(grads, flat.split([g.numel() for g in grads]))])
+
+
+class PeerAllReduce:
+    """All-reduce of small fp32 buffers over peer-mapped symmetric memory (rq_peer_allreduce_f32): one kernel
+    launch on the caller's stream, NVLink loads, no NCCL on the data path, capturable into the step's CUDA graph.
+
+    `buffer` is a [slots, *shape] fp32 tensor in a symmetric allocation: the producer (e.g. the fused backward,
+    through `functional.quantize_backward(..., g_codebooks_out=peer.buffer[s])`) writes slot s, then
+    `all_reduce_(s)` replaces it with the sum (or mean) over the ranks, bit-identical on every rank.  All ranks
+    must make the same calls in the same order.  torch.distributed._symmetric_memory supplies allocation,
+    rendezvous and the peer pointer tables."""
+
+    def __init__(self, shape, slots: int = 1, group=None, device=None):
+        import math
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib as L
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("PeerAllReduce needs an initialised process group")
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.shape = tuple(int(v) for v in shape)
+        self.numel = math.prod(self.shape)
+        lib = L.lib()
+        if self.numel % 4 or self.numel > lib.rq_peer_allreduce_max_floats():
+            raise ValueError(f"PeerAllReduce: {self.numel} floats per slot (need a multiple of 4, at most "
+                             f"{lib.rq_peer_allreduce_max_floats()})")
+        device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.buffer = symm.empty((int(slots),) + self.shape, dtype=torch.float32, device=device)
+        self.handle = symm.rendezvous(self.buffer, self.group)
+        if self.handle.signal_pad_size < lib.rq_peer_allreduce_pad_bytes():
+            raise RuntimeError("PeerAllReduce: signal pad too small")
+        self.buffer.zero_()
+        self._epoch = torch.zeros(lib.rq_peer_allreduce_state_words(), dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(self.group)                         # every rank's buffer, pad and counters are in place
+
+    @staticmethod
+    def available(group=None) -> bool:
+        import torch.distributed as dist
+        try:
+            import torch.distributed._symmetric_memory  # noqa: F401
+        except Exception:
+            return False
+        return (dist.is_available() and dist.is_initialized() and dist.get_backend(group) == "nccl"
+                and torch.cuda.is_available() and dist.get_world_size(group) <= 16)
+
+    def all_reduce_(self, slot: int = 0, average: bool = True, out=None, stream=None):
+        """buffer[slot] <- sum (mean) over ranks of buffer[slot]; `out` redirects the result to another fp32
+        tensor of the same size (the slot then keeps this rank's own contribution).  `stream` (a
+        torch.cuda.Stream; default: the current one) is where the kernel is launched."""
+        from . import _lib as L
+        dst = self.buffer[slot] if out is None else out
+        if dst.numel() != self.numel or dst.dtype != torch.float32 or not dst.is_contiguous() or not dst.is_cuda:
+            raise ValueError("PeerAllReduce.all_reduce_: out must be a contiguous CUDA fp32 tensor of the slot's size")
+        rc = L.lib().rq_peer_allreduce_f32(self.handle.buffer_ptrs_dev, self.handle.signal_pad_ptrs_dev, self.rank,
+                                           self.world, int(slot) * self.numel, self.numel, dst.data_ptr(),
+                                           (1.0 / self.world) if average else 1.0, self._epoch.data_ptr(),
+                                           L.stream_of(self.buffer) if stream is None else stream.cuda_stream)
+        L.check(rc, "rq_peer_allreduce_f32")
+        return dst
 
 
 def is_distributed(group=None) -> bool:

@@ -319,3 +319,20 @@ def test_full_size_properties_c4_tokenize_d64():
         excess = d.gather(1, ids_s[l][:8192, None]).squeeze(1) - d.min(1).values
         scale = (r ** 2).sum(1) + (cb[l].double() ** 2).sum(1).max()
         assert bool((excess <= 1e-6 * scale).all())
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (run through gpurun --gpus 2)")
+def test_peer_allreduce_two_ranks():
+    """parallel.PeerAllReduce / rq_peer_allreduce_f32 on two ranks: sums equal NCCL's, identical on both ranks, in place
+    and out of place, eager and replayed from a CUDA graph (tools/test_peer_allreduce.py under torchrun)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533",
+                        os.path.join(root, "tools", "test_peer_allreduce.py")],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "ok=True timeout_flag=0" in r.stdout
+
