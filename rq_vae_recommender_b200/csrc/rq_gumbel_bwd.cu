@@ -70,6 +70,9 @@ __global__ void __launch_bounds__(kGbThreads) rq_bwd_gumbel_kernel(GumbelBwdPara
     extern __shared__ __align__(16) float smem[];
     float* sC = smem;                  // [KC][D]
     float* sN = smem + P.KC * D;       // [KC] ||c||^2
+    // [D][threads]: the running gradient G waits here during the two passes over the codes (x, de, v and G together
+    // are 4 D registers — at D = 64 one more than a thread has)
+    float* sG = sN + ((P.KC + 3) & ~3) + threadIdx.x;
     const int tid = threadIdx.x, lane = tid & 31;
     const int64_t row = (int64_t)blockIdx.x * kGbThreads + tid;
     const bool active = row < p.B;
@@ -132,12 +135,16 @@ __global__ void __launch_bounds__(kGbThreads) rq_bwd_gumbel_kernel(GumbelBwdPara
         }
         const float inv_s = 1.0f / s;
         float t = 0.f;
+        // emb is retired here (its share of d objective / d residual_l goes into G right away), so that pass 2 holds
+        // x, de, v and G only: at D = 64 the extra 64 live registers spilled 1.7 KB per thread
 #pragma unroll
         for (int j = 0; j < D; ++j) {
-            emb[j] *= inv_s;
+            const float ej = emb[j] * inv_s;
             const float ge = (active && p.g_emb) ? __ldg(p.g_emb + off + j) : 0.f;
-            de[j] = (ge - G[j]) + 2.f * (emb[j] - x[j]) * gl;
-            t = fmaf(de[j], emb[j], t);
+            const float tg = (active && p.g_res) ? __ldg(p.g_res + off + j) : 0.f;
+            de[j] = (ge - G[j]) + 2.f * (ej - x[j]) * gl;
+            t = fmaf(de[j], ej, t);
+            sG[j * kGbThreads] = G[j] + (2.f * p.beta * (x[j] - ej) * gl + tg);
         }
         // ---- pass 2: gradients ------------------------------------------------------------------------------
         float sdd = 0.f, v[D];
@@ -159,29 +166,27 @@ __global__ void __launch_bounds__(kGbThreads) rq_bwd_gumbel_kernel(GumbelBwdPara
                 const float W = __expf(y - m) * inv_s;
                 const float dd = -(W * (dW - t)) * invT;
                 sdd += dd;
-                float contrib[D];
-#pragma unroll
-                for (int j = 0; j < D; ++j) {
-                    v[j] = fmaf(dd, c[j], v[j]);
-                    contrib[j] = fmaf(W, de[j], 2.f * dd * (c[j] - x[j]));
-                }
-                float red[(D + 31) / 32];
-                warp_transpose_sum<D>(contrib, red);
                 float* dst = p.g_cb + ((int64_t)l * p.K + k0 + k) * D;
-                if (D >= 32) {
+                constexpr int BLK = D >= 32 ? 32 : D;          // contributions are built and reduced 32 elements at a time
 #pragma unroll
-                    for (int b = 0; b < (D + 31) / 32; ++b) atomicAdd(dst + 32 * b + lane, red[b]);
-                } else if (lane < D) {
-                    atomicAdd(dst + lane, red[0]);
+                for (int b = 0; b < D / BLK; ++b) {
+                    float contrib[BLK];
+#pragma unroll
+                    for (int j = 0; j < BLK; ++j) {
+                        const int jj = b * BLK + j;
+                        v[jj] = fmaf(dd, c[jj], v[jj]);
+                        contrib[j] = fmaf(W, de[jj], 2.f * dd * (c[jj] - x[jj]));
+                    }
+                    float red[1];
+                    warp_transpose_sum<BLK>(contrib, red);
+                    if (D >= 32) atomicAdd(dst + 32 * b + lane, red[0]);
+                    else if (lane < D) atomicAdd(dst + lane, red[0]);
                 }
             }
         }
         // ---- d objective / d residual_l ------------------------------------------------------------------------
 #pragma unroll
-        for (int j = 0; j < D; ++j) {
-            const float tg = (active && p.g_res) ? __ldg(p.g_res + off + j) : 0.f;
-            G[j] += 2.f * p.beta * (x[j] - emb[j]) * gl + 2.f * x[j] * sdd - 2.f * v[j] + tg;
-        }
+        for (int j = 0; j < D; ++j) G[j] = sG[j * kGbThreads] + (2.f * x[j] * sdd - 2.f * v[j]);
     }
     if (active) store_row<D>(p.g_x + row * D, G);
 }
@@ -194,7 +199,8 @@ static int launch_gumbel_bwd(const BwdParams& p, float temperature, const float*
     int kc = 16384 / D;
     if (kc > p.K) kc = p.K;
     P.KC = kc;
-    const size_t smem = (size_t)kc * D * sizeof(float) + (size_t)kc * sizeof(float);
+    const size_t smem = (size_t)kc * D * sizeof(float) + (size_t)((kc + 3) & ~3) * sizeof(float) +
+                        (size_t)D * kGbThreads * sizeof(float);
     auto kern = rq_bwd_gumbel_kernel<D>;
     RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned grid = (unsigned)((p.B + kGbThreads - 1) / kGbThreads);
