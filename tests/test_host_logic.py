@@ -151,3 +151,26 @@ def test_data_utils_batch_to_and_cycle():
         U.batch_to(3.5, "cpu")
     with pytest.raises(RuntimeError):
         U.DevicePrefetcher([torch.ones(1)], "cpu")
+
+
+def test_bench_reference_arm_prints_exactly_one_json_line():
+    """bench.py's contract: stdout carries ONE JSON line (library banners are sent to stderr; the line is written to
+    the saved descriptor, so an os._exit on the multi-rank path cannot lose it).  The reference arm runs on CPU."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1",
+                        "--cpu-sample-items", "2048"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "items/s" and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["e2e"]["h2d_bytes_per_step"] == 0
+    # a non-zero rank of a multi-rank launch does no work and prints nothing
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2")
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and r.stdout.strip() == ""
