@@ -16,7 +16,10 @@
 
 namespace rq {
 
-constexpr int kGbThreads = 128;
+#ifndef RQ_GB_THREADS
+#define RQ_GB_THREADS 128
+#endif
+constexpr int kGbThreads = RQ_GB_THREADS;
 
 // sum over the 32 lanes of v[0..D): on return lane j (and j + 32, ...) holds element j's total in v[0], v[1]...
 // i.e. element (lane + 32 * i) is in out[i].  D in {4, 8, 16, 32, 64}.
