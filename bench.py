@@ -543,6 +543,8 @@ def run_engine(args):
                          "algorithmic_bytes_per_launch": B_PER_GPU * BYTES_FWD, "launch_ms": dom_ms},
             "clocks": clk.summary(),
             "extra": {"fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "ids_only_ms": ids_only_ms,
+                      "fwd_hbm_frac": B_PER_GPU * BYTES_FWD / (fwd_ms * 1e-3) / 1e9 / hbm,
+                      "bwd_hbm_frac": B_PER_GPU * BYTES_FWD / (bwd_ms * 1e-3) / 1e9 / hbm,
                       "ids_only_items_per_s": B_PER_GPU / (ids_only_ms * 1e-3),
                       "fwd_items_per_s": B_PER_GPU / (fwd_ms * 1e-3),
                       "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode,
