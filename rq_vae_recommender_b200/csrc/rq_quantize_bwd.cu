@@ -921,21 +921,26 @@ __global__ void __launch_bounds__(bwdrow3::THREADS, 2) rq_bwd_row3_kernel(BwdPar
             uint8_t* tG = tR + TILE_BYTES;
             uint8_t* tE = tG + TILE_BYTES;
             float cg, cr, ce;
+            // the row halves stay in registers from the dot products to the update (occupancy is bounded by the
+            // 12 KB of shared memory per warp, not by registers)
+            float R_[16], E_[16], Gv_[16];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float4 r4 = *reinterpret_cast<const float4*>(tR + ro[c]);
+                const float4 e4 = *reinterpret_cast<const float4*>(tE + ro[c]);
+                float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (has_gemb) g4 = *reinterpret_cast<const float4*>(tG + ro[c]);
+                R_[4 * c] = r4.x; R_[4 * c + 1] = r4.y; R_[4 * c + 2] = r4.z; R_[4 * c + 3] = r4.w;
+                E_[4 * c] = e4.x; E_[4 * c + 1] = e4.y; E_[4 * c + 2] = e4.z; E_[4 * c + 3] = e4.w;
+                Gv_[4 * c] = g4.x - G[4 * c]; Gv_[4 * c + 1] = g4.y - G[4 * c + 1];
+                Gv_[4 * c + 2] = g4.z - G[4 * c + 2]; Gv_[4 * c + 3] = g4.w - G[4 * c + 3];
+            }
             if (MODE == RQ_MODE_ROTATION_TRICK) {
                 float rr = 0.f, ee = 0.f, re = 0.f, gr = 0.f, ge = 0.f;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const float4 r4 = *reinterpret_cast<const float4*>(tR + ro[c]);
-                    const float4 e4 = *reinterpret_cast<const float4*>(tE + ro[c]);
-                    float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (has_gemb) g4 = *reinterpret_cast<const float4*>(tG + ro[c]);
-                    const float rv[4] = {r4.x, r4.y, r4.z, r4.w}, ev[4] = {e4.x, e4.y, e4.z, e4.w};
-                    const float gv[4] = {g4.x - G[4 * c], g4.y - G[4 * c + 1], g4.z - G[4 * c + 2], g4.w - G[4 * c + 3]};
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        rr = fmaf(rv[j], rv[j], rr); ee = fmaf(ev[j], ev[j], ee); re = fmaf(rv[j], ev[j], re);
-                        gr = fmaf(gv[j], rv[j], gr); ge = fmaf(gv[j], ev[j], ge);
-                    }
+                for (int j = 0; j < 16; ++j) {
+                    rr = fmaf(R_[j], R_[j], rr); ee = fmaf(E_[j], E_[j], ee); re = fmaf(R_[j], E_[j], re);
+                    gr = fmaf(Gv_[j], R_[j], gr); ge = fmaf(Gv_[j], E_[j], ge);
                 }
                 rr += __shfl_xor_sync(0xffffffffu, rr, 1); ee += __shfl_xor_sync(0xffffffffu, ee, 1);
                 re += __shfl_xor_sync(0xffffffffu, re, 1); gr += __shfl_xor_sync(0xffffffffu, gr, 1);
@@ -950,14 +955,9 @@ __global__ void __launch_bounds__(bwdrow3::THREADS, 2) rq_bwd_row3_kernel(BwdPar
                 if (__any_sync(0xffffffffu, redo)) {
                     float n2 = 0.f;
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const float4 r4 = *reinterpret_cast<const float4*>(tR + ro[c]);
-                        const float4 e4 = *reinterpret_cast<const float4*>(tE + ro[c]);
-                        float w;
-                        w = fmaf(r4.x, iu, e4.x * iq); n2 = fmaf(w, w, n2);
-                        w = fmaf(r4.y, iu, e4.y * iq); n2 = fmaf(w, w, n2);
-                        w = fmaf(r4.z, iu, e4.z * iq); n2 = fmaf(w, w, n2);
-                        w = fmaf(r4.w, iu, e4.w * iq); n2 = fmaf(w, w, n2);
+                    for (int j = 0; j < 16; ++j) {
+                        const float w = fmaf(R_[j], iu, E_[j] * iq);
+                        n2 = fmaf(w, w, n2);
                     }
                     n2 += __shfl_xor_sync(0xffffffffu, n2, 1);
                     if (redo) ns = n2;
@@ -975,18 +975,13 @@ __global__ void __launch_bounds__(bwdrow3::THREADS, 2) rq_bwd_row3_kernel(BwdPar
             }
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                const float4 r4 = *reinterpret_cast<const float4*>(tR + ro[c]);
-                const float4 e4 = *reinterpret_cast<const float4*>(tE + ro[c]);
-                float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (has_gemb) g4 = *reinterpret_cast<const float4*>(tG + ro[c]);
-                const float rv[4] = {r4.x, r4.y, r4.z, r4.w}, ev[4] = {e4.x, e4.y, e4.z, e4.w};
-                const float gv[4] = {g4.x - G[4 * c], g4.y - G[4 * c + 1], g4.z - G[4 * c + 2], g4.w - G[4 * c + 3]};
                 float v[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    v[j] = g2 * (ev[j] - rv[j]);
-                    if (MODE == RQ_MODE_EVAL) v[j] += gv[j];
-                    G[4 * c + j] += fmaf(cg, gv[j], fmaf(cr, rv[j], ce * ev[j]));
+                    const float rvj = R_[4 * c + j], evj = E_[4 * c + j], gvj = Gv_[4 * c + j];
+                    v[j] = g2 * (evj - rvj);
+                    if (MODE == RQ_MODE_EVAL) v[j] += gvj;
+                    G[4 * c + j] += fmaf(cg, gvj, fmaf(cr, rvj, ce * evj));
                 }
                 *reinterpret_cast<float4*>(tG + ro[c]) = make_float4(v[0], v[1], v[2], v[3]);
             }

@@ -21,7 +21,10 @@ def child():
     xs = [t.to(dev) for t in xs]; cbs = cbs.to(dev)
     mode = RF.MODE_ROTATION_TRICK
     out = {}
-    for name, fn in (("fwd", lambda s: RF.quantize_forward(xs[s], cbs, mode, 0.25, 0.2)),
+    g_emb = [t.to(dev) for t in g_emb]; g_loss = g_loss.to(dev)
+    fo = [RF.quantize_forward(xs[s], cbs, mode, 0.25, 0.2) for s in range(N)]
+    for name, fn in (("bwd", lambda s: RF.quantize_backward(g_emb[s], None, g_loss, fo[s][1], fo[s][2], cbs, mode, 0.25, 0.2)),
+                     ("fwd", lambda s: RF.quantize_forward(xs[s], cbs, mode, 0.25, 0.2)),
                      ("ids", lambda s: RF.quantize_forward(xs[s], cbs, RF.MODE_EVAL, want_embeddings=False,
                                                            want_residuals=False, want_loss=False))):
         for s in range(N):
@@ -47,7 +50,7 @@ def child():
             best = min(best, e0.elapsed_time(e1) / 40 * 1e3)
         out[name] = best
     ref = keep[0]
-    print(f"{os.environ.get('RQ_AB_LIB', 'default'):50s} fwd {out['fwd']:.2f} us  ids-only {out['ids']:.2f} us", flush=True)
+    print(f"{os.environ.get('RQ_AB_LIB', 'default'):50s} fwd {out['fwd']:.2f} us  ids-only {out['ids']:.2f} us  bwd {out['bwd']:.2f} us", flush=True)
 
 
 if __name__ == "__main__":
