@@ -41,11 +41,14 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
         : "memory");
     return ok != 0;
 }
+#ifndef RQ_MBAR_HINT_NS
+#define RQ_MBAR_HINT_NS 200
+#endif
 // Bounded wait: returns false instead of hanging the GPU if the barrier never completes.
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
 #pragma unroll 1
     for (uint32_t i = 0; i < (1u << 22); ++i)
-        if (mbar_try_wait_hint(bar, parity, 200)) return true;
+        if (mbar_try_wait_hint(bar, parity, RQ_MBAR_HINT_NS)) return true;
     return false;
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
