@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librqengine.so")
 OBJ = os.path.join(HERE, "build")
-SOURCES = ["rq_capi.cu", "rq_quantize_simt.cu", "rq_quantize_tc.cu", "rq_quantize_tc64.cu", "rq_quantize_bigk.cu", "rq_quantize_bwd.cu", "rq_gumbel_bwd.cu", "rq_kmeans.cu",
+SOURCES = ["rq_capi.cu", "rq_quantize_simt.cu", "rq_quantize_tc.cu", "rq_quantize_tc32.cu", "rq_quantize_tc64.cu", "rq_quantize_bigk.cu", "rq_quantize_bwd.cu", "rq_gumbel_bwd.cu", "rq_kmeans.cu",
            "rq_tokenizer.cu", "rq_peer.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr",
@@ -39,17 +39,20 @@ def _digest():
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, experiments: bool = False) -> str:
+    """`experiments=True` compiles the profiling marks / what-if switches in (-DRQ_EXPERIMENTS); the release library
+    has none of them and reads no environment variable on a launch path."""
     os.makedirs(OBJ, exist_ok=True)
     stamp = os.path.join(OBJ, "digest.txt")
-    dig = _digest()
+    flags = NVCC_FLAGS + (["-DRQ_EXPERIMENTS"] if experiments else [])
+    dig = _digest() + ("+experiments" if experiments else "")
     if not force and os.path.exists(OUT) and os.path.exists(stamp) and open(stamp).read() == dig:
         return OUT
     nvcc = _nvcc()
 
     def compile_one(src):
         obj = os.path.join(OBJ, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *flags, "-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log = os.path.join(OBJ, src + ".log")
         open(log, "w").write(r.stdout + r.stderr)
@@ -71,4 +74,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, experiments="--experiments" in sys.argv))

@@ -3,6 +3,8 @@
 #include <string.h>
 #include <stdlib.h>
 #include <initializer_list>
+#include <mutex>
+#include <vector>
 
 #include "rq_common.cuh"
 #include "rq_kernels.h"
@@ -19,19 +21,41 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 
+// SM count of the current device minus the SMs reserved for concurrently running collectives (RQ_SM_RESERVE is read
+// once per process: NCCL kernels need a few CTAs' worth of SM resources and a persistent grid that fills every SM
+// would make one of the two wait for the other).  Cached per device.
 int sm_count() {
-    static int cached = 0;
-    if (!cached) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
-        if (cached <= 0) cached = 148;
-        // SMs left free for concurrently running collectives (NCCL kernels need a few CTAs' worth of SM
-        // resources; a persistent grid that fills every SM would make one of the two wait for the other)
+    static std::atomic<int> cached[64];
+    static const int reserve = [] {
         const char* e = getenv("RQ_SM_RESERVE");
-        const int reserve = e ? atoi(e) : 0;
-        if (reserve > 0 && reserve < cached) cached -= reserve;
+        return e ? atoi(e) : 0;
+    }();
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int n = cached[dev].load(std::memory_order_relaxed);
+    if (!n) {
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+        if (reserve > 0 && reserve < n) n -= reserve;
+        cached[dev].store(n, std::memory_order_relaxed);
     }
-    return cached;
+    return n;
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per (function, device): set it once for each pair.
+cudaError_t ensure_max_dynamic_smem(const void* fn, int bytes) {
+    struct Entry { const void* fn; int dev; int bytes; };
+    static std::mutex mu;
+    static std::vector<Entry> done;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    for (const Entry& d : done)
+        if (d.fn == fn && d.dev == dev && d.bytes >= bytes) return cudaSuccess;
+    e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) done.push_back({fn, dev, bytes});
+    return e;
 }
 
 static bool pow2_dim(int D) { return D == 4 || D == 8 || D == 16 || D == 32 || D == 64 || D == 128; }

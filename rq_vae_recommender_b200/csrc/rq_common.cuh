@@ -43,6 +43,7 @@ extern std::atomic<uint64_t> g_launches;
     } while (0)
 
 int sm_count();
+cudaError_t ensure_max_dynamic_smem(const void* fn, int bytes);   // per (function, device), set once
 
 // ---- small device helpers -------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

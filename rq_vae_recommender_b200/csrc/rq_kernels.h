@@ -28,6 +28,9 @@ struct FwdParams {
     // > 1: the launch covers `n_chunks` consecutive 256-code chunks of ONE codebook of `K` codes (L must be 1):
     // CTA b serves chunk b % n_chunks, ids / best_dist of chunk c are written at offset c * B.
     int n_chunks = 1;
+    // first row served by the launch (SIMT family only): the tcgen05 d=32 kernel handles whole 128-row tiles and
+    // hands the last B % 128 rows to the exact family; level strides stay B
+    int64_t row0 = 0;
 };
 
 struct BwdParams {

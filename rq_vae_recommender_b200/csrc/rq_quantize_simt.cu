@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(kSimtThreads) rq_fwd_simt_kernel(FwdParams p) 
     float* sC = smem;                 // [KC][D]
     float* sN = smem + p.KC * D;      // [KC]  ||c||^2 (L2) or ||c|| (COSINE)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t row = (int64_t)blockIdx.x * kSimtThreads + tid;
+    const int64_t row = p.row0 + (int64_t)blockIdx.x * kSimtThreads + tid;
     const bool active = row < p.B;
 
     float r[D];
@@ -153,7 +153,9 @@ __global__ void __launch_bounds__(kSimtThreads) rq_fwd_simt_kernel(FwdParams p) 
             const int64_t off = ((int64_t)l * p.B + row) * D;
             if (p.res) store_row<D>(p.res + off, r);
             if (p.emb) store_row<D>(p.emb + off, o);
-            p.ids[(int64_t)l * p.B + row] = bi;
+            int64_t* idp = p.ids + (int64_t)l * p.B + row;
+            if (p.n_changed && (!p.has_prev || *idp != (int64_t)bi)) atomicAdd(p.n_changed, 1ull);   // k-means tail rows
+            *idp = bi;
             residual_update<D>(r, o);                                      // rqvae.py:129
         }
     }
@@ -169,7 +171,7 @@ static int launch_fwd(const FwdParams& p0, cudaStream_t st) {
     if (kc > ((p.K + 3) & ~3)) kc = (p.K + 3) & ~3;
     p.KC = kc;
     size_t smem = (size_t)kc * D * sizeof(float) + (size_t)kc * sizeof(float);
-    dim3 grid((unsigned)((p.B + kSimtThreads - 1) / kSimtThreads));
+    dim3 grid((unsigned)((p.B - p.row0 + kSimtThreads - 1) / kSimtThreads));
     if (p.mode == RQ_MODE_GUMBEL_SOFTMAX) {
         if (D > 64) { set_error("GUMBEL_SOFTMAX supports D <= 64 in the SIMT family (got %d)", D); return RQ_ERR_UNSUPPORTED_SHAPE; }
         auto kern = rq_fwd_simt_kernel<(D > 64 ? 64 : D), true>;
@@ -185,7 +187,7 @@ static int launch_fwd(const FwdParams& p0, cudaStream_t st) {
 }
 
 int quantize_forward_simt(const FwdParams& p, int D, cudaStream_t st) {
-    if (p.B == 0) return 0;
+    if (p.B - p.row0 <= 0) return 0;
     switch (D) {
         case 4: return launch_fwd<4>(p, st);
         case 8: return launch_fwd<8>(p, st);

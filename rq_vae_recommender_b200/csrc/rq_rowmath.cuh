@@ -19,18 +19,78 @@ __device__ __forceinline__ void store_row(float* __restrict__ dst, const float (
 #pragma unroll
     for (int j = 0; j < D / 4; ++j) d4[j] = make_float4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
 }
-// ||r||^2: even and odd elements accumulate in the two lanes of one FFMA2 chain, then the lanes are added.
-// (Both kernel families and the re-scoring path use this one definition, so they agree bit for bit.)
-template <int D>
-__device__ __forceinline__ float dot_self(const float (&r)[D]) {
-    if (D < 2) return r[0] * r[0];
+// ---- canonical dot products ---------------------------------------------------------------------------------
+// A row is cut into 8-element chunks.  A chunk's partial is one FFMA2 chain over its 4 element pairs (even and odd
+// elements in the two lanes) followed by the sum of the two lanes; the chunk partials are combined by a balanced
+// pairwise tree ((p0+p1)+(p2+p3) for D = 32).  A thread that owns a whole row and a group of D/8 lanes that own one
+// chunk each (partials combined by shfl.xor 1, 2, 4) therefore produce the same bits — the SIMT family, the tcgen05
+// families and the re-scoring paths all use these definitions.
+constexpr int kRowChunk = 8;
+template <int W>
+__device__ __forceinline__ float chunk_dot(const float* a, const float* b) {
     f32x2 s = pack2(0.f, 0.f);
 #pragma unroll
-    for (int j = 0; j + 1 < D; j += 2) {
-        const f32x2 v = pack2(r[j], r[j + 1]);
-        s = fma2(v, v, s);
+    for (int j = 0; j + 1 < W; j += 2) s = fma2(pack2(a[j], a[j + 1]), pack2(b[j], b[j + 1]), s);
+    return hsum2(s);
+}
+template <int W>
+__device__ __forceinline__ float chunk_sqdiff(const float* a, const float* b) {      // sum (a - b)^2
+    f32x2 s = pack2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j + 1 < W; j += 2) {
+        const f32x2 t = sub2(pack2(a[j], a[j + 1]), pack2(b[j], b[j + 1]));
+        s = fma2(t, t, s);
     }
     return hsum2(s);
+}
+template <int W>
+__device__ __forceinline__ float chunk_sq_axpby(const float* a, const float* b, float ia, float ib) {   // sum (ia a + ib b)^2
+    f32x2 s = pack2(0.f, 0.f);
+    const f32x2 ia2 = pack2(ia, ia), ib2 = pack2(ib, ib);
+#pragma unroll
+    for (int j = 0; j + 1 < W; j += 2) {
+        const f32x2 t = fma2(pack2(a[j], a[j + 1]), ia2, mul2(pack2(b[j], b[j + 1]), ib2));
+        s = fma2(t, t, s);
+    }
+    return hsum2(s);
+}
+template <int NP>
+__device__ __forceinline__ float tree_sum(float (&p)[NP]) {
+#pragma unroll
+    for (int s = 1; s < NP; s *= 2) {
+#pragma unroll
+        for (int q = 0; q + s < NP; q += 2 * s) p[q] += p[q + s];
+    }
+    return p[0];
+}
+template <int D>
+__device__ __forceinline__ float dot_self(const float (&r)[D]) {
+    constexpr int W = D >= kRowChunk ? kRowChunk : D;
+    float p[D / W];
+#pragma unroll
+    for (int q = 0; q < D / W; ++q) p[q] = chunk_dot<W>(&r[q * W], &r[q * W]);
+    return tree_sum(p);
+}
+
+// Scalars of the rotation trick (see level_epilogue) from the dot products xx = r.r, ee = e.e, re = r.e.
+// rot_prepare returns |u+q|^2 by the expanded form; when it is < 1/16 the caller recomputes it directly
+// (sum (iu r + iq e)^2, canonical order) before rot_finish.
+__device__ __forceinline__ float rot_prepare(float xx, float ee, float re, float& nx, float& ne, float& iu, float& iq) {
+    nx = fast_sqrt(xx);
+    ne = fast_sqrt(ee);
+    iu = fast_rcp(nx + 1e-8f);
+    iq = fast_rcp(ne + 1e-8f);
+    return fmaf(iu * iu, xx, fmaf(2.f * iu * iq, re, iq * iq * ee));
+}
+constexpr float kRotCancel = 0.0625f;                         // |u+q| < 1/4: recompute without cancellation
+__device__ __forceinline__ void rot_finish(float xx, float re, float nx, float ne, float iu, float iq, float ns,
+                                           float& ca, float& ce) {
+    const float iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f));   // F.normalize(eps=1e-6)
+    const float rs = fmaf(iu, xx, iq * re);                   // r.(u+q)
+    const float rsw = rs * iw * iw;                           // (r.w) * iw
+    const float lam = ne * fast_rcp(nx + 1e-6f);
+    ca = lam * (1.f - 2.f * rsw * iu);
+    ce = 2.f * lam * iq * (iu * xx - rsw);
 }
 
 // Canonical ||c||^2 of a codeword, bit-identical in both kernel families: sequential fmaf over
@@ -74,62 +134,44 @@ template <int D>
 __device__ __forceinline__ float level_epilogue(int mode, float beta, const float (&r)[D], const float (&e)[D],
                                                 float xx, float (&o)[D]) {
     static_assert(D % 2 == 0, "rows are processed as fp32 pairs");
-    f32x2 rp[D / 2], ep[D / 2];
+    constexpr int W = D >= kRowChunk ? kRowChunk : D;
+    constexpr int NP = D / W;
+    float pd[NP];
 #pragma unroll
-    for (int j = 0; j < D / 2; ++j) {
-        rp[j] = pack2(r[2 * j], r[2 * j + 1]);
-        ep[j] = pack2(e[2 * j], e[2 * j + 1]);
-    }
-    float dsq;
+    for (int q = 0; q < NP; ++q) pd[q] = chunk_sqdiff<W>(&r[q * W], &e[q * W]);
+    const float dsq = tree_sum(pd);
     if (mode == RQ_MODE_ROTATION_TRICK) {
-        f32x2 d2 = pack2(0.f, 0.f), e2 = d2, re2 = d2;
+        float pe[NP], pre[NP];
 #pragma unroll
-        for (int j = 0; j < D / 2; ++j) {
-            const f32x2 t = sub2(rp[j], ep[j]);
-            d2 = fma2(t, t, d2);
-            e2 = fma2(ep[j], ep[j], e2);
-            re2 = fma2(rp[j], ep[j], re2);
+        for (int q = 0; q < NP; ++q) {
+            pe[q] = chunk_dot<W>(&e[q * W], &e[q * W]);
+            pre[q] = chunk_dot<W>(&r[q * W], &e[q * W]);
         }
-        dsq = hsum2(d2);
-        const float ee = hsum2(e2), re = hsum2(re2);
-        const float nx = fast_sqrt(xx), ne = fast_sqrt(ee);
-        const float iu = fast_rcp(nx + 1e-8f), iq = fast_rcp(ne + 1e-8f);
-        float ns = fmaf(iu * iu, xx, fmaf(2.f * iu * iq, re, iq * iq * ee));
-        if (ns < 0.0625f) {                                   // |u+q| < 1/4: recompute without cancellation
-            f32x2 n2 = pack2(0.f, 0.f);
-            const f32x2 iu2 = pack2(iu, iu), iq2 = pack2(iq, iq);
+        const float ee = tree_sum(pe), re = tree_sum(pre);
+        float nx, ne, iu, iq;
+        float ns = rot_prepare(xx, ee, re, nx, ne, iu, iq);
+        if (ns < kRotCancel) {
+            float pn[NP];
 #pragma unroll
-            for (int j = 0; j < D / 2; ++j) {
-                const f32x2 sj = fma2(rp[j], iu2, mul2(ep[j], iq2));
-                n2 = fma2(sj, sj, n2);
-            }
-            ns = hsum2(n2);
+            for (int q = 0; q < NP; ++q) pn[q] = chunk_sq_axpby<W>(&r[q * W], &e[q * W], iu, iq);
+            ns = tree_sum(pn);
         }
-        const float iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f)); // F.normalize(eps=1e-6)
-        const float rs = fmaf(iu, xx, iq * re);               // r.(u+q)
-        const float rsw = rs * iw * iw;                       // (r.w) * iw
-        const float lam = ne * fast_rcp(nx + 1e-6f);
-        const float ca = lam * (1.f - 2.f * rsw * iu);
-        const float ce = 2.f * lam * iq * (iu * xx - rsw);
+        float ca, ce;
+        rot_finish(xx, re, nx, ne, iu, iq, ns, ca, ce);
         const f32x2 ca2 = pack2(ca, ca), ce2 = pack2(ce, ce);
 #pragma unroll
-        for (int j = 0; j < D / 2; ++j) unpack2(fma2(ca2, rp[j], mul2(ce2, ep[j])), o[2 * j], o[2 * j + 1]);
-    } else {
-        f32x2 d2 = pack2(0.f, 0.f);
+        for (int j = 0; j < D / 2; ++j)
+            unpack2(fma2(ca2, pack2(r[2 * j], r[2 * j + 1]), mul2(ce2, pack2(e[2 * j], e[2 * j + 1]))), o[2 * j],
+                    o[2 * j + 1]);
+    } else if (mode == RQ_MODE_STE) {
 #pragma unroll
-        for (int j = 0; j < D / 2; ++j) {
-            const f32x2 t = sub2(rp[j], ep[j]);
-            d2 = fma2(t, t, d2);
+        for (int j = 0; j < D / 2; ++j) {                                  // quantize.py:132: x + (emb - x)
+            const f32x2 rp = pack2(r[2 * j], r[2 * j + 1]), ep = pack2(e[2 * j], e[2 * j + 1]);
+            unpack2(add2(rp, sub2(ep, rp)), o[2 * j], o[2 * j + 1]);
         }
-        dsq = hsum2(d2);
-        if (mode == RQ_MODE_STE) {
+    } else {                                                               // EVAL: quantize.py:149
 #pragma unroll
-            for (int j = 0; j < D / 2; ++j)                                // quantize.py:132: x + (emb - x)
-                unpack2(add2(rp[j], sub2(ep[j], rp[j])), o[2 * j], o[2 * j + 1]);
-        } else {                                                           // EVAL: quantize.py:149
-#pragma unroll
-            for (int j = 0; j < D; ++j) o[j] = e[j];
-        }
+        for (int j = 0; j < D; ++j) o[j] = e[j];
     }
     return dsq + beta * dsq;                                               // loss.py:40-42
 }

@@ -66,6 +66,14 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  : "memory");
 }
 
+// 16-byte cp.async (LDGSTS), L2 only; `src_bytes` < 16 zero-fills the rest (0 = all zeros, nothing is read)
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // ---- proxies / fences -----------------------------------------------------------------------------
 // generic-proxy smem writes -> visible to the async proxy (tcgen05.mma operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
@@ -220,6 +228,23 @@ __device__ __forceinline__ void split_pair(float a, float b, uint32_t& hi, uint3
     uint32_t ah = bf16_hi_bits(a), bh = bf16_hi_bits(b);
     hi = pack_hi16(ah, bh);
     // both subtractions in one FADD2 (exact: a - hi(a) is representable)
+    unsigned long long ab, hh, dd;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(ab) : "f"(a), "f"(b));
+    asm("mov.b64 %0, {%1, %2};" : "=l"(hh) : "r"(ah), "r"(bh));
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dd) : "l"(ab), "l"(hh));
+    uint32_t la, lb;
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(la), "=r"(lb) : "l"(dd));
+    lo = pack_hi16(la, lb);
+}
+
+// The same split with the rounding done by the conversion unit: hi = cvt.rn.bf16x2 (one F2FP per pair, already packed),
+// its two fp32 values are rebuilt with a shift (IMAD.SHL, FMA pipe) and a mask, lo = bf16 truncation of the exact
+// x - hi.  Two ALU-pipe operations per pair instead of six: the ALU pipe is the loaded one in the fused kernel
+// (accumulator scan).  (A Veltkamp split on packed FMA operations does not survive ptxas: it contracts
+// mul.rn.f32x2 + sub.rn.f32x2 into one FFMA2, which returns x itself.)
+__device__ __forceinline__ void split_pair_cvt(float a, float b, uint32_t& hi, uint32_t& lo) {
+    hi = pack_bf16x2(a, b);                              // {bf16(b) : bf16(a)}, round to nearest even
+    const uint32_t ah = hi << 16, bh = hi & 0xFFFF0000u;
     unsigned long long ab, hh, dd;
     asm("mov.b64 %0, {%1, %2};" : "=l"(ab) : "f"(a), "f"(b));
     asm("mov.b64 %0, {%1, %2};" : "=l"(hh) : "r"(ah), "r"(bh));

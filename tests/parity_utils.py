@@ -1,4 +1,8 @@
 """Shared parity checks: CUDA engine vs the CPU oracle (tests only)."""
+import json
+import os
+from typing import NamedTuple
+
 import numpy as np
 import torch
 
@@ -20,11 +24,35 @@ def assert_close(a, b, what, tol=REL_TOL):
     assert e <= tol, f"{what}: max rel err {e:.3e} > {tol}"
 
 
+class IdCheck(NamedTuple):
+    """Result of check_ids.  Unpacks as (n_mismatch_rows, n_outside_band_def1) for the older call sites."""
+    n_mismatch_rows: int
+    n_outside_band_def1: int
+
+
+_RATES_LOG = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out", "parity_rates.jsonl")
+
+
+def report_rates(what, rows, n_mismatch, n_out1, n_out2=0, **extra):
+    """Mismatch rates of a parity run: printed (pytest -s / failure output) and appended to
+    gpurun_out/parity_rates.jsonl when that directory exists (copied to profiles/ per round)."""
+    rec = {"case": what, "rows": int(rows), "id_mismatch_rows": int(n_mismatch),
+           "mismatch_rate": (n_mismatch / rows) if rows else 0.0,
+           "outside_band_def1": int(n_out1), "outside_band_def2": int(n_out2)}
+    rec.update(extra)
+    print("[parity]", json.dumps(rec))
+    d = os.path.dirname(_RATES_LOG)
+    if os.path.isdir(d):
+        with open(_RATES_LOG, "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    return rec
+
+
 def check_ids(ids_gpu, oracle_out, codebooks, what=""):
     """ids_gpu [L,B] vs oracle; a row may differ only from a level whose fp32 top-2 gap is inside
     the tie band (both definitions of SURVEY.md §7.3-3 are evaluated; definition 2 — relative to
     ||x||^2+||c||^2, the error scale of the expanded form — is the gate).  Returns
-    (n_mismatch_rows, n_outside_band_def1)."""
+    IdCheck(n_mismatch_rows, n_outside_band_def1) and reports the rates (report_rates)."""
     ids_gpu = torch.as_tensor(ids_gpu).cpu()
     ids_ref = oracle_out.sem_ids
     Lv, B = ids_ref.shape
@@ -45,7 +73,9 @@ def check_ids(ids_gpu, oracle_out, codebooks, what=""):
         assert bool(in2[0]), (f"{what}: row {r} level {l}: ids differ ({int(ids_gpu[l, r])} vs "
                               f"{int(ids_ref[l, r])}) outside the tie band: gap {float(gap[0]):.3e}, d1 {float(d1[0]):.3e}")
         out1 += int(not bool(in1[0]))
-    return len(rows), out1
+    # outside definition 2 would have failed the assert above, so that count is 0 whenever we get here
+    report_rates(what, B, len(rows), out1, 0, levels=int(Lv))
+    return IdCheck(len(rows), out1)
 
 
 def matching_rows(ids_gpu, oracle_out):

@@ -193,6 +193,32 @@ def test_full_size_properties_c2():
         assert torch.equal(ids, ids2) and torch.equal(emb, emb2) and torch.equal(loss, loss2)
 
 
+@pytest.mark.parametrize("B,mode", [(65536, O.MODE_ROTATION_TRICK), (200000, O.MODE_ROTATION_TRICK),
+                                    (200000, O.MODE_EVAL), (151297, O.MODE_STE)])
+def test_large_batches_full_outputs_vs_oracle(B, mode):
+    """The bench shape (65,536 rows: one tile per warpgroup) and batches past 148 * 4 * 128 = 75,776 rows, where a
+    warpgroup of the d=32 tcgen05 kernel takes a second tile (next-tile prefetch into the residual tile, barrier
+    parities of the second use): ids, embeddings, residuals and loss against the oracle on the same rows."""
+    D, K, L = 32, 256, 3
+    g = torch.Generator().manual_seed(B)
+    x = torch.randn(B, D, generator=g)
+    cbs = synthetic_codebooks(x[:20000], L, K, seed=4)
+    ref = O.rq_forward(x, cbs, mode)
+    emb, res, ids, loss = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), mode, beta=0.25)
+    assert R.lib().rq_debug_tc_timeout_flag() == 0
+    chk = check_ids(ids, ref, cbs, f"d32 3x256 B={B} mode={mode}")
+    assert chk.n_mismatch_rows <= 2 + B // 5000        # every one of them inside the tie band (check_ids)
+    ok = matching_rows(ids, ref)
+    assert_close(emb.cpu()[:, ok], ref.embeddings[:, ok], "emb")
+    assert_close(res.cpu()[:, ok], ref.residuals[:, ok], "res")
+    assert_close(loss.cpu()[ok], ref.quantize_loss[ok], "loss")
+    # and the ids-only launch (tokenisation) of the same batch
+    _, _, ids2, _ = RF.quantize_forward(x.to(DEV), torch.stack(cbs).to(DEV), O.MODE_EVAL, want_embeddings=False,
+                                        want_residuals=False, want_loss=False)
+    if mode == O.MODE_EVAL:
+        assert torch.equal(ids, ids2)
+
+
 @pytest.mark.parametrize("mode", [O.MODE_ROTATION_TRICK, O.MODE_STE])
 @pytest.mark.parametrize("which", ["loss_only", "emb_only", "res_only", "emb_res_loss"])
 def test_backward_with_partial_upstream_gradients(which, mode):

@@ -1,11 +1,12 @@
 """Per-CTA wall-clock stamps (%globaltimer at entry / exit, %smid) of the tcgen05 forward kernel, next to the
-CUDA-event duration of the same launches.  Needs RQ_TC_DBG_FLAGS=4 (set here).  Profiling only."""
+CUDA-event duration of the same launches.  Needs an -DRQ_EXPERIMENTS build (RQ_AB_LIB=path).  Profiling only."""
 import os, sys
-os.environ["RQ_TC_DBG_FLAGS"] = "4"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import bench
 from rq_vae_recommender_b200 import functional as RF, _lib
+if os.environ.get("RQ_AB_LIB"):
+    _lib.LIB_PATH = os.environ["RQ_AB_LIB"]
 
 dev = torch.device("cuda:0")
 N = 8
@@ -22,15 +23,17 @@ for rep in range(6):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     buf.zero_()
     torch.cuda.synchronize()
+    nq = int(os.environ.get("TC_QUEUE", "1"))          # launches queued back to back; stamps are the last one's
     e0.record()
-    RF.quantize_forward(xs[rep % N], cbs, mode, 0.25, 0.2)
+    for j in range(nq):
+        RF.quantize_forward(xs[(rep + j) % N], cbs, mode, 0.25, 0.2)
     e1.record()
     torch.cuda.synchronize()
     t = buf.cpu()[2048:2048 + 4 * 148].view(148, 4)
     st, sm, en = t[:, 0], t[:, 1], t[:, 2]
     t0 = int(st.min())
     dur = (en - st).float() / 1e3
-    print(f"rep {rep}: event {e0.elapsed_time(e1) * 1e3:.1f} us | first start -> last end {(int(en.max()) - t0) / 1e3:.2f} us | "
+    print(f"rep {rep}: event {e0.elapsed_time(e1) * 1e3 / nq:.1f} us/launch | first start -> last end {(int(en.max()) - t0) / 1e3:.2f} us | "
           f"start spread {(int(st.max()) - t0) / 1e3:.2f} us | CTA dur min/med/max {dur.min():.2f}/{dur.median():.2f}/{dur.max():.2f} us")
     if rep == 5:
         order = torch.argsort(en)

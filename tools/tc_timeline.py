@@ -4,6 +4,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import bench
 from rq_vae_recommender_b200 import functional as RF, _lib
+if os.environ.get("RQ_AB_LIB"):                      # an -DRQ_EXPERIMENTS build of the library (build.py --experiments)
+    _lib.LIB_PATH = os.environ["RQ_AB_LIB"]
 
 dev = torch.device("cuda:0")
 xs, cbs, g_emb, g_loss = bench.make_inputs(torch, dev, 2, seed=1)
@@ -22,13 +24,11 @@ torch.cuda.synchronize()
 _lib.lib().rq_debug_tc_set_timeline(None)
 t = buf.cpu()
 t0 = int(t[t > 0].min())
-names = ["start", "init", "tma", "conv", "prolog"] + [f"L{l}:{n}" for l in range(3) for n in ("Awr", "mmaiss", "accrdy", "scan", "slow", "gather", "epi", "done")]
-print("prologue detail (tma_issued, -, tmem_alloc, ones, x_landed, xx_ready):")
-for w in range(32):
-    if int(t[w, 0]):
-        print(w, [int(v) - t0 if int(v) else -1 for v in t[w, 45:51]])
-print("warp " + " ".join(f"{n:>7s}" for n in names))
+names = ["start", "init", "conv", "stagein"] + [f"L{l}:{n}" for l in range(3) for n in
+                                              ("issued", "gathered", "accrdy", "scanned", "id", "est", "Awr", "pwait")]
+print("x landed:", [int(t[w, 60]) - t0 for w in range(16)])
+print("warp " + " ".join(f"{n:>9s}" for n in names))
 for w in range(32):
     if int(t[w, 0]) == 0:
         continue
-    print(f"{w:4d} " + " ".join(f"{(int(v) - t0) if int(v) else -1:7d}" for v in t[w, :len(names)]))
+    print(f"{w:4d} " + " ".join(f"{(int(v) - t0) if int(v) else -1:9d}" for v in t[w, :len(names)]))
