@@ -17,9 +17,12 @@ Weak scaling: every rank processes its own 65,536-row batch per step.
             step's result one step behind the launch front.
 `roofline`: the dominant kernel's algorithmic bytes / its mean launch duration (CUDA events inside the
             timed region) against MEASURED_PEAKS.json.
-`cpu_baseline` / `--impl reference`: the CPU restatement of the reference's quantiser (oracle/, the same
-            ATen ops the reference runs on CPU) on the box's host cores; the reference itself is a
-            Python tree that does not travel to the GPU box.
+`cpu_baseline` / `--impl reference`: the reference's OWN `Quantize.forward` + autograd (vendored unmodified under
+            oracle/_ref by oracle/build_ref.py, kind = "reference") on the box's host cores, all threads; the
+            CPU restatement in oracle/rq_oracle.py (kind = "port") only when oracle/_ref is absent.
+`extra`   : outside the timed region — parity of the bench kernels on the bench inputs against the oracle
+            (mismatch rates under both tie-band definitions), ids-only tokenisation of this rank's shard of a
+            100M-item d=64 corpus (SURVEY 8d protocol) and 10 sharded k-means iterations over 10M x 32 points.
 """
 import argparse
 import json
@@ -46,6 +49,9 @@ def parse():
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--cpu-sample-items", type=int, default=B_PER_GPU)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the tokenisation / k-means / parity side legs")
+    ap.add_argument("--min-timed-s", type=float, default=0.3,
+                    help="repeat the K-step timed block until this much device time has elapsed; report the median block")
     return ap.parse_args()
 
 
@@ -57,20 +63,24 @@ def peaks():
     return 6650.0, "fallback"
 
 
+NCU_CAPTURES = {"rq_fwd": "r2_ncu_full_fwd_tc32.csv", "rq_bwd": "r1_ncu_full_bwd_row3_v7.csv"}
+
+
 def ncu_traffic(kernel):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
-    `ncu --set full` extract under profiles/ (None when no capture of that kernel is committed)."""
-    name = {"rq_fwd": "r1_ncu_full_fwd_tc_v7.csv", "rq_bwd": "r1_ncu_full_bwd_row3_v7.csv"}.get(kernel)
+    """(bytes, source): dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, read from the
+    committed `ncu --set full` extract under profiles/ — NOT a live counter of this run (None when no capture of
+    that kernel is committed)."""
+    name = NCU_CAPTURES.get(kernel)
     path = os.path.join(ROOT, "profiles", name) if name else None
     if not path or not os.path.exists(path):
-        return None
+        return None, None
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     tot = 0.0
     for line in open(path):
         f = line.strip().split(",")
         if len(f) == 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and f[1] in unit:
             tot += float(f[2]) * unit[f[1]]
-    return tot or None
+    return (tot or None), "profiles/" + name
 
 
 def make_inputs(torch, device, n_slots, seed):
@@ -150,14 +160,8 @@ class ClockSampler:
                 "samples": len(s)}
 
 
-def cpu_reference_run(n_items, steps, warmup):
-    """Times the CPU restatement of the reference's quantiser (fwd + autograd bwd) with all host
-    threads.  Returns (items_per_s, ms_per_step, cores)."""
+def cpu_inputs(n_items):
     import torch
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import rq_oracle as O
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
     g = torch.Generator().manual_seed(0)
     x = torch.randn(n_items, D, generator=g)
     gcb = torch.Generator().manual_seed(1234)
@@ -167,18 +171,67 @@ def cpu_reference_run(n_items, steps, warmup):
         cb = res[torch.randperm(res.shape[0], generator=gcb)[:K]] * 0.9
         cl.append(cb)
         res = res - cb[torch.cdist(res, cb).argmin(1)]
-    cbs = torch.stack(cl)
     g_emb = torch.randn(L, n_items, D, generator=g) * 0.01
     g_loss = torch.full((n_items,), 1.0 / n_items)
+    return x, torch.stack(cl), g_emb, g_loss
+
+
+def cpu_reference_run(n_items, steps, warmup):
+    """Times the reference's quantiser (fwd + autograd bwd) on the host with all threads.  Prefers the UNMODIFIED
+    reference vendored under oracle/_ref (three `modules.quantize.Quantize` layers driven by the level loop of
+    `RqVae.get_semantic_ids`, rqvae.py:124-131); falls back to the CPU restatement (oracle/rq_oracle.py).
+    Returns (items_per_s, ms_per_step, cores, kind, what)."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    x, cbs, g_emb, g_loss = cpu_inputs(n_items)
+    kind, what = "port", "oracle/rq_oracle.py (torch CPU ATen fp32)"
+    step = None
+    try:
+        import build_ref
+        if build_ref.available():
+            ref = build_ref.load()
+            Q = ref.quantize
+            layers = []
+            for l in range(L):
+                q = Q.Quantize(embed_dim=D, n_embed=K, do_kmeans_init=False, forward_mode=Q.QuantizeForwardMode.ROTATION_TRICK,
+                               commitment_weight=BETA)
+                with torch.no_grad():
+                    q.embedding.weight.copy_(cbs[l])
+                q.train()
+                layers.append(q)
+
+            def step():
+                for q in layers:
+                    q.embedding.weight.grad = None
+                xin = x.clone().requires_grad_(True)
+                res, loss, obj = xin, 0, 0
+                for l, q in enumerate(layers):                          # rqvae.py:124-131
+                    out = q(res, temperature=TEMP)
+                    loss = loss + out.loss
+                    obj = obj + (out.embeddings * g_emb[l]).sum()
+                    res = res - out.embeddings
+                (obj + (loss * g_loss).sum()).backward()
+                return xin.grad
+            kind, what = "reference", "unmodified reference modules.quantize.Quantize x3 + autograd (oracle/_ref)"
+    except Exception as ex:                                             # keep a baseline, say which
+        print(f"bench.py: oracle/_ref unusable ({type(ex).__name__}: {ex}); timing the oracle port", file=sys.stderr)
+        step = None
+    if step is None:
+        import rq_oracle as O
+
+        def step():
+            return O.rq_forward_backward(x, list(cbs), O.MODE_ROTATION_TRICK, BETA, TEMP, g_emb, g_loss)
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        O.rq_forward_backward(x, list(cbs), O.MODE_ROTATION_TRICK, BETA, TEMP, g_emb, g_loss)
+        step()
         t1 = time.perf_counter()
         if i >= warmup:
             times.append(t1 - t0)
     t = sum(times)
-    return n_items * len(times) / t, 1e3 * t / len(times), cores
+    return n_items * len(times) / t, 1e3 * t / len(times), cores, kind, what
 
 
 def run_reference(args):
@@ -186,10 +239,10 @@ def run_reference(args):
     if rank != 0:
         return
     n = args.cpu_sample_items
-    steps, warm = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
-    ips, ms, cores = cpu_reference_run(n, steps, warm)
-    cb = {"value": ips, "unit": "items/s", "cores": cores, "kind": "port",
-          "sample": f"{steps} steps x {n} items fwd+bwd (oracle/rq_oracle.py, torch CPU ATen, fp32)"}
+    steps, warm = max(1, args.steps), max(0, args.warmup)        # the driver's K and W, as given
+    ips, ms, cores, kind, what = cpu_reference_run(n, steps, warm)
+    cb = {"value": ips, "unit": "items/s", "cores": cores, "kind": kind,
+          "sample": f"{steps} steps x {n} items fwd+bwd, {what}, {cores} threads"}
     emit(json.dumps({
         "impl": "reference", "metric": "items/sec semantic-ID quantize (3x256,d=32)", "value": ips,
         "unit": "items/s", "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": ms,
@@ -205,6 +258,115 @@ def workload_config(n):
             "n_levels": L, "mode": "ROTATION_TRICK", "commitment_weight": BETA,
             "l2_policy": f"ring of {N_SLOTS} distinct batches ({N_SLOTS * (B_PER_GPU * D * 4 * (1 + L)) >> 20} MiB of inputs) > 126 MB L2",
             "parallelism": f"dp{n} row-sharded, replicated codebooks"}
+
+
+def side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss_h, xs, cbs, g_embs, g_loss, mode, fence):
+    """Outside the timed region.  (1) parity of the bench kernels on the bench inputs against the CPU oracle;
+    (2) ids-only tokenisation of this rank's shard of a 100M-item d=64 corpus (SURVEY 8d protocol: a resident 4M-item
+    chunk cycled, ids written into the shard's [3, N/G] table; no collective), barrier + max over ranks;
+    (3) 10 sharded k-means iterations over 10M x 32 points, K = 256 (assign + accumulate, all-reduce of sums / counts /
+    changed count over the ranks, update).  Returns the `extra` entries."""
+    out = {}
+    # ---- (1) parity: slot 0's 65,536 rows, forward + backward, engine vs oracle/rq_oracle.py ------------------------
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import rq_oracle as O
+        x0, ge0 = xs_h[0], g_emb_h[0]
+        ref, gx_ref, gcb_ref = O.rq_forward_backward(x0, list(cbs_h), O.MODE_ROTATION_TRICK, BETA, TEMP, ge0, g_loss_h)
+        emb, res, ids, loss = RF.quantize_forward(xs[0], cbs, mode, BETA, TEMP)
+        g_x, g_cb = RF.quantize_backward(g_embs[0], None, g_loss, res, ids, cbs, mode, BETA, TEMP)
+        ids_c = ids.cpu()
+        diff = ids_c != ref.sem_ids
+        bad = torch.nonzero(diff.any(dim=0)).flatten().tolist()
+        out1 = out2 = 0
+        for r in bad:
+            l = int(torch.nonzero(diff[:, r]).flatten()[0])
+            in1, in2, _, _ = O.tie_band(ref.residuals[l, r:r + 1], cbs_h[l], 1e-6)
+            out1 += int(not bool(in1[0]))
+            out2 += int(not bool(in2[0]))
+        ok = ~diff.any(dim=0)
+
+        def rel(a, b):
+            a, b = a.double().cpu(), b.double().cpu()
+            return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+        out["parity"] = {
+            "checked_against": "oracle/rq_oracle.py (CPU restatement pinned to the reference's golden fixtures)",
+            "rows": int(ids_c.shape[1]), "levels": L, "id_mismatch_rows": len(bad),
+            "id_mismatch_rate": len(bad) / ids_c.shape[1], "outside_band_def1": out1, "outside_band_def2": out2,
+            "max_rel_err": {"emb": rel(emb[:, ok.to(dev)], ref.embeddings[:, ok]), "loss": rel(loss[ok.to(dev)], ref.quantize_loss[ok]),
+                            "gx": rel(g_x[ok.to(dev)], gx_ref[ok]), "gcb": rel(g_cb, gcb_ref)},
+            "tolerance": {"ids": "bit-exact outside the 1e-6 relative tie band", "floats": 1e-3},
+            "note": "float errors over the rows whose ids agree at every level; gcb over all rows"}
+        del ref, gx_ref, gcb_ref, emb, res, ids, loss, g_x, g_cb
+
+    def maxed(ms):
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    # ---- (2) 100M-item corpus tokenisation, d = 64, 3 x 256, ids only -------------------------------------------------
+    n_total, n_chunk, D64 = 100_000_000, 4 << 20, 64
+    lo, hi = R.parallel.shard_range(n_total, rank, world)
+    n_shard = hi - lo
+    g = torch.Generator(device="cpu").manual_seed(7)
+    cb64 = torch.stack([torch.randn(K, D64, generator=g) * (0.6 ** l) for l in range(L)]).to(dev)
+    chunk = torch.randn(n_chunk, D64, device=dev)
+    table = torch.empty((L, n_shard), dtype=torch.int64, device=dev)
+
+    def tokenize_shard():
+        for s0 in range(0, n_shard, n_chunk):
+            n = min(n_chunk, n_shard - s0)
+            _, _, ids, _ = RF.quantize_forward(chunk[:n], cb64, RF.MODE_EVAL, want_embeddings=False, want_residuals=False,
+                                               want_loss=False)
+            table[:, s0:s0 + n].copy_(ids)
+    RF.quantize_forward(chunk[:65536], cb64, RF.MODE_EVAL, want_embeddings=False, want_residuals=False, want_loss=False)
+    fence()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    tokenize_shard()
+    b.record()
+    fence()
+    ms = maxed(a.elapsed_time(b))
+    out["tokenize_100m"] = {"items": n_total, "items_per_gpu": n_shard, "per_gpu_ms": ms, "items_per_s": n_total / (ms * 1e-3),
+                            "shape": "d=64, 3x256, ids only", "collectives": 0,
+                            "protocol": "SURVEY 8d: resident 4M-item chunk cycled, [3, N/G] int64 id table written per rank; "
+                                        "barrier + max over ranks"}
+    del chunk, table
+    # ---- (3) sharded k-means: 10 fixed iterations over 10M x 32, K = 256 ---------------------------------------------
+    n_pts = 10_000_000
+    lo, hi = R.parallel.shard_range(n_pts, rank, world)
+    pts = torch.randn(hi - lo, D, device=dev, generator=torch.Generator(device=dev).manual_seed(11 + rank))
+    cent = torch.randn(K, D, device=dev, generator=torch.Generator(device=dev).manual_seed(5))      # same on every rank
+    assign = torch.empty(hi - lo, dtype=torch.int64, device=dev)
+
+    def km_iter():
+        _, sums, counts, n_changed = RF.kmeans_assign_accumulate(pts, cent, assign)
+        if world > 1:
+            packed = torch.cat([sums.reshape(-1).double(), counts.double(), n_changed.double()])
+            dist.all_reduce(packed)
+            kd = sums.numel()
+            sums = packed[:kd].float().reshape(sums.shape)
+            counts = packed[kd:kd + counts.numel()].round().long()
+        RF.kmeans_update(sums, counts, cent)
+    assign.zero_()
+    km_iter()
+    km_iter()
+    fence()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(10):
+        km_iter()
+    b.record()
+    fence()
+    ms = maxed(a.elapsed_time(b)) / 10
+    hbm, _ = peaks()
+    out["kmeans_10m"] = {"points": n_pts, "points_per_gpu": hi - lo, "k": K, "d": D, "iterations": 10, "ms_per_iter": ms,
+                         "points_per_s": n_pts / (ms * 1e-3),
+                         "hbm_frac": ((hi - lo) * 4 * D / (ms * 1e-3) / 1e9) / hbm,
+                         "collective": None if world == 1 else "NCCL all_reduce of [K*D + K + 1] fp64 per iteration"}
+    del pts, assign
+    return out
 
 
 def run_engine(args):
@@ -370,22 +532,43 @@ def run_engine(args):
         b.record()
         return a, b
 
+    def timed_block(fn):
+        """EXACTLY K steps bracketed by barrier + synchronize on both sides; device time of the block, max over ranks."""
+        fence()
+        a, b = timed(fn, args.steps)
+        fence()
+        t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    def timed_blocks(fn):
+        """A K-step block lasts ~1 ms here, one context switch away from noise: repeat it until --min-timed-s of device
+        time has elapsed (every rank runs the same number of blocks: the count comes from the max-reduced first block)
+        and report the MEDIAN block."""
+        first = timed_block(fn)
+        n_more = int(min(400, max(2, args.min_timed_s * 1e3 / max(first, 1e-3))))
+        blocks = [first] + [timed_block(fn) for _ in range(n_more)]
+        srt = sorted(blocks)
+        return srt[len(srt) // 2], {"blocks": len(blocks), "block_ms_median": srt[len(srt) // 2], "block_ms_min": srt[0],
+                                    "block_ms_max": srt[-1], "steps_per_block": args.steps}
+
     for i in range(args.warmup):
         run_step(i)
     fence()
     l0 = R.launch_count()
     with ClockSampler(local) as clk:
-        fence()
-        t_start, t_end = timed(run_step, args.steps)
-        fence()
+        ms_total, timing = timed_blocks(run_step)
         # the dominant kernels on their own, same ring, same clocks window (roofline legs)
-        f0, f1 = timed(run_fwd, args.steps)
-        b0, b1 = timed(run_bwd, args.steps)
-        fence()
-    launches = (launches_per_step * args.steps) if use_graphs else (R.launch_count() - l0)
-    ms_total = t_start.elapsed_time(t_end)
-    fwd_ms = f0.elapsed_time(f1) / args.steps
-    bwd_ms = b0.elapsed_time(b1) / args.steps
+        fwd_block, _ = timed_blocks(run_fwd)
+        bwd_block, _ = timed_blocks(run_bwd)
+    launches = (launches_per_step * args.steps) if use_graphs else None
+    if launches is None:                                # eager: count one block
+        l0 = R.launch_count()
+        timed_block(run_step)
+        launches = R.launch_count() - l0
+    fwd_ms = fwd_block / args.steps
+    bwd_ms = bwd_block / args.steps
 
     # ---- e2e: public module API, host buffers, copies inside the timed region ------------------
     model = R.RqVae(input_dim=D, embed_dim=D, hidden_dims=[], codebook_size=K, codebook_kmeans_init=False,
@@ -515,6 +698,11 @@ def run_engine(args):
     torch.cuda.synchronize()
     ids_only_ms = a.elapsed_time(b) / 20
 
+    extras = {}
+    if not args.no_extras:
+        extras = side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss_h, xs, cbs, g_embs, g_loss,
+                           mode, fence)
+
     stats = torch.tensor([ms_total, e2e_s * 1e3, float(launches)], dtype=torch.float64, device=dev)
     if world > 1:
         mx = stats.clone()
@@ -539,7 +727,8 @@ def run_engine(args):
                     "h2d_bytes_per_step": B_PER_GPU * D * 4, "d2h_bytes_per_step": B_PER_GPU * 4 + L * B_PER_GPU * 8},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "unit": "GB/s",
-                         "frac": achieved / hbm, "traffic": ncu_traffic(dom), "peak_source": which + " (burst copy)",
+                         "frac": achieved / hbm, "traffic": ncu_traffic(dom)[0], "traffic_source": ncu_traffic(dom)[1],
+                         "peak_source": which + " (burst copy)",
                          "algorithmic_bytes_per_launch": B_PER_GPU * BYTES_FWD, "launch_ms": dom_ms},
             "clocks": clk.summary(),
             "extra": {"fwd_ms": fwd_ms, "bwd_ms": bwd_ms, "ids_only_ms": ids_only_ms,
@@ -550,13 +739,12 @@ def run_engine(args):
                       "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode,
                       "grad_exchange": (None if world == 1 else ("rq_peer_allreduce_f32 (peer memory, " + ("in the step graph)" if peer_inline else "side stream beside the graphs)"))
                                         if peer is not None else "NCCL all_reduce, async beside the graphs"),
-                      "e2e_result_checked": e2e_ok},
+                      "e2e_result_checked": e2e_ok, "timing": timing, **extras},
         }
         if not args.no_cpu_baseline and world == 1:
-            ips, ms, cores = cpu_reference_run(args.cpu_sample_items, 3, 1)
-            out["cpu_baseline"] = {"value": ips, "unit": "items/s", "cores": cores, "kind": "port",
-                                   "sample": f"3 steps x {args.cpu_sample_items} items fwd+bwd, oracle/rq_oracle.py "
-                                             f"(torch CPU ATen fp32, {cores} threads)"}
+            ips, ms, cores, kind, what = cpu_reference_run(args.cpu_sample_items, 3, 1)
+            out["cpu_baseline"] = {"value": ips, "unit": "items/s", "cores": cores, "kind": kind,
+                                   "sample": f"3 steps x {args.cpu_sample_items} items fwd+bwd, {what}, {cores} threads"}
         emit(json.dumps(out))
     if world > 1:
         # Captured NCCL all-reduces live inside the step graphs; tearing the communicator down under them

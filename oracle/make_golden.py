@@ -189,6 +189,76 @@ def golden_rqvae_mlp(ref, name, seed):
     np.savez_compressed(os.path.join(OUT, name), **out)
 
 
+def golden_rqvae_forward_cat(ref, name, seed, n_cat=18):
+    """`RqVae.forward` (modules/rqvae.py:140-165, un-compiled body) with categorical features: the decoder output is
+    split into an L2-normalised dense part and n_cat logits (rqvae.py:146), CategoricalReconstuctionLoss
+    (modules/loss.py:19-30).  All five outputs + gradients."""
+    Q, R = ref.quantize, ref.rqvae
+    torch.manual_seed(seed)
+    B, IN, D, K, L = 160, 40 + n_cat, 16, 32, 3
+    model = R.RqVae(input_dim=IN, embed_dim=D, hidden_dims=[32], codebook_size=K, codebook_kmeans_init=False,
+                    codebook_mode=Q.QuantizeForwardMode.STE, n_layers=L, commitment_weight=0.25,
+                    n_cat_features=n_cat)
+    gen = torch.Generator().manual_seed(seed + 1)
+    dense = torch.nn.functional.normalize(torch.randn(B, IN - n_cat, generator=gen), dim=-1)
+    cats = (torch.rand(B, n_cat, generator=gen) < 0.2).float()
+    x = torch.cat([dense, cats], dim=-1)
+    with torch.no_grad():
+        res = model.encode(x).clone()
+        model.eval()
+        for l in range(L):
+            idx = torch.randint(0, B, (K,), generator=gen)         # duplicates on purpose: p_unique_ids < 1
+            model.layers[l].embedding.weight.copy_(res[idx] * 0.9)
+            res = res - model.layers[l](res, 0.2).embeddings
+    x[B // 2:B // 2 + 20] = x[:20]                                   # repeated items -> repeated id tuples
+    out = {"x": _np(x), "n_cat": np.int64(n_cat)}
+    for k, v in model.state_dict().items():
+        out["sd::" + k] = _np(v)
+    model.train()
+    fwd = R.RqVae.forward
+    inner = getattr(fwd, "_torchdynamo_orig_callable", None) or getattr(fwd, "__wrapped__", None)
+    assert inner is not None, "cannot reach the un-compiled body of RqVae.forward"
+    batch = ref.schemas.SeqBatch(user_ids=None, ids=None, ids_fut=None, x=x, x_fut=None, seq_mask=None)
+    losses = inner(model, batch, 0.2)
+    out["train_loss"] = _np(losses.loss)
+    out["train_recon"] = _np(losses.reconstruction_loss)
+    out["train_rqvae_loss"] = _np(losses.rqvae_loss)
+    out["train_p_unique"] = _np(losses.p_unique_ids)
+    out["train_embs_norm"] = _np(losses.embs_norm)
+    losses.loss.backward()
+    out["train_grad_enc0"] = _np(model.encoder.mlp[0].weight.grad)
+    out["train_grad_cb"] = _np(torch.stack([model.layers[l].embedding.weight.grad for l in range(L)]))
+    np.savez_compressed(os.path.join(OUT, name), **out)
+
+
+def golden_checkpoint(ref, name, seed):
+    """A checkpoint file written exactly as the reference's training driver writes it (train_rqvae.py:209-221:
+    {"iter", "model", "model_config", "optimizer"}; model_config = RqVae.config = locals() of __init__, i.e. it
+    pickles the reference's own classes), plus the ids the reference computes from it on a probe batch."""
+    Q, R = ref.quantize, ref.rqvae
+    torch.manual_seed(seed)
+    B, IN, D, K, L = 64, 24, 8, 16, 3
+    model = R.RqVae(input_dim=IN, embed_dim=D, hidden_dims=[16], codebook_size=K, codebook_kmeans_init=False,
+                    codebook_mode=Q.QuantizeForwardMode.ROTATION_TRICK, n_layers=L, commitment_weight=0.25,
+                    n_cat_features=0)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3)
+    gen = torch.Generator().manual_seed(seed + 1)
+    x = torch.nn.functional.normalize(torch.randn(B, IN, generator=gen), dim=-1)
+    model.train()
+    out_t = model.get_semantic_ids(x, 0.2)
+    (out_t.quantize_loss.mean() + out_t.embeddings.sum() * 1e-3).backward()
+    opt.step()                                                        # so that the optimizer state is not empty
+    state = {"iter": 41, "model": model.state_dict(), "model_config": model.config, "optimizer": opt.state_dict()}
+    torch.save(state, os.path.join(OUT, name + ".pt"))
+    model.eval()
+    with torch.no_grad():
+        ev = model.get_semantic_ids(x)
+    out = {"x": _np(x), "eval_ids": _np(ev.sem_ids), "eval_loss": _np(ev.quantize_loss), "iter": np.int64(41)}
+    for k, v in model.state_dict().items():
+        out["sd::" + k] = _np(v)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+
+
 def golden_kmeans(ref, name, seed):
     """init/kmeans.py: a full run (seeded np.random.choice init, :36) and single
     _update_centroids steps, one of them with empty clusters (torch.randint reseed, :53)."""
@@ -309,6 +379,8 @@ def main():
     golden_rq_stack(ref, "rq_stack_norm_simvq_d16_k32_l2.npz", B=90, D=16, K=32, L=2, seed=6,
                     modes=("eval", "ste", "rot"), normalize=True, sim_vq=True)
     golden_rqvae_mlp(ref, "rqvae_mlp_small.npz", seed=7)
+    golden_rqvae_forward_cat(ref, "rqvae_forward_cat18.npz", seed=10)
+    golden_checkpoint(ref, "rqvae_checkpoint_ref", seed=11)
     golden_kmeans(ref, "kmeans_small.npz", seed=8)
     golden_tokenizer(ref, "tokenizer_small.npz", seed=9)
     for f in sorted(os.listdir(OUT)):

@@ -6,11 +6,15 @@ stop_threshold).run(x) -> KmeansOutput(centroids, assignment)`.  The assignment 
 (max shift, number of empty clusters, number of changed assignments) instead of the K + 1 host
 syncs of the reference's Python loop.
 
-Multi-GPU: points are row-sharded, centroids replicated.  Per iteration the [K, D] sums, the
-[K] counts and the changed-assignment count are all-reduced (NCCL over NVLink when
-torch.distributed is initialised); initial rows and empty-cluster re-seeds are chosen by global
-row index so every rank ends up with bit-identical centroids.  The reference runs k-means
-independently per rank from the unseeded NumPy RNG and never re-synchronises.
+Rank-local by default, like the reference: it runs k-means independently per rank on the same first
+20,000 rows (train_rqvae.py:140) and never synchronises, so `Kmeans(k).run(x)` makes no collective call even when
+torch.distributed is initialised.
+
+Multi-GPU is OPT-IN — `Kmeans(k, group=some_group)` or `distributed=True` — and then every rank of the group
+must call `run` with ITS row shard of the global point set: points are row-sharded, centroids replicated; per
+iteration the [K, D] sums, the [K] counts and the changed-assignment count are all-reduced (NCCL over NVLink);
+initial rows and empty-cluster re-seeds are chosen by global row index on rank 0 and broadcast, so every rank
+ends up with bit-identical centroids.
 """
 from typing import NamedTuple, Optional
 
@@ -48,13 +52,14 @@ class Kmeans:
         self.centroids = None
         self.assignment = None
         self.group = group
-        # distributed=None: shard-aware iff torch.distributed is initialised with world_size > 1
+        # opt-in: sharded iff a group is passed or distributed=True (and the group has more than one rank)
         self.distributed = distributed
         self.n_iters_run = 0
 
     # -- sharding helpers ----------------------------------------------------------------
     def _is_dist(self) -> bool:
-        return _dist_ready(self.group) if self.distributed is None else bool(self.distributed)
+        want = (self.group is not None) if self.distributed is None else bool(self.distributed)
+        return want and _dist_ready(self.group)
 
     def _shard_layout(self, n_local: int, device):
         """(offset of this rank's rows in the global order, global row count)."""

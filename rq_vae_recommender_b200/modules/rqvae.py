@@ -25,6 +25,46 @@ except Exception:  # pragma: no cover
         pass
 
 
+class _Placeholder:
+    """Stands in for a class of the reference tree that is not importable while reading its checkpoint."""
+
+    def __init__(self, *a, **k):
+        pass
+
+    def __setstate__(self, state):
+        pass
+
+    def __call__(self, *a, **k):          # enum lookups such as QuantizeForwardMode(3)
+        return self
+
+
+def load_reference_checkpoint(path: str, map_location=None) -> dict:
+    """torch.load of a reference checkpoint; falls back to a tolerant unpickler when the file refers to classes of
+    the reference's own module tree (`modules.*`, `init.*`, ...) that cannot be imported here."""
+    try:
+        return torch.load(path, map_location=map_location, weights_only=False)
+    except (ModuleNotFoundError, AttributeError, ImportError):
+        pass
+    import pickle
+    import types
+
+    class _TolerantUnpickler(pickle.Unpickler):
+        def find_class(self, module, name):
+            try:
+                return super().find_class(module, name)
+            except (ModuleNotFoundError, AttributeError, ImportError):
+                return type(name, (_Placeholder,), {"__module__": module})
+
+    shim = types.ModuleType("rq_tolerant_pickle")
+    shim.Unpickler = _TolerantUnpickler
+    shim.load = lambda f, **kw: _TolerantUnpickler(f, **kw).load()
+    shim.__name__ = "pickle"
+    for attr in ("dumps", "dump", "loads", "Pickler", "PickleError", "UnpicklingError", "HIGHEST_PROTOCOL",
+                 "DEFAULT_PROTOCOL"):
+        setattr(shim, attr, getattr(pickle, attr))
+    return torch.load(path, map_location=map_location, weights_only=False, pickle_module=shim)
+
+
 class RqVaeOutput(NamedTuple):
     embeddings: Tensor
     residuals: Tensor
@@ -87,7 +127,12 @@ class RqVae(nn.Module, PyTorchModelHubMixin):
         return next(self.encoder.parameters()).device
 
     def load_pretrained(self, path: str) -> None:
-        state = torch.load(path, map_location=self.device, weights_only=False)
+        """Loads a checkpoint written by the reference's training driver (train_rqvae.py:209-221:
+        {"iter", "model", "model_config", "optimizer"}; rqvae.py:103-106).  `model_config` is `RqVae.config`, i.e. the
+        `locals()` of the reference's `__init__`: it pickles the reference's own classes (`modules.rqvae.RqVae`,
+        `modules.quantize.QuantizeForwardMode`).  When those modules are not importable the file is read again with
+        an unpickler that stands unknown classes in with inert placeholders; only "model" and "iter" are used."""
+        state = load_reference_checkpoint(path, map_location=self.device)
         self.load_state_dict(state["model"])
         print(f"---Loaded RQVAE Iter {state['iter']}---")
 

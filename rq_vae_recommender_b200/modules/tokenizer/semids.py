@@ -81,18 +81,24 @@ class SemanticIdTokenizer(nn.Module):
 
     @torch.no_grad()
     @eval_mode
-    def precompute_corpus_ids(self, movie_dataset, group=None) -> Tensor:
+    def precompute_corpus_ids(self, movie_dataset, group=None, distributed: bool = False) -> Tensor:
         """`movie_dataset[list_of_idx]` must return a SeqBatch whose `.x` is [n, input_dim]
         (data/processed.py:74-84 of the reference).
 
-        With torch.distributed initialised (world size G > 1) every rank tokenises only its contiguous
-        row shard (N/G items; no data-path collective), the [N/G, L] ids are all-gathered once, and each
-        rank builds the identical [N, L+1] table — the dedup column needs the global corpus order."""
+        Rank-local by default, like the reference (its driver calls this under `accelerator.is_main_process` only,
+        train_rqvae.py:209-227): no collective is issued even when torch.distributed is initialised.
+
+        Sharded tokenisation is OPT-IN (`group=` or `distributed=True`; then EVERY rank of the group must make the
+        call): each rank tokenises only its contiguous row shard (N/G items, no data-path collective) and builds
+        the dedup column of its shard from its own sort plus the per-key counts of the lower ranks (one all-gather
+        of a radix^L count table when that fits 2^26 entries; otherwise the [N/G, L] ids are gathered and every rank
+        sorts the corpus); the [N/G, L+1] shards are then all-gathered so every rank holds the full table."""
         from ... import parallel
         n = len(movie_dataset)
         device = self.rq_vae.device
         lo, hi = 0, n
-        if parallel.is_distributed(group):
+        sharded = (distributed or group is not None) and parallel.is_distributed(group)
+        if sharded:
             import torch.distributed as dist
             lo, hi = parallel.shard_range(n, dist.get_rank(group), dist.get_world_size(group))
         def host_batches():
@@ -104,8 +110,10 @@ class SemanticIdTokenizer(nn.Module):
         from ...data.utils import DevicePrefetcher
         chunks = [self.semantic_ids(batch.x) for batch in DevicePrefetcher(host_batches(), device)]
         ids = torch.cat(chunks, dim=0) if chunks else torch.zeros((0, self.n_layers), dtype=torch.int64, device=device)
-        ids = parallel.gather_row_shards(ids.contiguous(), n, group)
-        self.cached_ids = RF.corpus_table(ids, self.codebook_size)
+        if sharded:
+            self.cached_ids = parallel.sharded_corpus_table(ids.contiguous(), n, self.codebook_size, group)
+        else:
+            self.cached_ids = RF.corpus_table(ids, self.codebook_size)
         self._prefix_index = {}
         return self.cached_ids
 

@@ -131,3 +131,41 @@ def gather_row_shards(local: torch.Tensor, n: int, group=None) -> torch.Tensor:
         a, b = shard_range(n, r, world)
         parts.append(out[r * per:r * per + (b - a)])
     return torch.cat(parts, dim=0)
+
+
+def sharded_corpus_table(local_ids: torch.Tensor, n: int, codebook_size: int, group=None,
+                         max_dense_keys: int = 1 << 26, table_fn=None) -> torch.Tensor:
+    """[N/G, L] ids of this rank's contiguous row shard (shard_range order) -> the full [N, L+1] corpus table
+    `[ids | dedup]` on every rank (semids.py:86-99: dedup = number of EARLIER corpus items with the same tuple).
+
+    SURVEY.md 8(e) partitioning: dedup(item) = rank of the item among this shard's items with the same key (local
+    sort, rq_corpus_table) + number of items with that key on the LOWER ranks.  The second term comes from one
+    all-gather of the per-rank key-count table (radix^L int32 entries: 64 MB at 3 x 256) — no rank sorts more than
+    its own N/G keys.  Key spaces beyond `max_dense_keys` entries fall back to gathering the ids and sorting the
+    whole corpus on every rank."""
+    import torch.distributed as dist
+    if table_fn is None:                                 # the CUDA dedup kernel; tests inject a CPU stand-in
+        from . import functional as RF
+        table_fn = RF.corpus_table
+    if not is_distributed(group):
+        return table_fn(local_ids, codebook_size)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    Lv = local_ids.shape[1]
+    n_keys = int(codebook_size) ** Lv
+    if n_keys > max_dense_keys:
+        ids = gather_row_shards(local_ids, n, group)
+        return table_fn(ids, codebook_size)
+    local = table_fn(local_ids, codebook_size) if local_ids.shape[0] else \
+        torch.zeros((0, Lv + 1), dtype=torch.int64, device=local_ids.device)
+    key = torch.zeros(local_ids.shape[0], dtype=torch.int64, device=local_ids.device)
+    for l in range(Lv):
+        key = key * int(codebook_size) + local_ids[:, l]
+    counts = torch.bincount(key, minlength=n_keys).to(torch.int32)
+    flat = torch.empty((world * n_keys,), dtype=torch.int32, device=local_ids.device)
+    dist.all_gather_into_tensor(flat, counts, group=group)
+    all_counts = flat.view(world, n_keys)
+    if rank > 0:
+        below = all_counts[:rank].sum(dim=0, dtype=torch.int64)
+        local[:, -1] += below[key]
+    del all_counts, flat
+    return gather_row_shards(local.contiguous(), n, group)

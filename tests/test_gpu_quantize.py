@@ -251,6 +251,54 @@ def test_backward_with_partial_upstream_gradients(which, mode):
         assert_close(cin.grad.cpu(), gcb_ref, f"{which} grad codebooks")
 
 
+@pytest.mark.parametrize("name,kw", [
+    ("rqvae_mlp_small.npz", dict(input_dim=64, embed_dim=32, hidden_dims=[48, 40], codebook_size=64, n_layers=3,
+                                 n_cat_features=0, mode="rot")),
+    ("rqvae_forward_cat18.npz", dict(input_dim=58, embed_dim=16, hidden_dims=[32], codebook_size=32, n_layers=3,
+                                     n_cat_features=18, mode="ste")),
+])
+def test_rqvae_forward_golden(name, kw):
+    """`RqVae.forward` (reference modules/rqvae.py:140-165) — loss, reconstruction_loss, rqvae_loss, embs_norm,
+    p_unique_ids and the gradients it sends to the encoder and the codebooks — against fixtures produced by the
+    un-compiled body of the reference's forward, with n_cat_features = 0 and 18."""
+    z = load_golden(name)
+    mode = {"rot": R.QuantizeForwardMode.ROTATION_TRICK, "ste": R.QuantizeForwardMode.STE}[kw.pop("mode")]
+    m = R.RqVae(codebook_kmeans_init=False, codebook_mode=mode, commitment_weight=0.25, **kw).to(DEV)
+    m.load_state_dict({k[4:]: torch.from_numpy(z[k]) for k in z.keys() if k.startswith("sd::")})
+    m.train()
+    x = torch.from_numpy(z["x"]).to(DEV)
+    batch = R.SeqBatch(user_ids=None, ids=None, ids_fut=None, x=x, x_fut=None, seq_mask=None)
+    out = m(batch, 0.2)
+    assert isinstance(out, R.RqVaeComputedLosses)
+    assert_close(out.loss, torch.from_numpy(z["train_loss"]), "loss")
+    assert_close(out.reconstruction_loss, torch.from_numpy(z["train_recon"]), "reconstruction_loss")
+    assert_close(out.rqvae_loss, torch.from_numpy(z["train_rqvae_loss"]), "rqvae_loss")
+    assert out.embs_norm.shape == tuple(z["train_embs_norm"].shape)
+    assert_close(out.embs_norm, torch.from_numpy(z["train_embs_norm"]), "embs_norm")
+    assert float(out.p_unique_ids) == pytest.approx(float(z["train_p_unique"]), abs=1e-7)
+    out.loss.backward()
+    assert_close(m.encoder.mlp[0].weight.grad, torch.from_numpy(z["train_grad_enc0"]), "grad encoder.mlp.0")
+    gcb = torch.stack([layer.embedding.weight.grad for layer in m.layers])
+    assert_close(gcb, torch.from_numpy(z["train_grad_cb"]), "grad codebooks", tol=2e-3)
+
+
+def test_reference_checkpoint_ids_on_gpu():
+    """A checkpoint file written by the reference's driver (train_rqvae.py:209-221) loaded through
+    `load_pretrained`: the semantic ids of the probe batch are the reference's."""
+    import os
+    from conftest import GOLDEN
+    z = load_golden("rqvae_checkpoint_ref.npz")
+    m = R.RqVae(input_dim=24, embed_dim=8, hidden_dims=[16], codebook_size=16, codebook_kmeans_init=False,
+                codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, n_layers=3, n_cat_features=0).to(DEV)
+    m.load_pretrained(os.path.join(GOLDEN, "rqvae_checkpoint_ref.pt"))
+    m.eval()
+    with torch.no_grad():
+        out = m.get_semantic_ids(torch.from_numpy(z["x"]).to(DEV))
+    same = (out.sem_ids.cpu() == torch.from_numpy(z["eval_ids"])).all(dim=1)
+    assert same.float().mean() > 0.97
+    assert_close(out.quantize_loss.cpu()[same], torch.from_numpy(z["eval_loss"])[same], "loss")
+
+
 def test_c1_full_corpus_get_semantic_ids():
     """BASELINE config 1 at full size: 12,101 items, 768-d, encoder [512,256,128] -> d=32, 3x256, codebooks
     k-means-initialised on first use (quantize.py:102-103).  `RqVae.get_semantic_ids` on the GPU against the

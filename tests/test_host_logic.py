@@ -37,6 +37,63 @@ def test_state_dict_keys_and_load_from_reference_fixture():
     assert float(q.weight.min()) >= 0.0 and float(q.weight.max()) <= 1.0      # U[0,1) init
 
 
+def test_reference_checkpoint_file_loads_without_the_reference_tree(tmp_path, capsys):
+    """tests/golden/rqvae_checkpoint_ref.pt was written by the reference exactly as train_rqvae.py:209-221 does
+    ({"iter", "model", "model_config", "optimizer"}); its `model_config` pickles the reference's own classes, which do
+    not exist here.  `load_pretrained` (rqvae.py:103-106) must still restore every tensor bit for bit."""
+    import os
+    from conftest import GOLDEN
+    z = load_golden("rqvae_checkpoint_ref.npz")
+    m = R.RqVae(input_dim=24, embed_dim=8, hidden_dims=[16], codebook_size=16, codebook_kmeans_init=False,
+                codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, n_layers=3, n_cat_features=0)
+    m.load_pretrained(os.path.join(GOLDEN, "rqvae_checkpoint_ref.pt"))
+    assert "Loaded RQVAE Iter 41" in capsys.readouterr().out
+    sd = m.state_dict()
+    want = {k[4:]: torch.from_numpy(z[k]) for k in z.keys() if k.startswith("sd::")}
+    assert sorted(sd.keys()) == sorted(want.keys())
+    for k in want:
+        assert torch.equal(sd[k].cpu(), want[k]), k
+    # and the way back: a checkpoint written with the same four keys from the mirror loads into a fresh mirror
+    opt = torch.optim.AdamW(m.parameters(), lr=1e-3)
+    state = {"iter": 7, "model": m.state_dict(), "model_config": m.config, "optimizer": opt.state_dict()}
+    path = tmp_path / "checkpoint_7.pt"
+    torch.save(state, str(path))
+    m2 = R.RqVae(input_dim=24, embed_dim=8, hidden_dims=[16], codebook_size=16, codebook_kmeans_init=False,
+                 codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, n_layers=3, n_cat_features=0)
+    m2.load_pretrained(str(path))
+    for k in want:
+        assert torch.equal(m2.state_dict()[k].cpu(), want[k]), k
+
+
+def test_checkpoint_round_trip_with_the_live_reference(tmp_path):
+    """Both directions against the UNMODIFIED reference (container only): the reference loads a checkpoint the mirror
+    wrote, the mirror loads one the reference wrote."""
+    import ref_import
+    if not ref_import.available():
+        pytest.skip("reference tree not mounted")
+    ref = ref_import.load()
+    kw = dict(input_dim=24, embed_dim=8, hidden_dims=[16], codebook_size=16, codebook_kmeans_init=False, n_layers=3,
+              n_cat_features=0)
+    mine = R.RqVae(codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, **kw)
+    theirs = ref.rqvae.RqVae(codebook_mode=ref.quantize.QuantizeForwardMode.ROTATION_TRICK, **kw)
+    p1 = tmp_path / "from_mirror.pt"
+    torch.save({"iter": 3, "model": mine.state_dict(), "model_config": {k: v for k, v in mine.config.items()
+                                                                         if k not in ("self", "__class__")},
+                "optimizer": torch.optim.AdamW(mine.parameters()).state_dict()}, str(p1))
+    theirs.load_pretrained(str(p1))
+    for k, v in mine.state_dict().items():
+        assert torch.equal(theirs.state_dict()[k], v), k
+    with torch.no_grad():
+        for prm in theirs.parameters():
+            prm.add_(0.5)
+    p2 = tmp_path / "from_reference.pt"
+    torch.save({"iter": 4, "model": theirs.state_dict(), "model_config": theirs.config,
+                "optimizer": torch.optim.AdamW(theirs.parameters()).state_dict()}, str(p2))
+    mine.load_pretrained(str(p2))
+    for k, v in theirs.state_dict().items():
+        assert torch.equal(mine.state_dict()[k], v), k
+
+
 def test_constructor_signatures_match_reference():
     import inspect
     sig = inspect.signature(R.Quantize.__init__)
@@ -91,7 +148,8 @@ def _gloo_worker(rank, world, port, q):
         full = torch.randn(11, 4, generator=g)
         lo, hi = shard_range(11, rank, world)
         x = full[lo:hi]
-        km = Kmeans(k=3)
+        assert not Kmeans(k=3)._is_dist()        # rank-local unless asked: no collective behind the reference's call
+        km = Kmeans(k=3, distributed=True)
         off, n = km._shard_layout(x.shape[0], x.device)
         rows = km._global_rows(x, [0, 5, 10, 6], off)
         np.random.seed(123 + rank)               # ranks disagree on purpose: rank 0's draw must win
@@ -100,6 +158,21 @@ def _gloo_worker(rank, world, port, q):
         from rq_vae_recommender_b200.parallel import gather_row_shards
         ids_full = torch.arange(11 * 3, dtype=torch.int64).reshape(11, 3)
         gathered = gather_row_shards(ids_full[lo:hi].contiguous(), 11)
+        # dedup column of the sharded corpus table: local rank within the key + counts of the lower ranks
+        from rq_vae_recommender_b200.parallel import sharded_corpus_table
+
+        def cpu_table(ids, _k):                  # stable cumcount in corpus order (semids.py:86-99), CPU stand-in
+            seen, col = {}, []
+            for row in ids.tolist():
+                col.append(seen.get(tuple(row), 0))
+                seen[tuple(row)] = col[-1] + 1
+            return torch.cat([ids, torch.tensor(col, dtype=torch.int64).reshape(-1, 1)], dim=1)
+        gd = torch.Generator().manual_seed(5)
+        corpus = torch.randint(0, 3, (23, 2), generator=gd)          # 9 keys, 23 items: plenty of duplicates
+        a, b = shard_range(23, rank, world)
+        dense = sharded_corpus_table(corpus[a:b].contiguous(), 23, 3, table_fn=cpu_table)
+        gathered_path = sharded_corpus_table(corpus[a:b].contiguous(), 23, 3, max_dense_keys=1, table_fn=cpu_table)
+        table_ok = torch.equal(dense, cpu_table(corpus, 3)) and torch.equal(gathered_path, cpu_table(corpus, 3))
         # codebook-gradient all-reduce (mean over ranks), the training step's one collective
         from rq_vae_recommender_b200.parallel import allreduce_codebook_grads
 
@@ -114,7 +187,7 @@ def _gloo_worker(rank, world, port, q):
         grads_ok = (torch.allclose(_Model.layers[0].embedding.weight.grad, torch.full((5, 4), 1.5))
                     and torch.allclose(_Model.layers[1].embedding.weight.grad, torch.full((5, 4), 15.0)))
         q.put((rank, off, n, torch.equal(rows, full[[0, 5, 10, 6]]), km.centroids.clone(),
-               torch.equal(gathered, ids_full), grads_ok))
+               torch.equal(gathered, ids_full), grads_ok, table_ok))
     finally:
         dist.destroy_process_group()
 
@@ -133,6 +206,7 @@ def test_kmeans_sharding_helpers_gloo_world2():
     assert torch.equal(res[0][4], res[1][4])     # identical initial centroids on both ranks
     assert res[0][5] and res[1][5]               # row-shard all-gather reassembles the global order
     assert res[0][6] and res[1][6]               # codebook gradients averaged over the two ranks
+    assert res[0][7] and res[1][7]               # sharded dedup column == single-process table, both strategies
 
 
 def test_data_utils_batch_to_and_cycle():
