@@ -409,16 +409,20 @@ def run_engine(args):
 
     peer = R.parallel.PeerAllReduce((L, K, D), slots=N_SLOTS) if use_peer else None
 
+    g_cb_bufs = [torch.empty((L, K, D), device=dev) for _ in range(N_SLOTS)] if peer is None else \
+        [peer.buffer[s] for s in range(N_SLOTS)]
+
     def step_compute(s):
+        # the step's order of work: zero the codebook-gradient buffer, fused forward, fused backward accumulating into
+        # it.  The memset comes first so that the two kernels are adjacent in the stream (programmatic dependent
+        # launch: the backward's CTAs are scheduled as the forward's retire).
+        g_cb_bufs[s].zero_()
         emb, res, ids, loss = RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP)
-        if peer is not None:
-            # the backward scatters into slot s of the symmetric buffer; one more launch averages it over the ranks
-            g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP,
-                                             g_codebooks_out=peer.buffer[s])
-            if peer_inline:
-                peer.all_reduce_(s, average=True)
-        else:
-            g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP)
+        g_x, g_cb = RF.quantize_backward(g_embs[s], None, g_loss, res, ids, cbs, mode, BETA, TEMP,
+                                         g_codebooks_out=g_cb_bufs[s], accumulate=True)
+        if peer is not None and peer_inline:
+            # the backward scattered into slot s of the symmetric buffer; one more launch averages it over the ranks
+            peer.all_reduce_(s, average=True)
         return loss, g_x, g_cb
 
     # N > 1: the codebook-gradient all-reduce (98,304 B, the path's one exchange) runs on its own stream so

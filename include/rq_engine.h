@@ -96,6 +96,17 @@ int rq_quantize_backward(const float* g_emb, const float* g_res, const float* g_
                          const float* gumbel_u, uint64_t seed, uint64_t offset,
                          float* g_x, float* g_codebooks, rq_stream_t stream);
 
+/* The same with flags.  RQ_BWD_ACCUMULATE: the codebook gradient is ADDED to what g_codebooks holds (gradient
+ * accumulation; or zeros the caller wrote before the forward, which keeps the forward and this kernel adjacent in
+ * the stream so that programmatic dependent launch can overlap this kernel's launch with the forward's tail).
+ * Honoured by the EVAL / STE / ROTATION_TRICK modes; GUMBEL_SOFTMAX overwrites. */
+#define RQ_BWD_ACCUMULATE 1
+int rq_quantize_backward_ex(const float* g_emb, const float* g_res, const float* g_loss,
+                            const float* residuals, const int64_t* ids, const float* codebooks,
+                            int64_t B, int D, int K, int L, int mode, float beta, float temperature,
+                            const float* gumbel_u, uint64_t seed, uint64_t offset,
+                            float* g_x, float* g_codebooks, int flags, rq_stream_t stream);
+
 /*
  * One k-means assignment + accumulation pass.  Replaces init/kmeans.py:41-57 (the [B,K,D]
  * broadcast, argmin, and the per-cluster masked means' numerators).

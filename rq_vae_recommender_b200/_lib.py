@@ -31,6 +31,9 @@ SIGNATURES = {
     "rq_quantize_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                                      c_int, c_int, c_int, c_float, c_float, c_void_p, c_uint64, c_uint64,
                                      c_void_p, c_void_p, c_void_p]),
+    "rq_quantize_backward_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                        c_int, c_int, c_int, c_float, c_float, c_void_p, c_uint64, c_uint64,
+                                        c_void_p, c_void_p, c_int, c_void_p]),
     "rq_kmeans_assign_accumulate": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int, c_void_p,
                                             c_void_p, c_void_p, c_int, c_void_p]),
     "rq_kmeans_update": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,

@@ -44,8 +44,8 @@ def build(force: bool = False, verbose: bool = False, experiments: bool = False)
     has none of them and reads no environment variable on a launch path."""
     os.makedirs(OBJ, exist_ok=True)
     stamp = os.path.join(OBJ, "digest.txt")
-    flags = NVCC_FLAGS + (["-DRQ_EXPERIMENTS"] if experiments else [])
-    dig = _digest() + ("+experiments" if experiments else "")
+    flags = NVCC_FLAGS + (["-DRQ_EXPERIMENTS"] if experiments else []) + os.environ.get("RQ_EXTRA_NVCC_FLAGS", "").split()
+    dig = _digest() + ("+experiments" if experiments else "") + os.environ.get("RQ_EXTRA_NVCC_FLAGS", "")
     if not force and os.path.exists(OUT) and os.path.exists(stamp) and open(stamp).read() == dig:
         return OUT
     nvcc = _nvcc()

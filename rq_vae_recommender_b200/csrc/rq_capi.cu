@@ -42,6 +42,14 @@ int sm_count() {
     return n;
 }
 
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("RQ_NO_PDL");
+        return !(e && atoi(e) != 0);
+    }();
+    return on;
+}
+
 // cudaFuncAttributeMaxDynamicSharedMemorySize is per (function, device): set it once for each pair.
 cudaError_t ensure_max_dynamic_smem(const void* fn, int bytes) {
     struct Entry { const void* fn; int dev; int bytes; };
@@ -112,6 +120,15 @@ extern "C" int rq_quantize_backward(const float* g_emb, const float* g_res, cons
                                     int D, int K, int L, int mode, float beta, float temperature,
                                     const float* gumbel_u, uint64_t seed, uint64_t offset, float* g_x,
                                     float* g_codebooks, rq_stream_t stream) {
+    return rq_quantize_backward_ex(g_emb, g_res, g_loss, residuals, ids, codebooks, B, D, K, L, mode, beta, temperature,
+                                   gumbel_u, seed, offset, g_x, g_codebooks, 0, stream);
+}
+
+extern "C" int rq_quantize_backward_ex(const float* g_emb, const float* g_res, const float* g_loss,
+                                       const float* residuals, const int64_t* ids, const float* codebooks, int64_t B,
+                                       int D, int K, int L, int mode, float beta, float temperature,
+                                       const float* gumbel_u, uint64_t seed, uint64_t offset, float* g_x,
+                                       float* g_codebooks, int flags, rq_stream_t stream) {
     RQ_CHECK_ARG(B >= 0 && K >= 1 && L >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_backward: need B >= 0, K >= 1, L >= 1");
     RQ_CHECK_ARG(pow2_dim(D), RQ_ERR_UNSUPPORTED_SHAPE, "rq_quantize_backward: unsupported embed_dim D=%d", D);
     RQ_CHECK_ARG(mode >= RQ_MODE_EVAL && mode <= RQ_MODE_ROTATION_TRICK, RQ_ERR_INVALID_ARGUMENT,
@@ -122,6 +139,7 @@ extern "C" int rq_quantize_backward(const float* g_emb, const float* g_res, cons
     BwdParams p;
     p.g_emb = g_emb; p.g_res = g_res; p.g_loss = g_loss; p.res = residuals; p.ids = ids; p.cb = codebooks;
     p.B = B; p.K = K; p.L = L; p.mode = mode; p.beta = beta; p.g_x = g_x; p.g_cb = g_codebooks;
+    p.accumulate = (flags & RQ_BWD_ACCUMULATE) ? 1 : 0;
     cudaStream_t st = (cudaStream_t)stream;
     if (mode == RQ_MODE_GUMBEL_SOFTMAX) {
         RQ_CHECK_ARG(temperature > 0.f, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_backward: temperature must be > 0");

@@ -45,6 +45,7 @@ struct BwdParams {
     float beta;
     float* g_x;
     float* g_cb;
+    int accumulate = 0;      // 1: add into g_cb as it is (no zeroing)
 };
 
 

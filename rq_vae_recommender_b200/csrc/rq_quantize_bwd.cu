@@ -18,6 +18,17 @@
 
 namespace rq {
 
+// Timing what-ifs (skip the reductions / stores / math of a kernel; wrong gradients by construction) and the switches
+// that route around a kernel exist only in -DRQ_EXPERIMENTS builds; the release library reads no environment variable
+// on this path.
+#ifdef RQ_EXPERIMENTS
+static bool bwd_knob(const char* name) { return getenv(name) != nullptr; }
+static int bwd_dbg() { return getenv("RQ_BWD_DBG") ? atoi(getenv("RQ_BWD_DBG")) : 0; }
+#else
+static constexpr bool bwd_knob(const char*) { return false; }
+static constexpr int bwd_dbg() { return 0; }
+#endif
+
 constexpr int kBwdThreads = 256;
 
 template <int LPR>
@@ -627,212 +638,6 @@ __global__ void __launch_bounds__(bwdrow::THREADS, 2) rq_bwd_row_kernel(BwdParam
     asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
-// ---- D = 32, occupancy-first variant --------------------------------------------------------------------------
-// The ring-buffered kernel above keeps r, e, go and the prefetched codewords of a row in registers (250+ per
-// thread, 8 warps per SM) and spends most of its time on dependent-instruction latency (ncu: 31 % issue
-// utilisation).  Here a warp's tile lives in shared memory — residual rows | gradient rows | codeword rows, 12 KB,
-// filled by cp.async in the coalesced 4-rows-per-instruction pattern (the codeword gather included, so no load
-// passes through registers) — and is streamed through the math twice (dot products, then the update), leaving
-// only the running gradient G in registers: ~16 warps per SM hide each other's load and FMA latency.
-namespace bwdrow2 {
-constexpr int D = 32, TW = 32, WARPS = 8, THREADS = 32 * WARPS;
-constexpr int TILE_BYTES = TW * D * 4;
-constexpr int WARP_BYTES = 3 * TILE_BYTES;
-}  // namespace bwdrow2
-
-template <int MODE>
-__global__ void __launch_bounds__(bwdrow2::THREADS, 2) rq_bwd_row2_kernel(BwdParams p, int n_tiles, int dbg) {
-    using namespace bwdrow2;
-    using bwdrow::sw_off;
-    extern __shared__ __align__(1024) uint8_t smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint8_t* tR = smem + warp * WARP_BYTES;
-    uint8_t* tG = tR + TILE_BYTES;
-    uint8_t* tE = tG + TILE_BYTES;
-    const uint32_t tR_u32 = (uint32_t)__cvta_generic_to_shared(tR);
-    const bool has_gemb = p.g_emb != nullptr;
-    const int chunk = lane & 7, sub = lane >> 3;
-    const uint32_t co_sw = sw_off(sub, chunk);
-    auto co_off = [&](int i) -> uint32_t { return (co_sw + 512u * i) ^ ((i & 1) ? 64u : 0u); };
-    const int wglobal = blockIdx.x * WARPS + warp, nwarps = gridDim.x * WARPS;
-
-    int ids_n[kBwdMaxL];
-    float gl_n = 0.f;
-    auto load_ids = [&](int tile) {
-        const int64_t row = (int64_t)tile * TW + lane;
-        const bool ok = tile < n_tiles && row < p.B;
-#pragma unroll
-        for (int l = 0; l < kBwdMaxL; ++l) ids_n[l] = (ok && l < p.L) ? (int)__ldg(p.ids + (int64_t)l * p.B + row) : 0;
-        gl_n = (ok && p.g_loss) ? __ldg(p.g_loss + row) : 0.f;
-    };
-    auto pick = [&](const int (&a)[kBwdMaxL], int l) { return (l == 3) ? a[3] : (l == 2) ? a[2] : (l == 1) ? a[1] : a[0]; };
-    load_ids(wglobal);
-    // experiment: phase offset between the CTAs sharing an SM (dbg >> 8 = delay in units of 256 ns for odd CTAs)
-    if ((dbg >> 8) && (blockIdx.x & 1)) {
-        const long long t0 = clock64();
-        const long long wait = (long long)(dbg >> 8) * 256 * 2;      // ~2 cycles per ns
-        while (clock64() - t0 < wait) __nanosleep(64);
-    }
-
-    for (int tile = wglobal; tile < n_tiles; tile += nwarps) {
-        const int64_t row0 = (int64_t)tile * TW;
-        int ids[kBwdMaxL];
-#pragma unroll
-        for (int l = 0; l < kBwdMaxL; ++l) ids[l] = ids_n[l];
-        const float gl = gl_n;
-        load_ids(tile + nwarps);
-        const float g2 = 2.f * gl, b2 = g2 * p.beta;
-        float G[D];
-#pragma unroll
-        for (int j = 0; j < D; ++j) G[j] = 0.f;
-#pragma unroll 1
-        for (int l = p.L - 1; l >= 0; --l) {
-            const int id = pick(ids, l);
-            // ---- fill: residual rows, gradient rows, codeword rows (coalesced: 8 lanes per row) -----------------
-            {
-                const float* src_r = p.res + ((int64_t)l * p.B + row0 + sub) * D + chunk * 4;
-                const float* src_g = has_gemb ? p.g_emb + ((int64_t)l * p.B + row0 + sub) * D + chunk * 4 : nullptr;
-                const float* cbl = p.cb + (int64_t)l * p.K * D + chunk * 4;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int k = __shfl_sync(0xffffffffu, id, 4 * i + sub);
-                    const uint32_t o = co_off(i);
-                    if (dbg & 8) continue;
-                    if (row0 + sub + 4 * i < p.B) {
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tR_u32 + o), "l"(src_r + i * 4 * D) : "memory");
-                        if (has_gemb)
-                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tR_u32 + TILE_BYTES + o),
-                                         "l"(src_g + i * 4 * D) : "memory");
-                    }
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tR_u32 + 2 * TILE_BYTES + o),
-                                 "l"(cbl + (int64_t)k * D) : "memory");
-                }
-                asm volatile("cp.async.commit_group;" ::: "memory");
-                asm volatile("cp.async.wait_group 0;" ::: "memory");
-                __syncwarp();
-            }
-            // ---- pass 1: the five dot products of this lane's row --------------------------------------------------
-            float cg, cr, ce;
-            if (dbg & 4) continue;
-            if (MODE == RQ_MODE_ROTATION_TRICK) {
-                float rr = 0.f, ee = 0.f, re = 0.f, gr = 0.f, ge = 0.f;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    const uint32_t o = sw_off(lane, c);
-                    const float4 r4 = *reinterpret_cast<const float4*>(tR + o);
-                    const float4 e4 = *reinterpret_cast<const float4*>(tE + o);
-                    float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (has_gemb) g4 = *reinterpret_cast<const float4*>(tG + o);
-                    const float rv[4] = {r4.x, r4.y, r4.z, r4.w}, ev[4] = {e4.x, e4.y, e4.z, e4.w};
-                    const float gv[4] = {g4.x - G[4 * c], g4.y - G[4 * c + 1], g4.z - G[4 * c + 2], g4.w - G[4 * c + 3]};
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        rr = fmaf(rv[j], rv[j], rr); ee = fmaf(ev[j], ev[j], ee); re = fmaf(rv[j], ev[j], re);
-                        gr = fmaf(gv[j], rv[j], gr); ge = fmaf(gv[j], ev[j], ge);
-                    }
-                }
-                const float nx = fast_sqrt(rr), ne = fast_sqrt(ee);
-                const float iu = fast_rcp(nx + 1e-8f), iq = fast_rcp(ne + 1e-8f);
-                const float lam = ne * fast_rcp(nx + 1e-6f);
-                float ns = fmaf(iu * iu, rr, fmaf(2.f * iu * iq, re, iq * iq * ee));
-                if (ns < 0.0625f) {
-                    ns = 0.f;
-#pragma unroll
-                    for (int c = 0; c < 8; ++c) {
-                        const uint32_t o = sw_off(lane, c);
-                        const float4 r4 = *reinterpret_cast<const float4*>(tR + o);
-                        const float4 e4 = *reinterpret_cast<const float4*>(tE + o);
-                        float w;
-                        w = fmaf(r4.x, iu, e4.x * iq); ns = fmaf(w, w, ns);
-                        w = fmaf(r4.y, iu, e4.y * iq); ns = fmaf(w, w, ns);
-                        w = fmaf(r4.z, iu, e4.z * iq); ns = fmaf(w, w, ns);
-                        w = fmaf(r4.w, iu, e4.w * iq); ns = fmaf(w, w, ns);
-                    }
-                }
-                const float iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f));
-                const float gw = lam * iw * fmaf(iu, gr, iq * ge);
-                const float gq = lam * iq * ge;
-                cg = lam;
-                cr = 2.f * iu * (gq - gw * iw) + b2;
-                ce = -2.f * gw * iw * iq - b2;
-            } else if (MODE == RQ_MODE_STE) {
-                cg = 1.f; cr = b2; ce = -b2;
-            } else {
-                cg = 0.f; cr = b2; ce = -b2;
-            }
-            // ---- pass 2: this row's codebook-gradient contribution (staged over its gradient row) and G update ----
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const uint32_t o = sw_off(lane, c);
-                const float4 r4 = *reinterpret_cast<const float4*>(tR + o);
-                const float4 e4 = *reinterpret_cast<const float4*>(tE + o);
-                float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (has_gemb) g4 = *reinterpret_cast<const float4*>(tG + o);
-                const float rv[4] = {r4.x, r4.y, r4.z, r4.w}, ev[4] = {e4.x, e4.y, e4.z, e4.w};
-                const float gv[4] = {g4.x - G[4 * c], g4.y - G[4 * c + 1], g4.z - G[4 * c + 2], g4.w - G[4 * c + 3]};
-                float v[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    v[j] = g2 * (ev[j] - rv[j]);
-                    if (MODE == RQ_MODE_EVAL) v[j] += gv[j];
-                    G[4 * c + j] += fmaf(cg, gv[j], fmaf(cr, rv[j], ce * ev[j]));
-                }
-                *reinterpret_cast<float4*>(tG + o) = make_float4(v[0], v[1], v[2], v[3]);
-            }
-            __syncwarp();
-            {
-                float* gbase = p.g_cb + (int64_t)l * p.K * D + chunk * 4;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int k = __shfl_sync(0xffffffffu, id, 4 * i + sub);
-                    const float4 v = *reinterpret_cast<const float4*>(tG + co_off(i));
-                    if (row0 + sub + 4 * i < p.B && !(dbg & 1)) red_add_v4(gbase + (int64_t)k * D, v.x, v.y, v.z, v.w);
-                }
-            }
-            if (l == 0 && !(dbg & 2)) {
-                // g_x: staged over the residual rows and written out coalesced
-#pragma unroll
-                for (int c = 0; c < 8; ++c)
-                    *reinterpret_cast<float4*>(tR + sw_off(lane, c)) = make_float4(G[4 * c], G[4 * c + 1], G[4 * c + 2], G[4 * c + 3]);
-                __syncwarp();
-                float* dst = p.g_x + (row0 + sub) * D + chunk * 4;
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const float4 v = *reinterpret_cast<const float4*>(tR + co_off(i));
-                    if (row0 + sub + 4 * i < p.B) *reinterpret_cast<float4*>(dst + i * 4 * D) = v;
-                }
-            }
-            __syncwarp();                                    // staging reads done before the tile is refilled
-        }
-    }
-}
-
-static int launch_bwd_row2(const BwdParams& p, cudaStream_t st, bool* served) {
-    using namespace bwdrow2;
-    *served = false;
-    if (p.L > kBwdMaxL || getenv("RQ_BWD_NO_ROW2")) return 0;
-    if (p.g_res) return 0;                                    // residual-output gradients: ring-buffered kernel
-    if ((((uintptr_t)p.res | (uintptr_t)p.g_emb | (uintptr_t)p.cb | (uintptr_t)p.g_x | (uintptr_t)p.g_cb) & 15) != 0) return 0;
-    const size_t smem = (size_t)WARPS * WARP_BYTES;            // 96 KB: two CTAs (16 warps) per SM
-    const int n_tiles = (int)((p.B + TW - 1) / TW);
-    const int ctas_needed = (n_tiles + WARPS - 1) / WARPS;
-    const int grid = ctas_needed < 2 * sm_count() ? ctas_needed : 2 * sm_count();
-    const int dbg = getenv("RQ_BWD_DBG") ? atoi(getenv("RQ_BWD_DBG")) : 0;       // timing experiments only
-    auto launch = [&](auto kern) -> int {
-        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<grid, THREADS, smem, st>>>(p, n_tiles, dbg);
-        return 0;
-    };
-    int rc;
-    if (p.mode == RQ_MODE_ROTATION_TRICK) rc = launch(rq_bwd_row2_kernel<RQ_MODE_ROTATION_TRICK>);
-    else if (p.mode == RQ_MODE_STE) rc = launch(rq_bwd_row2_kernel<RQ_MODE_STE>);
-    else rc = launch(rq_bwd_row2_kernel<RQ_MODE_EVAL>);
-    if (rc) return rc;
-    RQ_LAUNCHED();
-    *served = true;
-    return 0;
-}
-
 // ---- D = 32, two lanes per row, double-buffered ---------------------------------------------------------------
 // Per warp the work is one serial chain (load -> dot products -> update -> scatter, level after level), so the
 // launch takes as long as the slowest warp's chain (tools/time_bwd.py: the phases add up instead of overlapping).
@@ -851,6 +656,8 @@ __global__ void __launch_bounds__(bwdrow3::THREADS, 2) rq_bwd_row3_kernel(BwdPar
     using namespace bwdrow3;
     using bwdrow::sw_off;
     extern __shared__ __align__(1024) uint8_t smem[];
+    pdl_launch_dependents();
+    pdl_wait();                     // launched with PDL: scheduled early, reads nothing before the forward has completed
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t* wbuf = smem + warp * WARP_BYTES;
     const uint32_t wbuf_u32 = (uint32_t)__cvta_generic_to_shared(wbuf);
@@ -1021,7 +828,7 @@ __global__ void __launch_bounds__(bwdrow3::THREADS, 2) rq_bwd_row3_kernel(BwdPar
 static int launch_bwd_row3(const BwdParams& p, cudaStream_t st, bool* served) {
     using namespace bwdrow3;
     *served = false;
-    if (p.L > kBwdMaxL || getenv("RQ_BWD_NO_ROW3")) return 0;
+    if (p.L > kBwdMaxL || bwd_knob("RQ_BWD_NO_ROW3")) return 0;
     if (p.g_res) return 0;                                    // residual-output gradients: ring-buffered kernel
     if ((((uintptr_t)p.res | (uintptr_t)p.g_emb | (uintptr_t)p.cb | (uintptr_t)p.g_x | (uintptr_t)p.g_cb) & 15) != 0) return 0;
     const size_t smem = (size_t)WARPS * WARP_BYTES;            // 96 KB: two CTAs (16 warps) per SM
@@ -1029,8 +836,8 @@ static int launch_bwd_row3(const BwdParams& p, cudaStream_t st, bool* served) {
     const int ctas_needed = (n_tiles + WARPS - 1) / WARPS;
     const int grid = ctas_needed < 2 * sm_count() ? ctas_needed : 2 * sm_count();
     auto launch = [&](auto kern) -> int {
-        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<grid, THREADS, smem, st>>>(p, n_tiles);
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)kern, (int)smem));
+        RQ_CUDA(launch_pdl(kern, dim3(grid), dim3(THREADS), smem, st, p, n_tiles));
         return 0;
     };
     int rc;
@@ -1046,15 +853,15 @@ static int launch_bwd_row3(const BwdParams& p, cudaStream_t st, bool* served) {
 static int launch_bwd_row(const BwdParams& p, cudaStream_t st, bool* served) {
     using namespace bwdrow;
     *served = false;
-    if (p.L > kBwdMaxL || getenv("RQ_BWD_NO_ROW")) return 0;
+    if (p.L > kBwdMaxL || bwd_knob("RQ_BWD_NO_ROW")) return 0;
     if ((((uintptr_t)p.res | (uintptr_t)p.g_emb | (uintptr_t)p.cb | (uintptr_t)p.g_x | (uintptr_t)p.g_cb) & 15) != 0) return 0;
     const size_t smem = (size_t)WARPS * STAGES * STAGE_BYTES;  // 96 KB: two CTAs per SM
     const int n_tiles = (int)((p.B + TW - 1) / TW);
     const int ctas_needed = (n_tiles + WARPS - 1) / WARPS;
     const int grid = ctas_needed < 2 * sm_count() ? ctas_needed : 2 * sm_count();
-    const int dbg = getenv("RQ_BWD_DBG") ? atoi(getenv("RQ_BWD_DBG")) : 0;
+    const int dbg = bwd_dbg();
     auto launch = [&](auto kern) -> int {
-        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)kern, (int)smem));
         kern<<<grid, THREADS, smem, st>>>(p, n_tiles, dbg);
         return 0;
     };
@@ -1072,7 +879,7 @@ template <int D>
 static int launch_bwd_tma(const BwdParams& p, cudaStream_t st, bool* served) {
     using namespace bwdtma;
     *served = false;
-    if (p.L > kBwdMaxL || getenv("RQ_BWD_NO_TMA")) return 0;
+    if (p.L > kBwdMaxL || bwd_knob("RQ_BWD_NO_TMA")) return 0;
     if ((((uintptr_t)p.res | (uintptr_t)p.g_emb | (uintptr_t)p.cb | (uintptr_t)p.g_x | (uintptr_t)p.g_cb) & 15) != 0) return 0;
     constexpr int RPW = 32 / (D / 4);
     constexpr int ROWS_PER_PASS = (THREADS / 32) * RPW;
@@ -1096,13 +903,13 @@ static int launch_bwd_tma(const BwdParams& p, cudaStream_t st, bool* served) {
     }
     if (!T) return 0;
     cfg.T = T;
-    cfg.dbg = getenv("RQ_BWD_DBG") ? atoi(getenv("RQ_BWD_DBG")) : 0;
+    cfg.dbg = bwd_dbg();
     cfg.stage_bytes = p.L * 2 * T * D * 4;
     cfg.n_tiles = (int)((p.B + T - 1) / T);
     const size_t smem = (size_t)STAGES * (cfg.stage_bytes + p.L * T * 8 + T * 4) + cfg.cb_bytes + 64;
     const int grid = cfg.n_tiles < sm_count() ? cfg.n_tiles : sm_count();
     auto launch = [&](auto kern) -> int {
-        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)kern, 227 * 1024));
         kern<<<grid, THREADS, smem, st>>>(p, cfg);
         return 0;
     };
@@ -1131,13 +938,14 @@ static int launch_bwd(const BwdParams& p, cudaStream_t st) {
 }
 
 int quantize_backward_simt(const BwdParams& p, int D, cudaStream_t st) {
-    RQ_CUDA(cudaMemsetAsync(p.g_cb, 0, (size_t)p.L * p.K * D * sizeof(float), st));
+    // accumulate: g_cb already holds what the codebook gradient is added to (zeros the caller wrote earlier, or a
+    // running gradient) — no memset between the forward and this kernel, so the two stay adjacent for PDL
+    if (!p.accumulate) RQ_CUDA(cudaMemsetAsync(p.g_cb, 0, (size_t)p.L * p.K * D * sizeof(float), st));
     if (p.B == 0) return 0;
     {
         bool served = false;
         int rc = 0;
         if (D == 32) rc = launch_bwd_row3(p, st, &served);
-        if (!rc && !served && D == 32) rc = launch_bwd_row2(p, st, &served);
         if (!rc && !served && D == 32) rc = launch_bwd_row(p, st, &served);
         if (!rc && !served && D == 32) rc = launch_bwd_tma<32>(p, st, &served);
         else if (D == 64) rc = launch_bwd_tma<64>(p, st, &served);

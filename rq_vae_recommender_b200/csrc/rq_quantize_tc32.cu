@@ -23,6 +23,8 @@
 // place over the fp32 rows a TMA bulk copy dropped into the B-tile space, plus a [hi, mid, lo] split of ||c||^2 that a
 // K = 16 MMA against a ones tile adds to the accumulator); the later levels are converted by warpgroups 2 and 3 while
 // they wait for their first turn on the accumulators, and published through per-level mbarriers.
+#include <stdlib.h>
+
 #include "rq_rowmath.cuh"
 #include "rq_tc_tiles.cuh"
 
@@ -69,7 +71,9 @@ __host__ __device__ inline SmemLayout smem_layout(int L) {
     do {                                                                                        \
         if (P.dbg_tl && threadIdx.x == 0) P.dbg_tl[2048 + 4 * blockIdx.x + (slot_)] = (long long)(val_); \
     } while (0)
+#define RQ_WHATIF(bit) (P.dbg_flags & (bit))
 #else
+#define RQ_WHATIF(bit) false
 #define RQ_TL(mark) do {} while (0)
 #define RQ_TL_DEP(mark, val) do {} while (0)
 #define RQ_CTA_STAMP(slot_, val_) do {} while (0)
@@ -95,6 +99,7 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
     int* cmax_bits = reinterpret_cast<int*>(smem + S.misc + 80);               // [MAX_L] max ||c||^2 per level
     uint64_t* mbar_load = reinterpret_cast<uint64_t*>(smem + S.misc + 96);     // [MAX_L] a level's bulk copy landed
     uint64_t* mbar_bready = reinterpret_cast<uint64_t*>(smem + S.misc + 128);  // [MAX_L] a level's operand tiles converted
+    uint64_t* mbar_tmem = reinterpret_cast<uint64_t*>(smem + S.misc + 160);    // TMEM allocated, address published
 
     // the warp index is made provably warp-uniform (shuffle from lane 0): everything derived from it — warpgroup, slot,
     // tile numbers, row offsets, output base pointers — then lives in uniform registers instead of the 128 per thread
@@ -127,10 +132,14 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
             ptx::cp_async16(sRw + sw128_off(wrow0 + 4 * j + (lane >> 3), lane & 7), src + j * 4 * D, 16u);
         ptx::cp_async_commit();
     };
-    if (n_mine > 0) prefetch_x(tile_of(0));
-
-    // ---- barriers; codebooks: one TMA bulk copy per level, fp32 rows straight into that level's B-tile space --------
-    if (tid == 0) {
+    // ---- prologue.  Warpgroups 0 and 1 own the first turns on the two accumulators: their x tiles are requested
+    // first thing (HBM latency + a 64 KB-per-SM burst are the long pole of the first MMA), while warpgroups 2 and 3 —
+    // which cannot start before the first scans are done — set the CTA up: barriers, codebook bulk copies (one per level,
+    // fp32 rows straight into that level's B-tile space), ones tile, TMEM.  pdl_wait(): with programmatic dependent
+    // launch this CTA is scheduled as soon as the SM's previous CTA retires; the preceding kernel's writes (x,
+    // codebooks) are visible once it returns.  Nobody waits for the TMEM allocation before it needs the address. ---------
+    pdl_launch_dependents();
+    if (tid == 2 * 128) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) ptx::mbar_init(&mbar_full[i], 1);
         ptx::mbar_init(&mbar_free[0], 4);
@@ -140,26 +149,37 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
             ptx::mbar_init(&mbar_load[i], 1);
             ptx::mbar_init(&mbar_bready[i], i == 0 ? 16 : 8);       // warps that convert the level
         }
+        ptx::mbar_init(mbar_tmem, 1);
         ptx::fence_mbar_init();
-        const uint32_t level_bytes = (uint32_t)p.K * D * 4;
-        for (int l = 0; l < p.L; ++l) {
-            ptx::mbar_arrive_expect_tx(&mbar_load[l], level_bytes);
-            ptx::bulk_g2s(sB + l * B_TILE_BYTES, p.cb + (int64_t)l * p.K * D, level_bytes, &mbar_load[l]);
+    }
+    pdl_wait();
+    if (!is_hi) {
+        if (n_mine > 0) prefetch_x(tile_of(0));
+    } else {
+        if (tid == 2 * 128) {
+            const uint32_t level_bytes = (uint32_t)p.K * D * 4;
+            for (int l = 0; l < p.L; ++l) {
+                ptx::mbar_arrive_expect_tx(&mbar_load[l], level_bytes);
+                ptx::bulk_g2s(sB + l * B_TILE_BYTES, p.cb + (int64_t)l * p.K * D, level_bytes, &mbar_load[l]);
+            }
         }
+        if (wtid < MAX_L && wg == 2) cmax_bits[wtid] = 0;
+        // ones tile: k = 0,1,2 -> 1.0 (multiplies hi/mid/lo of ||c||^2), rest 0
+        {
+            const int rr = (tid - 256) >> 1, c = tid & 1;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (c == 0) { v.x = 0x3F803F80u; v.y = 0x00003F80u; }
+            *reinterpret_cast<uint4*>(sOnes + nosw_off(rr, c)) = v;
+        }
+        ptx::fence_proxy_async_smem();
     }
-    if (tid < MAX_L) cmax_bits[tid] = 0;
-    if (warp == 1) ptx::tmem_alloc(tmem_base_s, 512);
-    // ones tile: k = 0,1,2 -> 1.0 (multiplies hi/mid/lo of ||c||^2), rest 0
-    for (int i = tid; i < TILE_M * 2; i += THREADS) {
-        const int rr = i >> 1, c = i & 1;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (c == 0) { v.x = 0x3F803F80u; v.y = 0x00003F80u; }
-        *reinterpret_cast<uint4*>(sOnes + nosw_off(rr, c)) = v;
+    __syncthreads();                                   // barrier inits, cmax zeros, ones tile
+    if (warp == 9) {
+        ptx::tmem_alloc(tmem_base_s, 512);
+        ptx::tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(mbar_tmem);
     }
-    ptx::fence_proxy_async_smem();
-    ptx::tc_fence_before_sync();
-    __syncthreads();                                   // barrier inits, cmax zeros, ones tile, TMEM address
-    ptx::tc_fence_after_sync();
     RQ_TL(1);
 
     // ---- operand conversion: level 0 by everybody, the later levels by warpgroups 2 and 3 (they cannot start before
@@ -181,11 +201,19 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
     // level 1 by the odd warpgroups (slot 1), level 2 by warpgroups 2 and 3: warpgroup 1 starts about half an
     // accumulator hold time after warpgroup 0, so the two slots stay out of phase (one scans while the other's MMAs
     // run) instead of competing for the tensor pipe and for the ALU pipe at the same moments
+#ifndef RQ_V_NOSHIFT
     if (p.L > 1 && (wg & 1)) convert_level(1, (wg >> 1) * 128 + wtid, 256, 2);   // 4 per thread
     if (p.L > 2 && is_hi) convert_level(2, tid - 256, 256, 2);
+#else
+    if (p.L > 1 && is_hi) convert_level(1, tid - 256, 256, 2);
+    if (p.L > 2 && is_hi) convert_level(2, tid - 256, 256, 2);
+#endif
+    if (is_hi && n_mine > 0) prefetch_x(tile_of(0));
     RQ_TL(2);
 
-    const uint32_t tmem_base = *tmem_base_s;
+    if (!ptx::mbar_wait(mbar_tmem, 0)) timed_out = true;
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_base_s);
     const uint32_t tmem_acc = tmem_base + (uint32_t)(slot * KC);                     // column offset
     const uint32_t tmem_row = tmem_acc + ((uint32_t)((warp & 3) * 32) << 16);        // this warp's lanes
     const uint32_t idesc = ptx::make_idesc_bf16_f32(TILE_M, KC);
@@ -193,12 +221,15 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
     // ---- row-math layout: lane = (row 8 i + rsub of the warp's 32 rows, floats 8 q .. 8 q + 7), i = 0..3 -------------
     const int q = lane & 3, rsub = lane >> 2;
     // residual tile: 16-byte chunks 2q, 2q+1 of row wrow0 + 8 i + rsub (row & 7 == rsub); + 1024 i
-    uint8_t* const pR0 = sRw + (wrow0 * 128 + rsub * 128 + (((2 * q) ^ rsub) << 4));
-    uint8_t* const pR1 = reinterpret_cast<uint8_t*>(reinterpret_cast<uintptr_t>(pR0) ^ 16);   // chunk index ^ 1
+    const uint32_t offR0 = (uint32_t)(wrow0 * 128 + rsub * 128 + (((2 * q) ^ rsub) << 4));
+    uint8_t* const pR0 = sRw + offR0;
+    uint8_t* const pR1 = sRw + (offR0 ^ 16u);          // chunk index ^ 1
     // A tile: hi chunk q, lo chunk 4 + q of the same row (chunk index ^ 4 = byte offset ^ 64).  The two rows of a
     // store phase land in the same half of the chunk columns (2-way bank conflict on these 8 stores per level); the
     // alternative, swapping hi / lo by row parity, costs 8 selects per row on the ALU pipe, the loaded one here.
-    uint8_t* const pA_hi = sAw + (wrow0 * 128 + rsub * 128 + ((q ^ rsub) << 4));
+    const uint32_t offA = (uint32_t)(wrow0 * 128 + rsub * 128 + ((q ^ rsub) << 4));
+    uint8_t* const pA_hi = sAw + offA;
+    uint8_t* const pA_lo = sAw + (offA ^ 64u);         // chunk index ^ 4
     const int lane_gofs = (wrow0 + rsub) * D + q * 8;      // float offset of my first 8 floats inside a [128, D] tile
 
     // Transposing reduction over the 4 lanes of a row group: v[i] is my chunk partial of row 8 i + rsub; the result is
@@ -231,8 +262,7 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
 #pragma unroll
         for (int j = 0; j < 4; ++j) ptx::split_pair_cvt(r[2 * j], r[2 * j + 1], h[j], lw[j]);
         *reinterpret_cast<uint4*>(pA_hi + 1024 * i) = make_uint4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(reinterpret_cast<uintptr_t>(pA_hi) ^ 64) + 1024 * i) =
-            make_uint4(lw[0], lw[1], lw[2], lw[3]);
+        *reinterpret_cast<uint4*>(pA_lo + 1024 * i) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
     };
     auto store_id = [&](int l, int64_t row, int bi) {
         int64_t* dst = p.ids + (int64_t)l * p.B + row;
@@ -299,6 +329,7 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
                 const int bk[6] = {0, 32, 0, 32, 64, 96};
 #pragma unroll
                 for (int i = 0; i < 6; ++i) {
+                    if (RQ_WHATIF(1) && i > 0) break;
                     const uint64_t ad = ptx::make_smem_desc(a0 + ak[i], 16, 1024, ptx::kLayoutSw128);
                     const uint64_t bd = ptx::make_smem_desc(b0 + bk[i], 16, 1024, ptx::kLayoutSw128);
                     ptx::umma_bf16(tmem_acc, ad, bd, idesc, i > 0);
@@ -311,6 +342,8 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
             __syncwarp();
             RQ_TL(4 + 8 * l);
             const float xs = __shfl_sync(0xffffffffu, xxq, owner_of_my_scan_row);     // ||r||^2 of my scan row
+            RotX X = {};
+            if (MODE == RQ_MODE_ROTATION_TRICK) X = rot_x(xxq);      // residual-only scalars, in the shadow of the MMAs
             if (!ptx::mbar_wait(&mbar_full[wg], use & 1)) timed_out = true;
             ptx::tc_fence_after_sync();
             RQ_TL(6 + 8 * l);
@@ -333,6 +366,10 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
             int bi;
             {
                 float accA[16], accB[16];
+                if (RQ_WHATIF(2)) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) { accA[i] = (float)((lane * 7 + i * 3 + l) & 15) + 1.f; accB[i] = (float)((lane * 5 + i) & 15) + 1.f; }
+                } else
                 scan_accumulator_row(tmem_row, accA, accB);
                 // the accumulator is read out: hand it back (one arrival per warp)
                 ptx::tc_fence_before_sync();            // orders this thread's tcgen05.ld before the arrival
@@ -408,10 +445,17 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
 
             // ---- row math, two rows per lane at a time: gather, estimator, loss, outputs, next residual, next A rows ----
             const float* cbl = p.cb + (int64_t)l * p.K * D + q * 8;
+            // my 8 floats of row 8 i + rsub in this level's embedding / the next level's residual output: + 1024 i bytes
+            float* const emb_l = p.emb ? p.emb + (int64_t)l * p.B * D + tile_gofs : nullptr;
+            float* const res_n = p.res ? p.res + (int64_t)(l + 1) * p.B * D + tile_gofs : nullptr;
             float e[4][8], r[4][8];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {               // all four gathers in flight (L2 latency)
                 const int k = __shfl_sync(0xffffffffu, bi, 8 * i + rsub);
+                if (RQ_WHATIF(4)) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) e[i][j] = (float)(k + j) * 0.01f;
+                } else
                 ptx::ld_global_v8(cbl + (int64_t)k * D, e[i]);
             }
 #pragma unroll
@@ -434,19 +478,19 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
                     pr[i] = chunk_dot<8>(r[i], e[i]);
                 }
                 const float e2 = quad_reduce_t(pe), re = quad_reduce_t(pr);
-                float nx, ne, iu, iq;
-                float ns = rot_prepare(xxq, e2, re, nx, ne, iu, iq);
+                float ne, iq;
+                float ns = rot_prepare(X, xxq, e2, re, ne, iq);
                 if (__any_sync(0xffffffffu, ns < kRotCancel)) {        // rare: |u + q| small, recompute it directly
                     float pn[4];
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
-                        pn[i] = chunk_sq_axpby<8>(r[i], e[i], __shfl_sync(0xffffffffu, iu, quad0 + i),
+                        pn[i] = chunk_sq_axpby<8>(r[i], e[i], __shfl_sync(0xffffffffu, X.iu, quad0 + i),
                                                   __shfl_sync(0xffffffffu, iq, quad0 + i));
                     const float nd = quad_reduce_t(pn);
                     if (ns < kRotCancel) ns = nd;
                 }
                 float ca, ce;
-                rot_finish(xxq, re, nx, ne, iu, iq, ns, ca, ce);
+                rot_finish(X, xxq, re, ne, iq, ns, ca, ce);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const float cai = __shfl_sync(0xffffffffu, ca, quad0 + i), cei = __shfl_sync(0xffffffffu, ce, quad0 + i);
@@ -473,7 +517,7 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
                 float px[4];
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    if (p.emb) ptx::st_global_v8(p.emb + (int64_t)l * p.B * D + tile_gofs + i * 8 * D, e[i]);
+                    if (emb_l && !RQ_WHATIF(8)) ptx::st_global_v8(emb_l + i * 8 * D, e[i]);
                     if (!last) {
 #pragma unroll
                         for (int j = 0; j < 4; ++j)                            // rqvae.py:129
@@ -482,7 +526,7 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
                         store_row8(i, r[i]);
                         write_a_row8(i, r[i]);
                         px[i] = chunk_dot<8>(r[i], r[i]);
-                        if (p.res) ptx::st_global_v8(p.res + (int64_t)(l + 1) * p.B * D + tile_gofs + i * 8 * D, r[i]);
+                        if (res_n && !RQ_WHATIF(8)) ptx::st_global_v8(res_n + i * 8 * D, r[i]);
                     }
                 }
                 if (!last) xxq = quad_reduce_t(px);
@@ -506,7 +550,7 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
     if (timed_out && P.err) atomicExch(P.err, 1);
     ptx::tc_fence_before_sync();
     __syncthreads();
-    if (warp == 1) ptx::tmem_dealloc(tmem_base, 512);
+    if (warp == 9) ptx::tmem_dealloc(tmem_base, 512);
     RQ_CTA_STAMP(2, ptx::globaltimer());
 }
 
@@ -542,6 +586,7 @@ int quantize_forward_tc32_fused(const FwdParams& p, cudaStream_t st) {
         P.dbg_acc = g_dbg_acc32;
 #ifdef RQ_EXPERIMENTS
         P.dbg_tl = g_dbg_tl32;
+        P.dbg_flags = getenv("RQ_TC_WHATIF") ? atoi(getenv("RQ_TC_WHATIF")) : 0;    // experiments build only
 #endif
         P.n_tiles = (int)n_tiles;
         const tc32::SmemLayout S = tc32::smem_layout(p.L);
@@ -550,15 +595,15 @@ int quantize_forward_tc32_fused(const FwdParams& p, cudaStream_t st) {
         switch (p.mode) {
             case RQ_MODE_ROTATION_TRICK:
                 RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_fwd_tc32_kernel<RQ_MODE_ROTATION_TRICK>, tc::kMaxSmem));
-                rq_fwd_tc32_kernel<RQ_MODE_ROTATION_TRICK><<<grid, tc32::THREADS, smem, st>>>(P);
+                RQ_CUDA(launch_pdl(rq_fwd_tc32_kernel<RQ_MODE_ROTATION_TRICK>, dim3(grid), dim3(tc32::THREADS), smem, st, P));
                 break;
             case RQ_MODE_STE:
                 RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_fwd_tc32_kernel<RQ_MODE_STE>, tc::kMaxSmem));
-                rq_fwd_tc32_kernel<RQ_MODE_STE><<<grid, tc32::THREADS, smem, st>>>(P);
+                RQ_CUDA(launch_pdl(rq_fwd_tc32_kernel<RQ_MODE_STE>, dim3(grid), dim3(tc32::THREADS), smem, st, P));
                 break;
             default:
                 RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_fwd_tc32_kernel<RQ_MODE_EVAL>, tc::kMaxSmem));
-                rq_fwd_tc32_kernel<RQ_MODE_EVAL><<<grid, tc32::THREADS, smem, st>>>(P);
+                RQ_CUDA(launch_pdl(rq_fwd_tc32_kernel<RQ_MODE_EVAL>, dim3(grid), dim3(tc32::THREADS), smem, st, P));
                 break;
         }
         RQ_LAUNCHED();

@@ -75,22 +75,32 @@ __device__ __forceinline__ float dot_self(const float (&r)[D]) {
 // Scalars of the rotation trick (see level_epilogue) from the dot products xx = r.r, ee = e.e, re = r.e.
 // rot_prepare returns |u+q|^2 by the expanded form; when it is < 1/16 the caller recomputes it directly
 // (sum (iu r + iq e)^2, canonical order) before rot_finish.
-__device__ __forceinline__ float rot_prepare(float xx, float ee, float re, float& nx, float& ne, float& iu, float& iq) {
-    nx = fast_sqrt(xx);
+// The part of the scalars that depends on the residual only (known before the codeword is): |r|, 1/(|r|+1e-8),
+// 1/(|r|+1e-6).  The fused kernel computes it while the level's MMAs are in flight.
+struct RotX {
+    float nx, iu, il;
+};
+__device__ __forceinline__ RotX rot_x(float xx) {
+    RotX X;
+    X.nx = fast_sqrt(xx);
+    X.iu = fast_rcp(X.nx + 1e-8f);
+    X.il = fast_rcp(X.nx + 1e-6f);
+    return X;
+}
+__device__ __forceinline__ float rot_prepare(const RotX& X, float xx, float ee, float re, float& ne, float& iq) {
     ne = fast_sqrt(ee);
-    iu = fast_rcp(nx + 1e-8f);
     iq = fast_rcp(ne + 1e-8f);
-    return fmaf(iu * iu, xx, fmaf(2.f * iu * iq, re, iq * iq * ee));
+    return fmaf(X.iu * X.iu, xx, fmaf(2.f * X.iu * iq, re, iq * iq * ee));
 }
 constexpr float kRotCancel = 0.0625f;                         // |u+q| < 1/4: recompute without cancellation
-__device__ __forceinline__ void rot_finish(float xx, float re, float nx, float ne, float iu, float iq, float ns,
-                                           float& ca, float& ce) {
+__device__ __forceinline__ void rot_finish(const RotX& X, float xx, float re, float ne, float iq, float ns, float& ca,
+                                           float& ce) {
     const float iw = fast_rcp(fmaxf(fast_sqrt(ns), 1e-6f));   // F.normalize(eps=1e-6)
-    const float rs = fmaf(iu, xx, iq * re);                   // r.(u+q)
+    const float rs = fmaf(X.iu, xx, iq * re);                 // r.(u+q)
     const float rsw = rs * iw * iw;                           // (r.w) * iw
-    const float lam = ne * fast_rcp(nx + 1e-6f);
-    ca = lam * (1.f - 2.f * rsw * iu);
-    ce = 2.f * lam * iq * (iu * xx - rsw);
+    const float lam = ne * X.il;
+    ca = lam * (1.f - 2.f * rsw * X.iu);
+    ce = 2.f * lam * iq * (X.iu * xx - rsw);
 }
 
 // Canonical ||c||^2 of a codeword, bit-identical in both kernel families: sequential fmaf over
@@ -148,16 +158,17 @@ __device__ __forceinline__ float level_epilogue(int mode, float beta, const floa
             pre[q] = chunk_dot<W>(&r[q * W], &e[q * W]);
         }
         const float ee = tree_sum(pe), re = tree_sum(pre);
-        float nx, ne, iu, iq;
-        float ns = rot_prepare(xx, ee, re, nx, ne, iu, iq);
+        const RotX X = rot_x(xx);
+        float ne, iq;
+        float ns = rot_prepare(X, xx, ee, re, ne, iq);
         if (ns < kRotCancel) {
             float pn[NP];
 #pragma unroll
-            for (int q = 0; q < NP; ++q) pn[q] = chunk_sq_axpby<W>(&r[q * W], &e[q * W], iu, iq);
+            for (int q = 0; q < NP; ++q) pn[q] = chunk_sq_axpby<W>(&r[q * W], &e[q * W], X.iu, iq);
             ns = tree_sum(pn);
         }
         float ca, ce;
-        rot_finish(xx, re, nx, ne, iu, iq, ns, ca, ce);
+        rot_finish(X, xx, re, ne, iq, ns, ca, ce);
         const f32x2 ca2 = pack2(ca, ca), ce2 = pack2(ce, ce);
 #pragma unroll
         for (int j = 0; j < D / 2; ++j)

@@ -232,9 +232,10 @@ __device__ __forceinline__ void split_pair(float a, float b, uint32_t& hi, uint3
     asm("mov.b64 %0, {%1, %2};" : "=l"(ab) : "f"(a), "f"(b));
     asm("mov.b64 %0, {%1, %2};" : "=l"(hh) : "r"(ah), "r"(bh));
     asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(dd) : "l"(ab), "l"(hh));
-    uint32_t la, lb;
-    asm("mov.b64 {%0, %1}, %2;" : "=r"(la), "=r"(lb) : "l"(dd));
-    lo = pack_hi16(la, lb);
+    float la, lb;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(la), "=f"(lb) : "l"(dd));
+    // truncation (round toward zero) of the exact remainders, packed by the conversion unit as well
+    asm("cvt.rz.bf16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(lb), "f"(la));
 }
 
 // The same split with the rounding done by the conversion unit: hi = cvt.rn.bf16x2 (one F2FP per pair, already packed),

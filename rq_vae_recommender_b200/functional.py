@@ -55,9 +55,13 @@ def quantize_forward(x: torch.Tensor, codebooks: torch.Tensor, mode: int = MODE_
 
 def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, beta, temperature,
                       gumbel_uniform=None, seed: int = 0, offset: int = 0,
-                      g_codebooks_out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+                      g_codebooks_out: Optional[torch.Tensor] = None,
+                      accumulate: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
     """rq_quantize_backward: returns (g_x [B,D], g_codebooks [L,K,D]).  `g_codebooks_out` (contiguous fp32
-    [L,K,D]) receives the codebook gradient in place — e.g. a persistent all-reduce bucket."""
+    [L,K,D]) receives the codebook gradient in place — e.g. a persistent all-reduce bucket.  `accumulate=True` adds
+    to what `g_codebooks_out` holds instead of overwriting it (gradient accumulation; with a buffer zeroed BEFORE the
+    forward no memset sits between the forward and the backward kernel, so the two overlap through programmatic
+    dependent launch)."""
     residuals = _f32c(residuals, "residuals")
     codebooks = _f32c(codebooks, "codebooks")
     L.require_cuda(ids, "ids", torch.int64)
@@ -77,10 +81,12 @@ def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, bet
             g_cb = L.require_cuda(g_codebooks_out, "g_codebooks_out", torch.float32)
             if tuple(g_cb.shape) != (Lv, K, D) or not g_cb.is_contiguous():
                 raise L.RqEngineError(f"g_codebooks_out must be contiguous [L,K,D]={Lv, K, D}")
-        rc = L.lib().rq_quantize_backward(L.ptr(g_emb), L.ptr(g_res), L.ptr(g_loss), L.ptr(residuals), L.ptr(ids),
-                                          L.ptr(codebooks), B, D, K, Lv, int(mode), float(beta), float(temperature),
-                                          L.ptr(gumbel_uniform), int(seed), int(offset), L.ptr(g_x), L.ptr(g_cb),
-                                          L.stream_of(residuals))
+        if accumulate and g_codebooks_out is None:
+            raise L.RqEngineError("quantize_backward: accumulate=True needs g_codebooks_out")
+        rc = L.lib().rq_quantize_backward_ex(L.ptr(g_emb), L.ptr(g_res), L.ptr(g_loss), L.ptr(residuals), L.ptr(ids),
+                                             L.ptr(codebooks), B, D, K, Lv, int(mode), float(beta), float(temperature),
+                                             L.ptr(gumbel_uniform), int(seed), int(offset), L.ptr(g_x), L.ptr(g_cb),
+                                             1 if accumulate else 0, L.stream_of(residuals))
     L.check(rc, "rq_quantize_backward")
     return g_x, g_cb
 
@@ -91,6 +97,9 @@ class ResidualQuantizeFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, codebooks, mode, beta, temperature, distance, gumbel_uniform, seed, offset, impl):
+        # the codebook gradient is zeroed HERE, ahead of the forward kernel: nothing but the caller's own kernels then
+        # sits between the fused forward and the fused backward, whose launch PDL overlaps with its predecessor's tail
+        ctx.g_cb = torch.zeros_like(codebooks) if mode != MODE_GUMBEL_SOFTMAX else None
         emb, res, ids, loss = quantize_forward(x, codebooks, mode, beta, temperature, distance, gumbel_uniform,
                                                seed, offset, True, True, True, impl)
         ctx.save_for_backward(res, ids, codebooks, gumbel_uniform if gumbel_uniform is not None else x.new_empty(0))
@@ -105,8 +114,10 @@ class ResidualQuantizeFn(torch.autograd.Function):
     def backward(ctx, g_emb, g_res, _g_ids, g_loss):
         res, ids, codebooks, gu = ctx.saved_tensors
         mode, beta, temperature, has_gu, seed, offset = ctx.cfg
+        g_cb_buf, ctx.g_cb = ctx.g_cb, None
         g_x, g_cb = quantize_backward(g_emb, g_res, g_loss, res, ids, codebooks, mode, beta, temperature,
-                                      gu if has_gu else None, seed, offset)
+                                      gu if has_gu else None, seed, offset, g_codebooks_out=g_cb_buf,
+                                      accumulate=g_cb_buf is not None)
         return g_x, g_cb, None, None, None, None, None, None, None, None
 
 
