@@ -205,7 +205,7 @@ static int launch_gumbel_bwd(const BwdParams& p, float temperature, const float*
     const size_t smem = (size_t)kc * D * sizeof(float) + (size_t)((kc + 3) & ~3) * sizeof(float) +
                         (size_t)D * kGbThreads * sizeof(float);
     auto kern = rq_bwd_gumbel_kernel<D>;
-    RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RQ_CUDA(ensure_max_dynamic_smem((const void*)kern, (int)smem));
     const unsigned grid = (unsigned)((p.B + kGbThreads - 1) / kGbThreads);
     kern<<<grid, kGbThreads, smem, st>>>(P);
     RQ_LAUNCHED();

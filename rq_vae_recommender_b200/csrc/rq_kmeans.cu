@@ -67,7 +67,7 @@ static int launch_km(const KmeansParams& p0, cudaStream_t st) {
     p.KC = kc;
     size_t smem = (size_t)kc * D * sizeof(float);
     auto kern = rq_kmeans_assign_simt_kernel<D>;
-    RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RQ_CUDA(ensure_max_dynamic_smem((const void*)kern, (int)smem));
     dim3 grid((unsigned)((p.B + kKmThreads - 1) / kKmThreads));
     kern<<<grid, kKmThreads, smem, st>>>(p);
     RQ_LAUNCHED();
@@ -180,13 +180,8 @@ template <int D>
 static int launch_kmeans_accumulate(const KmeansParams& p, cudaStream_t st) {
     const size_t smem = (size_t)p.K * D * 4 + (size_t)p.K * 4;
     const int64_t n_chunks = p.B * (D / 4);
-    if (smem <= 100 * 1024 && !getenv("RQ_KMEANS_GLOBAL_RED")) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            RQ_CUDA(cudaFuncSetAttribute(rq_kmeans_accumulate_smem_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         100 * 1024));
-            attr_set = true;
-        }
+    if (smem <= 100 * 1024) {
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_kmeans_accumulate_smem_kernel<D>, 100 * 1024));
         int per_sm = (int)((220 * 1024) / (smem + 1024));
         if (per_sm > 4) per_sm = 4;
         int64_t blocks = (n_chunks + 512 * 4 - 1) / (512 * 4);

@@ -13,7 +13,10 @@
 //   barrier 2   same counters, (2E+2) * world: nobody still reads -> results are written (in place is allowed)
 //
 // E = number of earlier launches on this allocation, kept per CTA in device memory, so replaying a captured launch
-// needs no host-side state.  Waits are bounded: a rank that never arrives sets a flag instead of hanging the GPU.
+// needs no host-side state.  Waits are bounded (2^23 polls of a system-scope load, a few seconds — the maximum rank
+// skew the exchange tolerates): a CTA whose barrier times out does NOT publish a sum of possibly stale buffers, it
+// fills its part of the output with NaN and raises the per-device error flag (rq_debug_peer_timeout_flag; PeerAllReduce
+// .check() turns it into an exception), so a rank that fell behind can never yield silently different gradients.
 #include "rq_common.cuh"
 #include "rq_kernels.h"
 
@@ -58,6 +61,8 @@ __global__ void __launch_bounds__(kPeerThreads, 2) rq_peer_allreduce_kernel(Peer
     const int b = blockIdx.x, t = threadIdx.x;
     const uint32_t E = P.epoch[b];
     uint32_t* my_ctr = P.pads[P.rank] + kPeerPadWord0 + b;
+    __shared__ int s_ok;
+    if (t == 0) s_ok = 1;
     auto barrier = [&](uint32_t target) {
         __syncthreads();                                   // this CTA's earlier accesses are done
         if (t < P.world) red_release_sys_add(P.pads[t] + kPeerPadWord0 + b, 1u);
@@ -67,11 +72,15 @@ __global__ void __launch_bounds__(kPeerThreads, 2) rq_peer_allreduce_kernel(Peer
             for (uint32_t i = 0; i < (1u << 23); ++i) {
                 if ((int32_t)(ld_acquire_sys(my_ctr) - target) >= 0) { ok = true; break; }
             }
-            if (!ok && P.err) atomicExch(P.err, 1);
+            if (!ok) {
+                s_ok = 0;
+                if (P.err) atomicExch(P.err, 1);
+            }
         }
         __syncthreads();
+        return s_ok != 0;
     };
-    barrier((2u * E + 1u) * (uint32_t)P.world);
+    bool ok = barrier((2u * E + 1u) * (uint32_t)P.world);
     float4 acc[kPeerChunksPerThread];
     const int64_t stride = (int64_t)gridDim.x * kPeerThreads;
 #pragma unroll
@@ -95,18 +104,30 @@ __global__ void __launch_bounds__(kPeerThreads, 2) rq_peer_allreduce_kernel(Peer
             }
         }
     }
-    barrier((2u * E + 2u) * (uint32_t)P.world);
+    ok = barrier((2u * E + 2u) * (uint32_t)P.world) && ok;
+    const float poison = ok ? 1.f : __int_as_float(0x7fc00000);     // a timed-out barrier: NaN, never a stale sum
 #pragma unroll
     for (int u = 0; u < kPeerChunksPerThread; ++u) {
         const int64_t i = (int64_t)b * kPeerThreads + t + u * stride;
         if (i < P.n4)
             reinterpret_cast<float4*>(P.out)[i] =
-                make_float4(acc[u].x * P.scale, acc[u].y * P.scale, acc[u].z * P.scale, acc[u].w * P.scale);
+                make_float4(acc[u].x * P.scale * poison, acc[u].y * P.scale * poison, acc[u].z * P.scale * poison,
+                            acc[u].w * P.scale * poison);
     }
     if (t == 0) P.epoch[b] = E + 1u;
 }
 
-static int* d_peer_err = nullptr;
+static int* d_peer_err[64] = {};          // one error word per device
+
+static int* peer_err_word() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!d_peer_err[dev]) {
+        if (cudaMalloc((void**)&d_peer_err[dev], sizeof(int)) != cudaSuccess) return nullptr;
+        cudaMemset(d_peer_err[dev], 0, sizeof(int));
+    }
+    return d_peer_err[dev];
+}
 
 }  // namespace rq
 
@@ -130,15 +151,13 @@ extern "C" int rq_peer_allreduce_f32(const void* peer_bufs_dev, const void* peer
     RQ_CHECK_ARG(peer_bufs_dev && peer_pads_dev && out && epoch_dev, RQ_ERR_NULL_POINTER, "rq_peer_allreduce_f32: null pointer");
     RQ_CHECK_ARG(((uintptr_t)out & 15) == 0, RQ_ERR_INVALID_ARGUMENT, "rq_peer_allreduce_f32: out must be 16-byte aligned");
     if (n_floats == 0) return 0;
-    if (!d_peer_err) {
-        RQ_CUDA(cudaMalloc((void**)&d_peer_err, sizeof(int)));
-        RQ_CUDA(cudaMemset(d_peer_err, 0, sizeof(int)));
-    }
+    int* err_word = peer_err_word();
+    RQ_CHECK_ARG(err_word != nullptr, RQ_ERR_NO_DEVICE, "rq_peer_allreduce_f32: no error word for the current device");
     PeerArParams P;
     P.bufs = reinterpret_cast<const float* const*>(peer_bufs_dev);
     P.pads = reinterpret_cast<uint32_t* const*>(peer_pads_dev);
     P.rank = rank; P.world = world; P.offset_floats = offset_floats; P.n4 = n_floats / 4;
-    P.out = out; P.scale = scale; P.epoch = epoch_dev; P.err = d_peer_err;
+    P.out = out; P.scale = scale; P.epoch = epoch_dev; P.err = err_word;
     // every rank must launch the same grid (the barrier counters are per CTA): a function of n only
     int64_t ctas = (P.n4 + kPeerThreads - 1) / kPeerThreads;
     if (ctas > kPeerMaxCtas) ctas = kPeerMaxCtas;
@@ -148,7 +167,8 @@ extern "C" int rq_peer_allreduce_f32(const void* peer_bufs_dev, const void* peer
 }
 
 extern "C" int rq_debug_peer_timeout_flag(void) {
-    int v = 0;
-    if (rq::d_peer_err) cudaMemcpy(&v, rq::d_peer_err, sizeof(int), cudaMemcpyDeviceToHost);
+    int v = 0, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && rq::d_peer_err[dev])
+        cudaMemcpy(&v, rq::d_peer_err[dev], sizeof(int), cudaMemcpyDeviceToHost);
     return v;
 }

@@ -67,7 +67,6 @@ __global__ void __launch_bounds__(kBigkThreads) rq_bigk_merge_kernel(BigkMergePa
 }
 
 bool tc64_bigk_supported(int D, int K, int L, int mode, int distance) {
-    if (getenv("RQ_DISABLE_TCGEN05")) return false;
     // also serves K <= 256 with more levels than the fused d=64 kernel keeps resident (L > 3)
     return D == 64 && K >= 1 && L >= 1 && (K > kBigkChunk || L > 3) && distance == RQ_DIST_L2 &&
            (mode == RQ_MODE_EVAL || mode == RQ_MODE_STE || mode == RQ_MODE_ROTATION_TRICK);

@@ -175,11 +175,11 @@ static int launch_fwd(const FwdParams& p0, cudaStream_t st) {
     if (p.mode == RQ_MODE_GUMBEL_SOFTMAX) {
         if (D > 64) { set_error("GUMBEL_SOFTMAX supports D <= 64 in the SIMT family (got %d)", D); return RQ_ERR_UNSUPPORTED_SHAPE; }
         auto kern = rq_fwd_simt_kernel<(D > 64 ? 64 : D), true>;
-        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)kern, (int)smem));
         kern<<<grid, kSimtThreads, smem, st>>>(p);
     } else {
         auto kern = rq_fwd_simt_kernel<D, false>;
-        RQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)kern, (int)smem));
         kern<<<grid, kSimtThreads, smem, st>>>(p);
     }
     RQ_LAUNCHED();

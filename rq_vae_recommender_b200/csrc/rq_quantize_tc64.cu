@@ -461,7 +461,6 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_kernel(Tc64Param
 }
 
 bool tc64_supported(int D, int K, int L, int mode, int distance) {
-    if (getenv("RQ_DISABLE_TCGEN05")) return false;
     return D == tc64::D && K >= 1 && K <= tc64::KC && L >= 1 && L <= tc64::MAX_L && distance == RQ_DIST_L2 &&
            (mode == RQ_MODE_EVAL || mode == RQ_MODE_STE || mode == RQ_MODE_ROTATION_TRICK);
 }
@@ -485,11 +484,7 @@ int quantize_forward_tc64(const FwdParams& p, cudaStream_t st) {
     P.err = d_err64;
     P.n_tiles = (int)((p.B + tc64::TILE_M - 1) / tc64::TILE_M);
     const tc64::SmemLayout S = tc64::smem_layout(p.L);
-    static bool attr_set = false;
-    if (!attr_set) {
-        RQ_CUDA(cudaFuncSetAttribute(rq_fwd_tc64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
+    RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_fwd_tc64_kernel, 227 * 1024));
     int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
     if (p.n_chunks > 1) {
         // equal share of the SMs per chunk (at least one CTA each)

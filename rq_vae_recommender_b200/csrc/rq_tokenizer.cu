@@ -204,7 +204,10 @@ __global__ void gather_tokens_kernel(const int64_t* __restrict__ table, int64_t 
     // negative ids wrap like torch indexing does (ids_fut padding is -1).
     int64_t id = item_ids[t];
     if (id < 0) id += n_rows;
-    out[i] = keep ? table[id * W + w] : -1;
+    // ids outside [-n_rows, n_rows) raise IndexError in the reference; the Python mirror checks the range before the
+    // launch (SemanticIdTokenizer.forward).  The kernel itself never reads out of bounds: such a token becomes -1.
+    const bool in_range = id >= 0 && id < n_rows;
+    out[i] = (keep && in_range) ? table[id * W + w] : -1;
 }
 
 extern "C" int rq_gather_tokens(const int64_t* table, int64_t n_rows, int W, const int64_t* item_ids,

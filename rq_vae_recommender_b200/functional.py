@@ -15,8 +15,14 @@ from ._lib import (DIST_COSINE, DIST_L2, IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05, MOD
 
 
 def _f32c(t: torch.Tensor, name: str) -> torch.Tensor:
+    """CUDA fp32, contiguous, 32-byte aligned (the kernels use 128/256-bit accesses and TMA bulk copies): a view with
+    an odd storage offset is cloned instead of being handed to the library misaligned."""
     L.require_cuda(t, name, torch.float32)
-    return t if t.is_contiguous() else t.contiguous()
+    if not t.is_contiguous():
+        t = t.contiguous()
+    if t.data_ptr() % 32 != 0 and t.numel():
+        t = t.clone(memory_format=torch.contiguous_format)
+    return t
 
 
 def quantize_forward(x: torch.Tensor, codebooks: torch.Tensor, mode: int = MODE_EVAL, beta: float = 0.25,
@@ -123,7 +129,21 @@ class ResidualQuantizeFn(torch.autograd.Function):
 
 def residual_quantize(x, codebooks, mode=MODE_EVAL, beta=0.25, temperature=0.2, distance=DIST_L2,
                       gumbel_uniform=None, seed=0, offset=0, impl=IMPL_AUTO):
-    """Differentiable fused quantiser: (emb [L,B,D], residuals [L,B,D], ids [L,B], loss [B])."""
+    """Differentiable fused quantiser: (emb [L,B,D], residuals [L,B,D], ids [L,B], loss [B]).
+
+    The engine computes in fp32 ("all arithmetic is fp32"): half / bfloat16 latents (the reference runs its
+    encoder under `accelerator.autocast()`, train_rqvae.py:147) are upcast here, outputs and gradients are fp32 like
+    the reference's quantiser, whose distance GEMM autocast keeps in fp32 only by accident of `torch.cdist`-free code."""
+    if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16):
+        x = x.float()
+    if codebooks.is_cuda and codebooks.dtype in (torch.float16, torch.bfloat16):
+        codebooks = codebooks.float()
+    if (mode == MODE_GUMBEL_SOFTMAX and distance == DIST_COSINE and torch.is_grad_enabled()
+            and (x.requires_grad or codebooks.requires_grad)):
+        raise L.RqEngineError(
+            "GUMBEL_SOFTMAX with COSINE distance is forward-only in the engine: the fused backward differentiates the "
+            "L2 logits (quantize.py:108-112).  Use distance_mode=L2 (what RqVae always does, rqvae.py:65-73), or call "
+            "under torch.no_grad()")
     if torch.is_grad_enabled() and (x.requires_grad or codebooks.requires_grad):
         return ResidualQuantizeFn.apply(x, codebooks, mode, beta, temperature, distance, gumbel_uniform, seed,
                                         offset, impl)

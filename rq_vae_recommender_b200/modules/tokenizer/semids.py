@@ -158,7 +158,12 @@ class SemanticIdTokenizer(nn.Module):
     @torch.no_grad()
     @eval_mode
     def forward(self, batch: SeqBatch) -> TokenizedSeqBatch:
-        if self.cached_ids is None or batch.ids.max() >= self.cached_ids.shape[0]:
+        ids_max, fut_max = -1, -1
+        if self.cached_ids is not None:
+            # one host read, like the reference's `batch.ids.max() >= ...` (semids.py:131); the future ids ride along
+            fut = batch.ids_fut.max() if batch.ids_fut is not None and batch.ids_fut.numel() else batch.ids.new_tensor(-1)
+            ids_max, fut_max = torch.stack([batch.ids.max(), fut.to(batch.ids.device)]).tolist()
+        if self.cached_ids is None or ids_max >= self.cached_ids.shape[0]:
             B, N = batch.ids.shape
             sem_ids = self.rq_vae.get_semantic_ids(batch.x).sem_ids
             D = sem_ids.shape[-1]
@@ -167,6 +172,9 @@ class SemanticIdTokenizer(nn.Module):
             B, N = batch.ids.shape
             _, D = self.cached_ids.shape
             seq_mask = batch.seq_mask.repeat_interleave(D, dim=1)
+            if fut_max >= self.cached_ids.shape[0]:
+                # `self.cached_ids[ids_fut.flatten(), :]` in the reference (semids.py:123,143)
+                raise IndexError(f"index {fut_max} is out of bounds for dimension 0 with size {self.cached_ids.shape[0]}")
             sem_ids = self._tokenize_seq_batch_from_cached(batch.ids, batch.seq_mask)
             sem_ids_fut = self._tokenize_seq_batch_from_cached(batch.ids_fut)
         token_type_ids = torch.arange(D, device=sem_ids.device).repeat(B, N)

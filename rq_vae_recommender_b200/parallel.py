@@ -104,6 +104,17 @@ class PeerAllReduce:
         L.check(rc, "rq_peer_allreduce_f32")
         return dst
 
+    def check(self) -> None:
+        """Raises if a barrier of an earlier `all_reduce_` on this device timed out (a rank more than a few seconds
+        behind: rank-0-only evaluation or checkpointing in the middle of a step).  The affected output was filled
+        with NaN by the kernel, never with a partial sum.  Synchronises the device: call it at a step boundary (e.g.
+        next to optimizer.step())."""
+        from . import _lib as L
+        if L.lib().rq_debug_peer_timeout_flag():
+            raise RuntimeError("PeerAllReduce: a rank did not reach the exchange within the timeout; the reduced "
+                               "buffer was poisoned with NaN (ranks must enter all_reduce_ within a few seconds of "
+                               "each other)")
+
 
 def is_distributed(group=None) -> bool:
     import torch.distributed as dist

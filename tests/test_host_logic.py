@@ -242,7 +242,10 @@ def test_bench_reference_arm_prints_exactly_one_json_line():
     assert len(lines) == 1, r.stdout
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["unit"] == "items/s" and d["value"] > 0
-    assert d["cpu_baseline"]["kind"] == "port" and d["e2e"]["h2d_bytes_per_step"] == 0
+    # "reference" when oracle/_ref holds the vendored reference (oracle/build_ref.py), else the oracle port
+    have_ref = os.path.exists(os.path.join(root, "oracle", "_ref", "MANIFEST.json"))
+    assert d["cpu_baseline"]["kind"] == ("reference" if have_ref else "port") and d["e2e"]["h2d_bytes_per_step"] == 0
+    assert d["steps"] == 1 and d["warmup"] == 1          # the arm honours the driver's --steps / --warmup
     # a non-zero rank of a multi-rank launch does no work and prints nothing
     env = dict(os.environ, RANK="1", WORLD_SIZE="2")
     r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
