@@ -179,6 +179,20 @@ int rq_id_diversity(const int64_t* table, int64_t N, int L, int64_t codebook_siz
                     int64_t* max_dup, void* workspace, int64_t workspace_bytes, rq_stream_t stream);
 
 /*
+ * rq_id_diversity without a workspace and without any allocation (no cudaMalloc / cudaFree / allocating library
+ * call on any path), for callers that cannot allocate: code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it.  No counterpart in the reference.
+ * Inputs, outputs and results are those of rq_id_diversity; the (level, id) bitmap lives in a file-scope device
+ * array of rq_id_diversity_static_max_bytes() = 65,536 bytes that every GPU loading the library holds until exit.
+ * Limit: L * ceil(codebook_size / 32) * 4 <= 65,536 (e.g. L = 4 levels of up to 131,072 ids); beyond it the call
+ * returns RQ_ERR_WORKSPACE_TOO_SMALL and launches nothing.  The array is shared by all calls on a device and is
+ * cleared at the start of each: calls that overlap on the GPU (different streams, no ordering) race on it.
+ */
+int64_t rq_id_diversity_static_max_bytes(void);
+int rq_id_diversity_static(const int64_t* table, int64_t N, int L, int64_t codebook_size, double* entropy,
+                           int64_t* used, int64_t* max_dup, rq_stream_t stream);
+
+/*
  * One-shot all-reduce (sum * scale) of a small fp32 region over peer-mapped symmetric memory (NVLink loads, no
  * NCCL): the codebook-gradient exchange of a training step, which the reference leaves to DDP
  * (train_rqvae.py:115-117,153), and the k-means sums / counts exchange.  Capturable in a CUDA graph; every rank

@@ -55,6 +55,8 @@ SIGNATURES = {
     "rq_id_diversity_workspace_bytes": (c_int64, [c_int, c_int64]),
     "rq_id_diversity": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
                                 c_void_p]),
+    "rq_id_diversity_static_max_bytes": (c_int64, []),
+    "rq_id_diversity_static": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "rq_debug_tc_timeout_flag": (c_int, []),
     "rq_debug_tc_set_accumulator_dump": (c_int, [c_void_p]),
     "rq_debug_tc_set_timeline": (c_int, [c_void_p]),

@@ -14,6 +14,8 @@
 // is hand-written.
 #include <cub/cub.cuh>
 
+#include <mutex>
+
 #include "rq_common.cuh"
 #include "rq_kernels.h"
 
@@ -325,6 +327,71 @@ extern "C" int rq_id_diversity(const int64_t* table, int64_t N, int L, int64_t c
         reinterpret_cast<uint32_t*>(workspace));
     RQ_LAUNCHED();
     id_usage_kernel<<<L, 256, 0, st>>>(reinterpret_cast<const uint32_t*>(workspace), L, words, used);
+    RQ_LAUNCHED();
+    return 0;
+}
+
+// ---- id diversity without any allocation -----------------------------------------------------
+// Same two kernels, with the (level, id) bitmap in a file-scope device array instead of a caller workspace, for
+// callers that may not allocate (graph capture, serving loops).  The array is part of the module image: every GPU
+// that loads the library holds kIdDiversityStaticBytes of it until exit.  In host code `g_id_bitmap_static` is only
+// a stand-in for the symbol; the device address comes from cudaGetSymbolAddress, looked up once per device with
+// that device current.  All calls on a device share the array: it is cleared at the start of every call, and two
+// calls that overlap on the GPU (different streams) race on it.
+namespace rq {
+constexpr int64_t kIdDiversityStaticBytes = 64 * 1024;
+static __device__ __align__(256) unsigned char g_id_bitmap_static[kIdDiversityStaticBytes];
+
+static cudaError_t id_bitmap_static_ptr(uint32_t** out) {
+    static std::mutex mu;
+    static uint32_t* per_dev[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!per_dev[dev]) {
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_id_bitmap_static);
+        if (e != cudaSuccess) return e;
+        per_dev[dev] = static_cast<uint32_t*>(ptr);
+    }
+    *out = per_dev[dev];
+    return cudaSuccess;
+}
+}  // namespace rq
+
+extern "C" int64_t rq_id_diversity_static_max_bytes(void) { return rq::kIdDiversityStaticBytes; }
+
+extern "C" int rq_id_diversity_static(const int64_t* table, int64_t N, int L, int64_t codebook_size, double* entropy,
+                                      int64_t* used, int64_t* max_dup, rq_stream_t stream) {
+    using namespace rq;
+    cudaStream_t st = (cudaStream_t)stream;
+    RQ_CHECK_ARG(N >= 1 && L >= 1 && codebook_size >= 1, RQ_ERR_INVALID_ARGUMENT,
+                 "rq_id_diversity_static: need N >= 1, L >= 1, codebook_size >= 1");
+    RQ_CHECK_ARG(table && entropy && used && max_dup, RQ_ERR_NULL_POINTER, "rq_id_diversity_static: null pointer");
+    const int64_t words64 = (codebook_size + 31) / 32;
+    RQ_CHECK_ARG(words64 <= kIdDiversityStaticBytes / 4 && (int64_t)L * words64 * 4 <= kIdDiversityStaticBytes,
+                 RQ_ERR_WORKSPACE_TOO_SMALL,
+                 "rq_id_diversity_static: L * ceil(codebook_size / 32) * 4 = %lld bytes exceeds the built-in %lld-byte "
+                 "bitmap; use rq_id_diversity with a caller workspace",
+                 (long long)L * (long long)words64 * 4, (long long)kIdDiversityStaticBytes);
+    const int64_t need = (int64_t)L * words64 * 4;
+    const int words = (int)words64;
+    uint32_t* bitmap = nullptr;
+    RQ_CUDA(id_bitmap_static_ptr(&bitmap));
+    RQ_CUDA(cudaMemsetAsync(bitmap, 0, (size_t)need, st));
+    RQ_CUDA(cudaMemsetAsync(entropy, 0, sizeof(double), st));
+    RQ_CUDA(cudaMemsetAsync(max_dup, 0, sizeof(int64_t), st));
+    const bool use_smem = need <= 32 * 1024;
+    const int T = 256;
+    int64_t blocks = (N + T - 1) / T;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    id_diversity_kernel<<<(unsigned)blocks, T, use_smem ? (size_t)need : 0, st>>>(
+        table, N, L, codebook_size, words, use_smem, entropy, reinterpret_cast<unsigned long long*>(max_dup), bitmap);
+    RQ_LAUNCHED();
+    id_usage_kernel<<<L, 256, 0, st>>>(bitmap, L, words, used);
     RQ_LAUNCHED();
     return 0;
 }
