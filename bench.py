@@ -684,6 +684,54 @@ def run_engine(args):
     if not e2e_ok:
         raise RuntimeError("e2e: the pipelined step's host result differs from a direct launch on the same batch")
 
+    # ---- the same e2e step through torch.compile(mode="reduce-overhead") — the reference's own decorator
+    # (rqvae.py:140) — instead of the hand-captured graphs above: Dynamo traces the module through the torch.library
+    # ops of rq_vae_recommender_b200/ops.py, AOTAutograd builds the backward, CUDA-graph trees replay both.  Reported
+    # beside the headline e2e (extra.e2e_compiled); a host without a working Inductor toolchain reports the error.
+    e2e_compiled = None
+    if not args.no_extras:
+        try:
+            cq = torch.compile(quantizer, mode="reduce-overhead")
+            feed_c = R.data.utils.DevicePrefetcher(R.data.utils.cycle(xs_pin), dev)
+
+            def compiled_step(i):
+                s = i % E2E_SLOTS
+                lat = next(feed_c).requires_grad_(True)
+                for prm in q_params:
+                    prm.grad = None
+                torch.compiler.cudagraph_mark_step_begin()
+                emb, sem_ids, qloss = cq(lat)
+                torch.autograd.backward([emb, qloss], [g_embs_bdl[s], g_loss])
+                loss_pin[s].copy_(qloss.detach(), non_blocking=True)
+                ids_pin[s].copy_(sem_ids.detach().t(), non_blocking=True)
+                done[s].record()
+                if i > 0:
+                    done[(i - 1) % E2E_SLOTS].synchronize()
+
+            t_c0 = time.perf_counter()
+            for i in range(6):                                                  # compile + CUDA-graph warm-up + recording
+                compiled_step(i)
+            fence()
+            compile_s = time.perf_counter() - t_c0
+            n_c = max(args.steps, 40)
+            t0 = time.perf_counter()
+            for i in range(n_c):
+                compiled_step(6 + i)
+            fence()
+            c_s = time.perf_counter() - t0
+            j_last = 6 + n_c - 1
+            _, _, ids_c, loss_c = RF.quantize_forward(xs_pin[j_last % len(xs_pin)].to(dev), cbs, mode, BETA, TEMP)
+            e2e_compiled = {"items_per_s": B_PER_GPU * n_c / c_s, "us_per_step": c_s / n_c * 1e6, "steps": n_c,
+                            "call": 'torch.compile(module, mode="reduce-overhead") forward + autograd backward, '
+                                    "DevicePrefetcher H2D, D2H of loss + ids",
+                            "compile_and_warmup_s": compile_s,
+                            "result_checked": bool(torch.equal(ids_pin[j_last % E2E_SLOTS], ids_c.cpu()) and
+                                                   torch.allclose(loss_pin[j_last % E2E_SLOTS], loss_c.cpu(),
+                                                                  rtol=1e-5, atol=1e-7))}
+        except Exception as ex:
+            e2e_compiled = {"error": f"{type(ex).__name__}: {str(ex)[:400]}"}
+            torch.cuda.synchronize()
+
     # ---- side numbers (outside the timed region): ids-only tokenisation launch -------------------
     ids_fn = lambda s: RF.quantize_forward(xs[s], cbs, RF.MODE_EVAL, want_embeddings=False,  # noqa: E731
                                            want_residuals=False, want_loss=False)
@@ -743,7 +791,7 @@ def run_engine(args):
                       "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode,
                       "grad_exchange": (None if world == 1 else ("rq_peer_allreduce_f32 (peer memory, " + ("in the step graph)" if peer_inline else "side stream beside the graphs)"))
                                         if peer is not None else "NCCL all_reduce, async beside the graphs"),
-                      "e2e_result_checked": e2e_ok, "timing": timing, **extras},
+                      "e2e_result_checked": e2e_ok, "e2e_compiled": e2e_compiled, "timing": timing, **extras},
         }
         if not args.no_cpu_baseline and world == 1:
             ips, ms, cores, kind, what = cpu_reference_run(args.cpu_sample_items, 3, 1)

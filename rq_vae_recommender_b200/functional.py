@@ -144,6 +144,11 @@ def residual_quantize(x, codebooks, mode=MODE_EVAL, beta=0.25, temperature=0.2, 
             "GUMBEL_SOFTMAX with COSINE distance is forward-only in the engine: the fused backward differentiates the "
             "L2 logits (quantize.py:108-112).  Use distance_mode=L2 (what RqVae always does, rqvae.py:65-73), or call "
             "under torch.no_grad()")
+    if torch.compiler.is_compiling():
+        # inside torch.compile the ctypes call is untraceable: go through the registered custom op (ops.py), which
+        # carries its own fake implementation and autograd formula
+        return _ops.quantize_forward(x, codebooks, int(mode), float(beta), float(temperature), int(distance),
+                                     gumbel_uniform, int(seed), int(offset), int(impl))
     if torch.is_grad_enabled() and (x.requires_grad or codebooks.requires_grad):
         return ResidualQuantizeFn.apply(x, codebooks, mode, beta, temperature, distance, gumbel_uniform, seed,
                                         offset, impl)
@@ -193,6 +198,8 @@ def kmeans_update(sums, counts, centroids):
 # ---- tokenizer integer paths ------------------------------------------------------------------
 def corpus_table(sem_ids: torch.Tensor, codebook_size: int) -> torch.Tensor:
     """[N,L] int64 (any strides) -> [N,L+1] int64 = [ids | dedup] (semids.py:86-99)."""
+    if torch.compiler.is_compiling():
+        return _ops.corpus_table(sem_ids, int(codebook_size))
     L.require_cuda(sem_ids, "sem_ids", torch.int64)
     N, Lv = sem_ids.shape
     dev = sem_ids.device
@@ -259,6 +266,8 @@ def prefix_exists(sorted_keys: torch.Tensor, queries: torch.Tensor, radix: int) 
 
 def gather_tokens(table: torch.Tensor, item_ids: torch.Tensor, seq_mask: Optional[torch.Tensor] = None):
     """table [N,W], item_ids [B,n] -> [B, n*W] with padding -> -1 (semids.py:122-123, 137-141)."""
+    if torch.compiler.is_compiling():
+        return _ops.gather_tokens(table, item_ids, seq_mask)
     L.require_cuda(table, "table", torch.int64)
     L.require_cuda(item_ids, "item_ids", torch.int64)
     table = table.contiguous()
@@ -275,3 +284,6 @@ def gather_tokens(table: torch.Tensor, item_ids: torch.Tensor, seq_mask: Optiona
                                       L.stream_of(table))
     L.check(rc, "rq_gather_tokens")
     return out
+
+
+from . import ops as _ops  # noqa: E402  (torch.library registration; imports this module back)

@@ -72,7 +72,9 @@ class GumbelNoise:
 
     @classmethod
     def next(cls, n_levels: int, B: int, K: int, device):
-        if cls.source == "torch":
+        # under torch.compile a Python-side call counter would be baked into the graph as a constant (the same noise
+        # every step): there the draws are torch.rand nodes of the graph, like the reference's (gumbel.py:9)
+        if cls.source == "torch" or torch.compiler.is_compiling():
             return torch.stack([torch.rand((B, K), device=device) for _ in range(n_levels)]), 0, 0
         cls._calls += 1
         return None, int(torch.initial_seed()) & 0xFFFFFFFFFFFFFFFF, cls._calls

@@ -5,6 +5,9 @@ Same constructor, attributes, NamedTuple outputs, memory layouts and state-dict 
 The level loop of `get_semantic_ids` (:124-131) is ONE fused CUDA launch over all L levels; the
 encoder / decoder MLPs stay on torch (cuBLAS), outside the named path.
 """
+import os
+import warnings
+import weakref
 from functools import cached_property
 from typing import List, NamedTuple
 
@@ -23,6 +26,9 @@ try:  # the reference mixes in huggingface_hub.PyTorchModelHubMixin (rqvae.py:37
 except Exception:  # pragma: no cover
     class PyTorchModelHubMixin:  # type: ignore
         pass
+
+
+_COMPILED: "weakref.WeakKeyDictionary" = weakref.WeakKeyDictionary()   # RqVae instance -> compiled forward + status
 
 
 class _Placeholder:
@@ -191,9 +197,40 @@ class RqVae(nn.Module, PyTorchModelHubMixin):
     def get_semantic_ids(self, x: Tensor, gumbel_t: float = 0.001) -> RqVaeOutput:
         return self.quantize_latents(self.encode(x), gumbel_t)
 
+    # The reference decorates forward with @torch.compile(mode="reduce-overhead") (rqvae.py:140).  Same here, through
+    # the torch.library ops of ops.py (Dynamo cannot trace ctypes): Inductor fuses the encoder / decoder / loss
+    # elementwise work, the fused quantiser is one opaque node forward and one backward, and the whole step replays
+    # as CUDA graphs.  Class-level switch: `RqVae.compile_forward = False` or RQ_COMPILE_FORWARD=0 keeps it eager.
+    compile_forward: bool = os.environ.get("RQ_COMPILE_FORWARD", "1") != "0"
+    compile_mode: str = "reduce-overhead"
+
+    def _wants_compiled(self, x: Tensor) -> bool:
+        if not (self.compile_forward and x.is_cuda) or torch.compiler.is_compiling():
+            return False
+        if _COMPILED.get(self, {}).get("failed", False):
+            return False
+        # the first training forward runs k-means on the host side of every level (data-dependent Python): eager
+        return not any(layer.needs_kmeans_init() for layer in self.layers) and self._uniform_config()
+
     def forward(self, batch: SeqBatch, gumbel_t: float) -> RqVaeComputedLosses:
-        """Training losses (rqvae.py:141-165).  Not wrapped in torch.compile: the fused kernel is a
-        single graph-capturable launch already."""
+        """Training losses (rqvae.py:141-165)."""
+        if self._wants_compiled(batch.x):
+            st = _COMPILED.setdefault(self, {})              # kept outside the module: state dict / deepcopy unchanged
+            if "fn" not in st:
+                st["fn"] = torch.compile(self._forward_impl, mode=self.compile_mode)
+            try:
+                out = st["fn"](batch, gumbel_t)
+            except Exception as e:                           # e.g. no compiler toolchain on this host: stay eager
+                if st.get("ok", False):
+                    raise                                    # it worked before: a real error, not a set-up problem
+                st["failed"] = True
+                warnings.warn(f"RqVae.forward: torch.compile failed ({type(e).__name__}: {e}); running eager")
+                return self._forward_impl(batch, gumbel_t)
+            st["ok"] = True
+            return out
+        return self._forward_impl(batch, gumbel_t)
+
+    def _forward_impl(self, batch: SeqBatch, gumbel_t: float) -> RqVaeComputedLosses:
         x = batch.x
         quantized = self.get_semantic_ids(x, gumbel_t)
         embs = quantized.embeddings

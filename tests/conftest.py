@@ -10,6 +10,10 @@ for p in (ROOT, os.path.join(ROOT, "oracle")):
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
+# RqVae.forward compiles itself by default (the reference's @torch.compile, rqvae.py:140); the suite runs it eager
+# except in tests/test_gpu_compile.py, which switches it on: one Inductor compile per model would dominate the run time
+os.environ.setdefault("RQ_COMPILE_FORWARD", "0")
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
