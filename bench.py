@@ -511,7 +511,55 @@ def run_engine(args):
                 allreduce_async(_keep1[i % N_SLOTS][2], i)
         run_fwd = lambda i: fwd_graphs[i % N_SLOTS].replay()
         run_bwd = lambda i: bwd_graphs[i % N_SLOTS].replay()
-        launch_mode = "cuda-graph replay (one graph per ring slot)"
+        # One graph for the whole K-step block: K x (memset, forward, backward) over the ring, replayed once per timed
+        # block.  A graph launch costs a few us of GPU idle time between two replays (tools/launch_gap.cu: 6.5 us for a
+        # one-kernel graph against 1.1 us per kernel inside a graph); a training loop pays it once per captured region,
+        # not once per quantiser step.  The roofline legs use the same form: K forward (backward) launches in one graph,
+        # so launch_ms is a kernel's duration back to back with its peers, not kernel + graph-launch gap.
+        def capture_block(fn):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                keep = [fn((args.warmup + i) % N_SLOTS) for i in range(args.steps)]
+            return g, keep
+        block_mode = os.environ.get("RQ_BENCH_BLOCK_GRAPH", "1") != "0"
+        if block_mode:
+            fwd_block_g, _kb2 = capture_block(lambda s: RF.quantize_forward(xs[s], cbs, mode, BETA, TEMP))
+            bwd_block_g, _kb3 = capture_block(lambda s: RF.quantize_backward(g_embs[s], None, g_loss, _fwd_out[s][1],
+                                                                             _fwd_out[s][2], cbs, mode, BETA, TEMP))
+            run_fwd.block = fwd_block_g.replay
+            run_bwd.block = bwd_block_g.replay
+            if world == 1:
+                step_block_g, _kb1 = capture_block(step_compute)
+                run_step.block = step_block_g.replay
+            elif os.environ.get("RQ_BENCH_DIST_BLOCK_GRAPH", "0") == "1" and peer is None:
+                # N > 1 (opt-in; measured at N = 2: 51.0 us/step against 50.8 for the default below, so the default stays
+                # one graph per ring slot with NCCL's async op beside the replays): the same K-step graph with the
+                # exchange captured on a forked stream.  Inside one graph the
+                # all-reduce of step i joins the main chain only where its buffer is reused (N_SLOTS steps later) and at
+                # the end of the block, so it overlaps the next steps' kernels like the eager async op does.
+                ex_stream = torch.cuda.Stream()
+                step_block_g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(step_block_g):
+                    main_s = torch.cuda.current_stream()
+                    done = [None] * N_SLOTS
+                    for i in range(args.steps):
+                        s_ = (args.warmup + i) % N_SLOTS
+                        if done[s_] is not None:
+                            main_s.wait_event(done[s_])
+                        out = step_compute(s_)
+                        ev = torch.cuda.Event()
+                        ev.record(main_s)
+                        ex_stream.wait_event(ev)
+                        with torch.cuda.stream(ex_stream):
+                            dist.all_reduce(out[2])
+                            ev2 = torch.cuda.Event()
+                            ev2.record(ex_stream)
+                        done[s_] = ev2
+                    main_s.wait_stream(ex_stream)
+                run_step.block = step_block_g.replay
+        launch_mode = (("cuda-graph replay (one graph per K-step block" +
+                        ("; the exchange captured on a forked stream)" if world > 1 else ")"))
+                       if getattr(run_step, "block", None) else "cuda-graph replay (one graph per ring slot)")
     except Exception as e:                              # pragma: no cover - capture unsupported in this setup
         if use_graphs:
             print(f"bench.py: CUDA-graph capture failed ({e}); timing eager launches", file=sys.stderr)
@@ -527,8 +575,11 @@ def run_engine(args):
     def timed(fn, n):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        for i in range(n):
-            fn(args.warmup + i)
+        if getattr(fn, "block", None) is not None and n == args.steps:
+            fn.block()                                  # the K steps as one captured graph
+        else:
+            for i in range(n):
+                fn(args.warmup + i)
         while pending:
             pending.pop(0).wait()                       # the last reductions are part of the K steps
         if side is not None:
@@ -559,6 +610,9 @@ def run_engine(args):
 
     for i in range(args.warmup):
         run_step(i)
+    for f_ in (run_step, run_fwd, run_bwd):
+        if getattr(f_, "block", None) is not None:
+            f_.block()                                  # untimed first replay of each block graph
     fence()
     l0 = R.launch_count()
     with ClockSampler(local) as clk:

@@ -49,8 +49,26 @@ def child():
             torch.cuda.synchronize()
             best = min(best, e0.elapsed_time(e1) / 40 * 1e3)
         out[name] = best
+        if name == "fwd":
+            # the same launches back to back inside ONE graph (40 kernel nodes): per-launch time without the
+            # graph-launch gap that a one-kernel graph pays
+            gg = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gg):
+                for i in range(40):
+                    keep.append(fn(i % N))
+            gg.replay()
+            bestg = 1e9
+            for rep in range(5):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                e0.record()
+                gg.replay()
+                e1.record()
+                torch.cuda.synchronize()
+                bestg = min(bestg, e0.elapsed_time(e1) / 40 * 1e3)
+            out["fwd_in_graph"] = bestg
     ref = keep[0]
-    print(f"{os.environ.get('RQ_AB_LIB', 'default'):50s} fwd {out['fwd']:.2f} us  ids-only {out['ids']:.2f} us  bwd {out['bwd']:.2f} us", flush=True)
+    print(f"{os.environ.get('RQ_AB_LIB', 'default'):50s} fwd {out['fwd']:.2f} us (40 in one graph: {out['fwd_in_graph']:.2f})  ids-only {out['ids']:.2f} us  bwd {out['bwd']:.2f} us", flush=True)
 
 
 if __name__ == "__main__":
