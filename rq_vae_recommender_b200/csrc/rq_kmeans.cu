@@ -175,12 +175,150 @@ __global__ void __launch_bounds__(512) rq_kmeans_accumulate_smem_kernel(const fl
         if (s_cnt[kk]) atomicAdd(counts + kk, (unsigned long long)s_cnt[kk]);
 }
 
+// The same accumulation on the integer unit.  atomicAdd(float*) on shared memory is a compare-and-swap loop on sm_100a
+// (ATOMS.CAST.SPIN); the 32-bit integer add is native (ATOMS.ADD).  A component v is therefore added as the fixed-point
+// number f = rint(v * S), S = 2^22 / range, in two pieces (f >> 11 and f & 0x7ff, each good for 2^20 rows per CTA
+// before an int32 could overflow), and the CTA's partials leave as one float reduction per (cluster, component).
+// `range` is a power of two >= 16 max|centroid component|, computed by every CTA from the centroids; a component outside
+// (-range, range) — an outlier far from every centroid, Inf or NaN — is added straight to the global sum in floating
+// point, so the result never depends on the choice of range, only the speed does.  |f / S - v| <= 2^-23 range, unbiased.
+template <int D>
+__global__ void __launch_bounds__(512, 2) rq_kmeans_accumulate_fx_kernel(const float* __restrict__ x,
+                                                                      const int64_t* __restrict__ assign, int64_t B,
+                                                                      int K, const float* __restrict__ centroids,
+                                                                      float* __restrict__ sums,
+                                                                      unsigned long long* __restrict__ counts) {
+    extern __shared__ __align__(16) int s_fx[];
+    int* s_hi = s_fx;
+    int* s_lo = s_fx + (size_t)K * D;
+    unsigned* s_cnt = reinterpret_cast<unsigned*>(s_fx + 2 * (size_t)K * D);
+    __shared__ float s_max[16];
+    for (int i = threadIdx.x; i < 2 * K * D + K; i += blockDim.x) s_fx[i] = 0;
+    float cm = 0.f;
+    for (int i = threadIdx.x; i < K * D; i += blockDim.x) cm = fmaxf(cm, fabsf(__ldg(centroids + i)));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cm = fmaxf(cm, __shfl_xor_sync(0xffffffffu, cm, o));
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = cm;
+    __syncthreads();
+    cm = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) cm = fmaxf(cm, s_max[w]);
+    // power of two in [16 cm, 32 cm); exponent clamped so that S and 1/S stay normal numbers (NaN / Inf centroids: cm
+    // propagates as the largest finite exponent, every component then takes the floating-point path or a tiny f)
+    int e = (int)((__float_as_uint(cm) >> 23) & 0xffu) + 5;
+    e = e < 30 ? 30 : (e > 220 ? 220 : e);
+    const float range = __uint_as_float((unsigned)e << 23);
+    const float S = 4194304.f / range;
+    // A warp takes whole rows, lane l the components l, l + 32, ...: every load instruction reads 128 contiguous bytes
+    // and the 32 lanes of a reduction hit 32 different banks whatever the id (word k D + 32 c + l), with no per-lane
+    // component shuffling.  The id is one broadcast load per row.  U rows are in flight per warp.  The loop is bound by
+    // instruction issue, so the body is branch-free (32-bit shared addresses, predicated count, outliers collected in
+    // one flag per U rows and handled after the fact).
+    constexpr int C = D / 32;
+    constexpr int U = 8;
+    const int lane = threadIdx.x & 31;
+    const uint32_t hi_base = (uint32_t)__cvta_generic_to_shared(s_hi) + lane * 4;
+    const uint32_t lo_base = (uint32_t)__cvta_generic_to_shared(s_lo) + lane * 4;
+    const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(s_cnt);
+    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    auto fx_add = [&](int k, int c, float val) -> bool {
+        const uint32_t off = (uint32_t)(k * D + 32 * c) * 4u;
+        const float sc = val * S;
+        const bool ok = fabsf(sc) < 4194304.f;
+        // rint(sc) for |sc| < 2^22: the low mantissa bits of sc + 1.5 * 2^23
+        const int f = ok ? (__float_as_int(sc + 12582912.f) - 0x4B400000) : 0;
+        asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(hi_base + off), "r"(f >> 11) : "memory");
+        asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(lo_base + off), "r"(f & 0x7ff) : "memory");
+        return !ok;
+    };
+    auto count_one = [&](int k) {
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %2, 0;\n\t@p red.shared.add.u32 [%0], %1;\n\t}"
+                     ::"r"(cnt_base + (uint32_t)k * 4u), "r"(1u), "r"((uint32_t)lane) : "memory");
+    };
+    const int64_t n_full = B / U;                         // blocks of U whole rows
+    auto load_block = [&](int64_t blk, int (&k)[U], float (&v)[U][C]) {
+        const int64_t r0 = blk * U;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            k[u] = (int)__ldg(reinterpret_cast<const int*>(assign + r0 + u));       // low word of the int64 id
+#pragma unroll
+            for (int c = 0; c < C; ++c)
+                asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v[u][c]) : "l"(x + (r0 + u) * D + 32 * c + lane));
+        }
+    };
+    auto add_block = [&](const int (&k)[U], const float (&v)[U][C]) {
+        bool bad = false;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) bad |= fx_add(k[u], c, v[u][c]);
+            count_one(k[u]);
+        }
+        if (__any_sync(0xffffffffu, bad)) {              // rare: components outside the fixed-point range
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+                    if (!(fabsf(v[u][c] * S) < 4194304.f)) atomicAdd(sums + k[u] * D + 32 * c + lane, v[u][c]);
+        }
+    };
+    // two blocks in flight per warp: the loads of one are outstanding while the other is added
+    {
+        int kA[U], kB[U];
+        float vA[U][C], vB[U][C];
+        int64_t blk = warp0;
+        if (blk < n_full) load_block(blk, kA, vA);
+        while (blk < n_full) {
+            const int64_t blkB = blk + n_warps;
+            const bool hasB = blkB < n_full;
+            if (hasB) load_block(blkB, kB, vB);
+            add_block(kA, vA);
+            blk = blkB + n_warps;
+            if (blk < n_full) load_block(blk, kA, vA);
+            if (hasB) add_block(kB, vB);
+        }
+    }
+    // the last B % U rows: one warp of the grid
+    if (warp0 == n_warps - 1) {
+        for (int64_t row = n_full * U; row < B; ++row) {
+            const int k = (int)__ldg(reinterpret_cast<const int*>(assign + row));
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const float val = __ldg(x + row * D + 32 * c + lane);
+                if (fx_add(k, c, val)) atomicAdd(sums + k * D + 32 * c + lane, val);
+            }
+            count_one(k);
+        }
+    }
+    __syncthreads();
+    const double inv = 1.0 / (double)S;
+    for (int i = threadIdx.x; i < K * D; i += blockDim.x) {
+        const long long tot = (long long)s_hi[i] * 2048 + (long long)s_lo[i];
+        if (tot != 0) atomicAdd(sums + i, (float)((double)tot * inv));
+    }
+    for (int kk = threadIdx.x; kk < K; kk += blockDim.x)
+        if (s_cnt[kk]) atomicAdd(counts + kk, (unsigned long long)s_cnt[kk]);
+}
+
 // sums / counts must be zeroed by the caller.  Picks the shared-memory kernel when K*D partials fit.
 template <int D>
 static int launch_kmeans_accumulate(const KmeansParams& p, cudaStream_t st) {
     const size_t smem = (size_t)p.K * D * 4 + (size_t)p.K * 4;
     const int64_t n_chunks = p.B * (D / 4);
-    if (smem <= 100 * 1024) {
+    const size_t smem_fx = 2 * (size_t)p.K * D * 4 + (size_t)p.K * 4;
+    // fixed-point partials: an int32 piece holds 2^20 rows per CTA (see the kernel), the grid below gives each CTA B / grid
+    if (smem_fx <= 200 * 1024) {
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_kmeans_accumulate_fx_kernel<D>, 200 * 1024));
+        int per_sm = (int)((224 * 1024) / (smem_fx + 1024));
+        if (per_sm > 3) per_sm = 3;
+        int64_t blocks = (n_chunks + 512 * 4 - 1) / (512 * 4);
+        const int64_t cap = (int64_t)sm_count() * per_sm;
+        if (blocks > cap) blocks = cap;
+        const int64_t min_blocks = (p.B >> 20) + 1;           // <= 2^20 rows per CTA
+        if (blocks < min_blocks) blocks = min_blocks;
+        rq_kmeans_accumulate_fx_kernel<D><<<(unsigned)blocks, 512, smem_fx, st>>>(p.x, p.assign, p.B, p.K, p.centroids,
+                                                                                 p.sums, p.counts);
+    } else if (smem <= 100 * 1024) {
         RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_kmeans_accumulate_smem_kernel<D>, 100 * 1024));
         int per_sm = (int)((220 * 1024) / (smem + 1024));
         if (per_sm > 4) per_sm = 4;
