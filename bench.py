@@ -437,6 +437,8 @@ def run_engine(args):
     fork_ev = [torch.cuda.Event() for _ in range(N_SLOTS)]
 
     def allreduce_async(g_cb, i=0):
+        if os.environ.get("RQ_BENCH_WHATIF_NO_EXCHANGE"):   # timing what-if only (tools/n2_variants.sh): the line is not a result
+            return
         if peer is not None:
             if peer_inline:
                 return                                  # already reduced inside the step (and its graph)
