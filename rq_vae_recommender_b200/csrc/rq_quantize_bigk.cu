@@ -146,8 +146,12 @@ static int quantize_forward_tc64_bigk_chunked(const FwdParams& p, cudaStream_t s
 //                            between levels, and the merge kernel and its [n_chunks, B] scratch are gone.
 namespace bigk {
 using namespace tc64;
-constexpr int STAGE_BYTES = B_TILE_BYTES + CC_TILE_BYTES;      // 40 KB: one chunk's operand images
-constexpr int N_STAGES = 3;
+// One chunk's operand images: [-2 t c] as fp16 hi and lo parts (two 32 KB tiles) + the ||c||^2 tile.  With the lo part
+// the product carries 22 bits of the codeword (error 3 * 2^-22 |t r||2 t c| instead of 2^-11): the scan's band shrinks
+// 25-fold and the re-scoring path, a fifth of the launch with hi-only images, all but disappears; 13 MMAs per chunk
+// instead of 9.
+constexpr int STAGE_BYTES = 2 * B_TILE_BYTES + CC_TILE_BYTES;  // 72 KB
+constexpr int N_STAGES = 2;
 constexpr int BIGK_MAX_L = 8;
 constexpr int SCRATCH_F32 = 64;                                // floats per warp: one parked row
 
@@ -224,14 +228,15 @@ __global__ void __launch_bounds__(1024) rq_bigk_prepare_kernel(BigkPrepParams q)
     for (int i = tid; i < Kp * 8; i += blockDim.x) {
         const int k = i >> 3, c8 = i & 7, ch = k >> 8, kk = k & 255;
         uint8_t* st = q.img + ((int64_t)l * q.n_chunks + ch) * STAGE_BYTES;
-        uint4 w = make_uint4(0, 0, 0, 0);
+        uint4 w = make_uint4(0, 0, 0, 0), wl = make_uint4(0, 0, 0, 0);
         if (k < q.K) {
             const float4* src = reinterpret_cast<const float4*>(cbl + (int64_t)k * D + c8 * 8);
             const float4 v0 = __ldg(src), v1 = __ldg(src + 1);
-            w.x = pack_h2(m2t * v0.x, m2t * v0.y); w.y = pack_h2(m2t * v0.z, m2t * v0.w);
-            w.z = pack_h2(m2t * v1.x, m2t * v1.y); w.w = pack_h2(m2t * v1.z, m2t * v1.w);
+            split_pair_h(m2t * v0.x, m2t * v0.y, w.x, wl.x); split_pair_h(m2t * v0.z, m2t * v0.w, w.y, wl.y);
+            split_pair_h(m2t * v1.x, m2t * v1.y, w.z, wl.z); split_pair_h(m2t * v1.z, m2t * v1.w, w.w, wl.w);
         }
         *reinterpret_cast<uint4*>(st + sw128_off(kk, c8)) = w;
+        *reinterpret_cast<uint4*>(st + B_TILE_BYTES + sw128_off(kk, c8)) = wl;
         if (c8 == 0) {
             uint4 c0 = make_uint4(0, 0, 0, 0);
             if (k < q.K) {
@@ -241,8 +246,8 @@ __global__ void __launch_bounds__(1024) rq_bigk_prepare_kernel(BigkPrepParams q)
             } else {
                 c0.x = pack_h2(60000.f, 0.f);                     // padding codes: larger than any real score, finite
             }
-            *reinterpret_cast<uint4*>(st + B_TILE_BYTES + nosw_off(kk, 0)) = c0;
-            *reinterpret_cast<uint4*>(st + B_TILE_BYTES + nosw_off(kk, 1)) = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4*>(st + 2 * B_TILE_BYTES + nosw_off(kk, 0)) = c0;
+            *reinterpret_cast<uint4*>(st + 2 * B_TILE_BYTES + nosw_off(kk, 1)) = make_uint4(0, 0, 0, 0);
         }
     }
 }
@@ -346,14 +351,15 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_bigk_kernel(Bigk
         ptx::tc_fence_after_sync();
         const uint32_t a0 = ptx::smem_u32(sAw), b0 = ptx::smem_u32(sStage + st * STAGE_BYTES);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            // i < 4: hi block, i >= 4: lo block; both against the same four K-steps of the B row
-            uint64_t ad = ptx::make_smem_desc(a0 + (i >> 2) * A_BLOCK_BYTES + (i & 3) * 32, 16, 1024, ptx::kLayoutSw128);
-            uint64_t bd = ptx::make_smem_desc(b0 + (i & 3) * 32, 16, 1024, ptx::kLayoutSw128);
+        for (int i = 0; i < 12; ++i) {
+            // (A block, B tile): hi.hi, lo.hi, hi.lo — four K-steps of 16 each
+            const int ab = (i >> 2) == 1, bb = (i >> 2) == 2;
+            uint64_t ad = ptx::make_smem_desc(a0 + ab * A_BLOCK_BYTES + (i & 3) * 32, 16, 1024, ptx::kLayoutSw128);
+            uint64_t bd = ptx::make_smem_desc(b0 + bb * B_TILE_BYTES + (i & 3) * 32, 16, 1024, ptx::kLayoutSw128);
             ptx::umma_bf16(tmem_acc, ad, bd, idesc, i > 0);         // kind::f16; the descriptor says fp16
         }
         uint64_t od = ptx::make_smem_desc(ptx::smem_u32(sOnes), 128, 256, ptx::kLayoutNone);
-        uint64_t cd = ptx::make_smem_desc(b0 + B_TILE_BYTES, 128, 256, ptx::kLayoutNone);
+        uint64_t cd = ptx::make_smem_desc(b0 + 2 * B_TILE_BYTES, 128, 256, ptx::kLayoutNone);
         ptx::umma_bf16(tmem_acc, od, cd, idesc, 1);
         ptx::umma_commit(&mbar_full[wg]);
     };
@@ -412,9 +418,13 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_bigk_kernel(Bigk
 #pragma unroll
                 for (int j = 0; j < D; j += 8) ptx::st_global_v8(p.res + off + j, &r[j]);
             }
-            // error of the accumulator in its own (scaled) units: see rq_fwd_tc64_kernel
+            // Error of the accumulator in its own (scaled) units, T = t r, C = -2 t c (|C| <= 2 tcm), both held as
+            // hi + lo fp16 pairs: |T - (Th + Tl)| <= 2^-22 |T|, |C - (Ch + Cl)| <= 2^-22 |C|, the dropped Tl.Cl term
+            // <= 2^-22 |T||C|: 3 * 2^-22 * 2 = 1.43e-6 |T| tcm, plus fp32 accumulation over 13 MMAs and the subnormal
+            // floors of the lo parts (the absolute terms, as in rq_fwd_tc64_kernel).  Winner and rival may both be off
+            // (2x); the factor below leaves a further 14x for the accumulation order of the tensor core.
             const float tcm = ts * sqrtf(s_cmax[l]);
-            const float tol = 1.07e-3f * trn * tcm + 2e-6f * trn + 8e-6f;
+            const float tol = 4e-5f * trn * tcm + 2e-6f * trn + 8e-6f;
             const float* cb_level = p.cb + (int64_t)l * p.K * D;
             float lead_lo = INFINITY, lead_hi = INFINITY, lead_d = 0.f;     // the leading chunk winner so far
             int lead_k = 0;

@@ -247,6 +247,14 @@ bool tc_supported(int D, int K, int L, int mode, int distance) {
     return tc32_supported(D, K, L, mode, distance) || tc64_supported(D, K, L, mode, distance);
 }
 int quantize_forward_tc(const FwdParams& p, int D, cudaStream_t st) {
+    // D = 64: the streamed-chunk kernel (rq_quantize_bigk.cu) also serves K <= 256 — one chunk per level, hi + lo fp16
+    // operand images from L2 instead of hi-only tiles resident in shared memory: 2.82 against 2.49 G items/s on the
+    // 4M-item ids-only tokenisation (tools/time_tok64.py), because the narrower band takes the re-scoring and its
+    // warpgroup-barrier stalls out.  rq_fwd_tc64_kernel remains as the chunk scorer of the L > 8 fallback
+    // (RQ_V_TC64_RESIDENT builds keep it as the K <= 256 kernel for A/B runs).
+#ifndef RQ_V_TC64_RESIDENT
+    if (D == 64) return quantize_forward_tc64_bigk(p, st);
+#endif
     return D == 64 ? quantize_forward_tc64(p, st) : quantize_forward_tc32(p, st);
 }
 
