@@ -223,6 +223,67 @@ static cudaError_t host_entry_alloc(void** p, size_t bytes, cudaStream_t st) {
     return pool ? cudaMallocFromPoolAsync(p, bytes, pool, st) : cudaMallocAsync(p, bytes, st);
 }
 
+// Side streams and events of the host entry: created once per device and reused (a call used to create and destroy
+// 2 streams + 7 events).  A second caller on the same device while the set is in use gets a fresh, temporary one.
+struct HostPlumbing {
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[2] = {}, ev_comp[2] = {}, ev_out[2] = {}, ev_start = nullptr;
+    bool cached = false;
+    cudaError_t create() {
+        cudaError_t e = cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming);
+        for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+            e = cudaEventCreateWithFlags(&ev_in[b], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_comp[b], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_out[b], cudaEventDisableTiming);
+        }
+        return e;
+    }
+    void destroy() {
+        for (int b = 0; b < 2; ++b) {
+            if (ev_in[b]) cudaEventDestroy(ev_in[b]);
+            if (ev_comp[b]) cudaEventDestroy(ev_comp[b]);
+            if (ev_out[b]) cudaEventDestroy(ev_out[b]);
+            ev_in[b] = ev_comp[b] = ev_out[b] = nullptr;
+        }
+        if (ev_start) cudaEventDestroy(ev_start);
+        if (s_in) cudaStreamDestroy(s_in);
+        if (s_out) cudaStreamDestroy(s_out);
+        ev_start = nullptr; s_in = s_out = nullptr;
+    }
+};
+static std::mutex g_plumbing_mu;
+static HostPlumbing g_plumbing[64];
+static bool g_plumbing_busy[64] = {};
+// returns the device's cached set when it is free (marks it busy), otherwise a temporary set; `e` reports creation errors
+static HostPlumbing acquire_plumbing(int dev, cudaError_t& e) {
+    e = cudaSuccess;
+    if (dev >= 0 && dev < 64) {
+        std::lock_guard<std::mutex> lk(g_plumbing_mu);
+        if (!g_plumbing_busy[dev]) {
+            if (!g_plumbing[dev].s_in) {
+                e = g_plumbing[dev].create();
+                if (e != cudaSuccess) { g_plumbing[dev].destroy(); HostPlumbing t; return t; }
+                g_plumbing[dev].cached = true;
+            }
+            g_plumbing_busy[dev] = true;
+            return g_plumbing[dev];
+        }
+    }
+    HostPlumbing t;
+    e = t.create();
+    return t;
+}
+static void release_plumbing(int dev, HostPlumbing& h) {
+    if (h.cached) {
+        std::lock_guard<std::mutex> lk(g_plumbing_mu);
+        g_plumbing_busy[dev] = false;
+    } else {
+        h.destroy();
+    }
+}
+
 extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B, int D, int K, int L,
                                     int distance, int64_t* ids_host, float* loss_host, int impl,
                                     rq_stream_t stream) {
@@ -238,19 +299,19 @@ extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks,
     float* dx[2] = {nullptr, nullptr};
     int64_t* dids[2] = {nullptr, nullptr};
     float* dloss[2] = {nullptr, nullptr};
-    cudaStream_t s_in = nullptr, s_out = nullptr;
-    cudaEvent_t ev_in[2] = {}, ev_comp[2] = {}, ev_out[2] = {}, ev_start = nullptr;
-    int rc = 0;
-    cudaError_t e = cudaSuccess;
+    int rc = 0, dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    cudaError_t e_pl = cudaSuccess;
+    HostPlumbing pl = acquire_plumbing(dev, e_pl);
+    if (e == cudaSuccess) e = e_pl;
+    cudaStream_t s_in = pl.s_in, s_out = pl.s_out;
+    cudaEvent_t* ev_in = pl.ev_in;
+    cudaEvent_t* ev_comp = pl.ev_comp;
+    cudaEvent_t* ev_out = pl.ev_out;
+    cudaEvent_t ev_start = pl.ev_start;
 #define HOST_TRY(call)                                                                        \
     do { if (rc == 0 && e == cudaSuccess) { e = (call); } } while (0)
-    HOST_TRY(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
-    HOST_TRY(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
-    HOST_TRY(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
     for (int b = 0; b < NB; ++b) {
-        HOST_TRY(cudaEventCreateWithFlags(&ev_in[b], cudaEventDisableTiming));
-        HOST_TRY(cudaEventCreateWithFlags(&ev_comp[b], cudaEventDisableTiming));
-        HOST_TRY(cudaEventCreateWithFlags(&ev_out[b], cudaEventDisableTiming));
         HOST_TRY(host_entry_alloc((void**)&dx[b], (size_t)C * D * sizeof(float), st));
         HOST_TRY(host_entry_alloc((void**)&dids[b], (size_t)L * C * sizeof(int64_t), st));
         if (loss_host) HOST_TRY(host_entry_alloc((void**)&dloss[b], (size_t)C * sizeof(float), st));
@@ -291,14 +352,7 @@ extern "C" int rq_semantic_ids_host(const float* x_host, const float* codebooks,
         if (dloss[b]) cudaFreeAsync(dloss[b], st);
     }
     cudaError_t e3 = cudaStreamSynchronize(st);
-    for (int b = 0; b < NB; ++b) {
-        if (ev_in[b]) cudaEventDestroy(ev_in[b]);
-        if (ev_comp[b]) cudaEventDestroy(ev_comp[b]);
-        if (ev_out[b]) cudaEventDestroy(ev_out[b]);
-    }
-    if (ev_start) cudaEventDestroy(ev_start);
-    if (s_in) cudaStreamDestroy(s_in);
-    if (s_out) cudaStreamDestroy(s_out);
+    release_plumbing(dev, pl);
     if (rc != 0) return rc;
     for (cudaError_t x : {e, e1, e2, e3})
         if (x != cudaSuccess) {

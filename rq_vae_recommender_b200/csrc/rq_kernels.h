@@ -80,6 +80,7 @@ int quantize_forward_tc32(const FwdParams& p, cudaStream_t st);
 bool tc64_supported(int D, int K, int L, int mode, int distance);
 int quantize_forward_tc64(const FwdParams& p, cudaStream_t st);
 int tc64_timeout_flag();
+int tc64_bigk_timeout_flag();
 // K > 256 at D = 64: level-major composition of the d=64 kernel over 256-code chunks (rq_quantize_bigk.cu)
 bool tc64_bigk_supported(int D, int K, int L, int mode, int distance);
 int quantize_forward_tc64_bigk(const FwdParams& p, cudaStream_t st);

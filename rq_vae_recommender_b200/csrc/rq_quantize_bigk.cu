@@ -621,6 +621,12 @@ __global__ void __launch_bounds__(tc64::THREADS, 1) rq_fwd_tc64_bigk_kernel(Bigk
 
 static int* d_err_bigk = nullptr;
 
+int tc64_bigk_timeout_flag() {
+    int v = 0;
+    if (d_err_bigk) cudaMemcpy(&v, d_err_bigk, sizeof(int), cudaMemcpyDeviceToHost);
+    return v;
+}
+
 int quantize_forward_tc64_bigk(const FwdParams& p, cudaStream_t st) {
     using namespace bigk;
     if (p.B == 0) return 0;

@@ -336,3 +336,30 @@ def test_peer_allreduce_two_ranks():
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "ok=True timeout_flag=0" in r.stdout
 
+
+
+def test_kmeans_fixed_point_accumulation_outliers_and_specials():
+    """rq_kmeans_accumulate_fx_kernel: components far outside the fixed-point range (outliers 1e7 x the centroid scale),
+    +-Inf and NaN take the floating-point path, so sums equal a float64 index_add where that is finite and propagate
+    Inf / NaN exactly where it is not; tiny components do not vanish; a row count that is not a multiple of 8."""
+    g = torch.Generator().manual_seed(3)
+    B, D, K = 50003, 32, 256
+    x = torch.randn(B, D, generator=g)
+    x[::97] *= 1e7                                  # outliers
+    x[5::1013] *= 1e-6                              # far below one fixed-point step: must still be accumulated to within it
+    c = torch.randn(K, D, generator=g)
+    xd, cd = x.to(DEV), c.to(DEV)
+    a, sums, counts, _ = RF.kmeans_assign_accumulate(xd, cd, impl=RF.IMPL_TCGEN05)
+    want = torch.zeros(K, D, dtype=torch.float64, device=DEV).index_add_(0, a, xd.double())
+    assert torch.equal(counts, torch.bincount(a, minlength=K))
+    assert_close(sums.cpu(), want.cpu(), "sums with outliers", tol=1e-5)
+    x2 = x.clone()
+    x2[11, 3] = float("inf"); x2[12, 4] = float("-inf"); x2[13, 5] = float("nan")
+    xd2 = x2.to(DEV)
+    a2, sums2, counts2, _ = RF.kmeans_assign_accumulate(xd2, cd, a.clone(), impl=RF.IMPL_TCGEN05)
+    want2 = torch.zeros(K, D, dtype=torch.float64, device=DEV).index_add_(0, a2, xd2.double())
+    fin = torch.isfinite(want2)
+    assert torch.equal(torch.isnan(sums2), torch.isnan(want2))
+    assert torch.equal(torch.isinf(sums2), torch.isinf(want2))
+    assert_close(torch.where(fin, sums2.double(), torch.zeros_like(want2)).cpu(),
+                 torch.where(fin, want2, torch.zeros_like(want2)).cpu(), "finite sums", tol=1e-5)

@@ -182,3 +182,50 @@ def test_tc64_bigk_ids_bit_identical_to_simt(B, K, L):
                                       want_loss=False, impl=RF.IMPL_TCGEN05)
     _, _, i1, _ = RF.quantize_forward(xd, cd, RF.MODE_EVAL, impl=RF.IMPL_SIMT)
     assert torch.equal(i1, i3)
+
+
+@pytest.mark.parametrize("B,K,L", [(70001, 700, 8), (129, 300, 5), (33000, 256, 3)])
+def test_tc64_streamed_kernel_shapes(B, K, L):
+    """The streamed-chunk kernel at shapes the round-1 tests did not reach: 8 levels, a partial last chunk, an odd
+    number of row tiles (the second warpgroup's last tile is empty), and K <= 256 (one chunk per level: since round 2
+    every D = 64 tcgen05 launch goes through this kernel)."""
+    x, cbs = _inputs(B, K, L, seed=B % 1000 + K + 11, D=64)
+    xd, cd = x.to(DEV), torch.stack(cbs).to(DEV)
+    e1, r1, i1, l1 = RF.quantize_forward(xd, cd, RF.MODE_ROTATION_TRICK, impl=RF.IMPL_SIMT)
+    e2, r2, i2, l2 = RF.quantize_forward(xd, cd, RF.MODE_ROTATION_TRICK, impl=RF.IMPL_TCGEN05)
+    torch.cuda.synchronize()
+    assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+    assert int((i1 != i2).sum()) == 0
+    assert_close(e2, e1, "emb", tol=1e-6)
+    assert_close(r2, r1, "res", tol=1e-6)
+    assert_close(l2, l1, "loss", tol=1e-6)
+
+
+def test_tc64_streamed_kernel_ties_across_chunks():
+    """The merge over the chunks of a level: exact duplicates of a code in later chunks (the lowest index must win, as
+    in the reference's first-index argmin, quantize.py:121), codes that differ from a code of another chunk in the last
+    bits (settled by the exact fp32 distances), rows that sit exactly on a codeword, and a row scale that sends the
+    scores of different chunks close together."""
+    g = torch.Generator().manual_seed(5)
+    D, K, L, B = 64, 1024, 2, 6000
+    base = torch.randn(256, D, generator=g)
+    cb0 = torch.cat([base,                                        # chunk 0
+                     base.clone(),                                # chunk 1: exact duplicates of chunk 0
+                     base * (1 + 1e-7) + 1e-8,                    # chunk 2: last-bit neighbours
+                     torch.randn(256, D, generator=g)])           # chunk 3: unrelated
+    cb0[512 + 7] = base[7]                                        # one exact duplicate inside the near-tie chunk
+    cb1 = torch.cat([torch.randn(512, D, generator=g) * 0.3, torch.zeros(256, D), torch.randn(256, D, generator=g) * 0.3])
+    cbs = torch.stack([cb0, cb1])
+    x = torch.randn(B, D, generator=g)
+    x[:256] = base                                                # rows on a codeword (distance 0 in three chunks)
+    x[256:512] = 0.5 * (base + cb0[768:1024])                     # bisectors between chunk 0 / 1 / 2 codes and chunk 3
+    x[512:600] = 0.0
+    xd, cd = x.to(DEV), cbs.to(DEV)
+    for mode in (RF.MODE_EVAL, RF.MODE_ROTATION_TRICK):
+        _, _, i1, _ = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_SIMT)
+        _, _, i2, _ = RF.quantize_forward(xd, cd, mode, impl=RF.IMPL_TCGEN05)
+        torch.cuda.synchronize()
+        assert _lib.lib().rq_debug_tc_timeout_flag() == 0
+        assert int((i1 != i2).sum()) == 0
+    # chunk 1 holds bit-identical copies of chunk 0: their exact distances are equal, so the copy can never be chosen
+    assert int(((i2[0] >= 256) & (i2[0] < 512)).sum()) == 0
