@@ -22,6 +22,10 @@ struct FwdParams {
     // stored at ids[] (all rows when !has_prev).  nullptr = off.
     unsigned long long* n_changed = nullptr;
     int has_prev = 0;
+    // k-means accumulation fused into the assignment (d = 32 tcgen05 kernel, L = 1, ids only): per-cluster sums [K, D]
+    // and counts [K] of the rows the launch serves (whole 128-row tiles), added into caller-zeroed buffers.  nullptr = off.
+    float* km_sums = nullptr;
+    unsigned long long* km_counts = nullptr;
     // optional [B]: exact fp32 distance (SIMT arithmetic) of the id chosen at the LAST level — lets a caller merge
     // the winners of several codebook chunks (rq_quantize_bigk.cu).  nullptr = off.  tcgen05 d=64 family only.
     float* best_dist = nullptr;

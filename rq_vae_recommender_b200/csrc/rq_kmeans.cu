@@ -346,8 +346,24 @@ int kmeans_assign_accumulate_tc(const KmeansParams& p, int D, cudaStream_t st) {
     f.beta = 0.f; f.temp = 1.f; f.gu = nullptr; f.seed = 0; f.offset = 0;
     f.emb = nullptr; f.res = nullptr; f.ids = p.assign; f.loss = nullptr; f.KC = 0;
     f.n_changed = p.n_changed; f.has_prev = p.has_prev;
+    // D = 32, K <= 256: the accumulation rides in the assignment launch (the rows are in shared memory when their id is
+    // known); only the last B % 128 rows, which that launch hands to the exact family, go through the stand-alone kernel
+    const bool fuse = (D == 32) && p.K <= 256 && p.B >= 128 && (p.B >> 20) < (int64_t)sm_count();
+    if (fuse) {
+        f.km_sums = p.sums;
+        f.km_counts = p.counts;
+    }
     int rc = quantize_forward_tc(f, D, st);
     if (rc) return rc;
+    if (fuse) {
+        const int64_t done = (p.B / 128) * 128;
+        if (done == p.B) return 0;
+        KmeansParams t = p;
+        t.x = p.x + done * D;
+        t.assign = p.assign + done;
+        t.B = p.B - done;
+        return launch_kmeans_accumulate<32>(t, st);
+    }
     if (D == 32) return launch_kmeans_accumulate<32>(p, st);
     if (D == 64) return launch_kmeans_accumulate<64>(p, st);
     set_error("kmeans tensor-core path: D=%d not served", D);

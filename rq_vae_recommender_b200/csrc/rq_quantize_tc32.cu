@@ -38,9 +38,11 @@ constexpr int MAX_L = 3;
 constexpr int R_TILE_BYTES = TILE_M * 128;   // [128 rows][32 fp32], SW128
 
 struct SmemLayout {
-    int b_tiles, a_tiles, r_tiles, cc_tiles, ones, cc_f32, misc, total;
+    int b_tiles, a_tiles, r_tiles, cc_tiles, ones, cc_f32, misc, km, total;
 };
-__host__ __device__ inline SmemLayout smem_layout(int L) {
+// km: room for the k-means partial sums of the fused assignment + accumulation launch (L = 1): two int32 pieces per
+// (cluster, component) + a count per cluster
+__host__ __device__ inline SmemLayout smem_layout(int L, bool km = false) {
     SmemLayout s;
     int off = 0;
     s.b_tiles = off; off += L * B_TILE_BYTES;
@@ -50,6 +52,7 @@ __host__ __device__ inline SmemLayout smem_layout(int L) {
     s.ones = off; off += ONES_TILE_BYTES;
     s.cc_f32 = off; off += L * KC * 4;
     s.misc = off; off += 256;
+    s.km = off; off += km ? (2 * KC * D + KC) * 4 : 0;
     s.total = off;
     return s;
 }
@@ -79,14 +82,14 @@ __host__ __device__ inline SmemLayout smem_layout(int L) {
 #define RQ_CTA_STAMP(slot_, val_) do {} while (0)
 #endif
 
-template <int MODE>
+template <int MODE, bool KM = false>
 __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams P) {
     using namespace tc32;
     const FwdParams& p = P.f;
     extern __shared__ uint8_t smem_raw[];
     // 128B-swizzled UMMA tiles need 1024-byte alignment; the launch over-allocates by 1 KB
     uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
-    const SmemLayout S = smem_layout(p.L);
+    const SmemLayout S = smem_layout(p.L, KM);
     uint8_t* sB = smem + S.b_tiles;
     uint8_t* sA = smem + S.a_tiles;
     uint8_t* sR = smem + S.r_tiles;
@@ -172,6 +175,10 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
             *reinterpret_cast<uint4*>(sOnes + nosw_off(rr, c)) = v;
         }
         ptx::fence_proxy_async_smem();
+    }
+    if (KM) {                                          // k-means partials start at zero
+        int* km = reinterpret_cast<int*>(smem + S.km);
+        for (int i = tid; i < 2 * KC * D + KC; i += THREADS) km[i] = 0;
     }
     __syncthreads();                                   // barrier inits, cmax zeros, ones tile
     if (warp == 9) {
@@ -439,6 +446,45 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
             const bool last = (l == p.L - 1);
             // ids-only launches (tokenisation, k-means assignment) need nothing past the id at the last level
             if (last && ids_only) {
+                if (KM) {
+                    // ---- k-means: the tile's rows are still in the residual tile and their ids are known — add them
+                    // to the CTA's partial sums here instead of reading x a second time.  Fixed point on the integer
+                    // unit as in rq_kmeans_accumulate_fx_kernel (rq_kmeans.cu): the warp takes its 32 rows one at a
+                    // time, lane l component l (one conflict-free LDS, two conflict-free reductions per row), the counts
+                    // are one reduction for the 32 rows.  range = 2^e >= 16 max||c||.
+                    const uint32_t km_hi = ptx::smem_u32(smem + S.km) + lane * 4;
+                    const uint32_t km_lo = km_hi + KC * D * 4;
+                    const uint32_t km_cnt = ptx::smem_u32(smem + S.km) + 2 * KC * D * 4;
+                    int e2 = (int)((__float_as_uint(fast_sqrt(cmax2)) >> 23) & 0xffu) + 5;
+                    e2 = e2 < 30 ? 30 : (e2 > 220 ? 220 : e2);
+                    const float S_fx = 4194304.f / __uint_as_float((unsigned)e2 << 23);
+                    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(km_cnt + (uint32_t)bi * 4u), "r"(1u) : "memory");
+                    bool bad = false;
+                    const uint8_t* rows = sRw + wrow0 * 128 + (lane & 3) * 4;
+#pragma unroll 8
+                    for (int t = 0; t < 32; ++t) {
+                        const int k = __shfl_sync(0xffffffffu, bi, t);
+                        const float v = *reinterpret_cast<const float*>(rows + (t >> 3) * 1024 + (t & 7) * 128 +
+                                                                        (((lane >> 2) ^ (t & 7)) << 4));
+                        const float sc = v * S_fx;
+                        const bool ok = fabsf(sc) < 4194304.f;
+                        const int f = ok ? (__float_as_int(sc + 12582912.f) - 0x4B400000) : 0;
+                        const uint32_t off = (uint32_t)k * (D * 4);
+                        asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(km_hi + off), "r"(f >> 11) : "memory");
+                        asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(km_lo + off), "r"(f & 0x7ff) : "memory");
+                        bad |= !ok;
+                    }
+                    if (__any_sync(0xffffffffu, bad)) {        // rare: components outside the fixed-point range
+#pragma unroll 1
+                        for (int t = 0; t < 32; ++t) {
+                            const int k = __shfl_sync(0xffffffffu, bi, t);
+                            const float v = *reinterpret_cast<const float*>(rows + (t >> 3) * 1024 + (t & 7) * 128 +
+                                                                            (((lane >> 2) ^ (t & 7)) << 4));
+                            if (!(fabsf(v * S_fx) < 4194304.f)) atomicAdd(p.km_sums + k * D + lane, v);
+                        }
+                    }
+                    __syncwarp();                               // every lane has read the rows: the tile may be refilled
+                }
                 if (it + 1 < n_mine) prefetch_x(tile_of(it + 1));       // the residual tile is free (__syncwarp above)
                 continue;
             }
@@ -551,6 +597,21 @@ __global__ void __launch_bounds__(tc32::THREADS, 1) rq_fwd_tc32_kernel(TcParams 
     ptx::tc_fence_before_sync();
     __syncthreads();
     if (warp == 9) ptx::tmem_dealloc(tmem_base, 512);
+    if (KM) {                                           // the CTA's partials: one float reduction per (cluster, component)
+        const int* km = reinterpret_cast<const int*>(smem + S.km);
+        const float cm2 = __int_as_float(*reinterpret_cast<volatile int*>(&cmax_bits[0]));
+        int e2 = (int)((__float_as_uint(fast_sqrt(cm2)) >> 23) & 0xffu) + 5;
+        e2 = e2 < 30 ? 30 : (e2 > 220 ? 220 : e2);
+        const double inv = (double)__uint_as_float((unsigned)e2 << 23) / 4194304.0;
+        for (int i = tid; i < p.K * D; i += THREADS) {
+            const long long tot = (long long)km[i] * 2048 + (long long)km[KC * D + i];
+            if (tot != 0) atomicAdd(p.km_sums + i, (float)((double)tot * inv));
+        }
+        for (int k = tid; k < p.K; k += THREADS) {
+            const unsigned c = (unsigned)km[2 * KC * D + k];
+            if (c) atomicAdd(p.km_counts + k, (unsigned long long)c);
+        }
+    }
     RQ_CTA_STAMP(2, ptx::globaltimer());
 }
 
@@ -589,9 +650,20 @@ int quantize_forward_tc32_fused(const FwdParams& p, cudaStream_t st) {
         P.dbg_flags = getenv("RQ_TC_WHATIF") ? atoi(getenv("RQ_TC_WHATIF")) : 0;    // experiments build only
 #endif
         P.n_tiles = (int)n_tiles;
-        const tc32::SmemLayout S = tc32::smem_layout(p.L);
+        const bool km = p.km_sums != nullptr;
+        const tc32::SmemLayout S = tc32::smem_layout(p.L, km);
         const int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
         const size_t smem = (size_t)S.total + 1024;
+        if (km) {
+            // fused k-means assignment + accumulation: single level, ids only (the caller checked), 2^20 rows per CTA at most
+            if (p.L != 1 || p.emb || p.res || p.loss || !p.km_counts || smem > (size_t)tc::kMaxSmem ||
+                (int64_t)P.n_tiles * tc::TILE_M > (int64_t)grid << 20) {
+                set_error("fused k-means accumulation: unsupported launch shape");
+                return RQ_ERR_UNSUPPORTED_SHAPE;
+            }
+            RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_fwd_tc32_kernel<RQ_MODE_EVAL, true>, tc::kMaxSmem));
+            RQ_CUDA(launch_pdl(rq_fwd_tc32_kernel<RQ_MODE_EVAL, true>, dim3(grid), dim3(tc32::THREADS), smem, st, P));
+        } else
         switch (p.mode) {
             case RQ_MODE_ROTATION_TRICK:
                 RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_fwd_tc32_kernel<RQ_MODE_ROTATION_TRICK>, tc::kMaxSmem));
