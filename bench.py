@@ -589,12 +589,15 @@ def run_engine(args):
         b.record()
         return a, b
 
+    local_block_ms = []                                 # this rank's own device time of every timed block
+
     def timed_block(fn):
         """EXACTLY K steps bracketed by barrier + synchronize on both sides; device time of the block, max over ranks."""
         fence()
         a, b = timed(fn, args.steps)
         fence()
         t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+        local_block_ms.append(float(t[0]))
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t[0])
@@ -619,6 +622,14 @@ def run_engine(args):
     l0 = R.launch_count()
     with ClockSampler(local) as clk:
         ms_total, timing = timed_blocks(run_step)
+        # how far apart the ranks are: each rank's own median block (the reported time is the max over ranks per block)
+        mine = sorted(local_block_ms)[len(local_block_ms) // 2]
+        if world > 1:
+            allm = torch.zeros(world, dtype=torch.float64, device=dev)
+            allm[rank] = mine
+            dist.all_reduce(allm)
+            timing["per_rank_us_per_step_median"] = [round(float(v) * 1e3 / args.steps, 2) for v in allm]
+        local_block_ms.clear()
         # the dominant kernels on their own, same ring, same clocks window (roofline legs)
         fwd_block, _ = timed_blocks(run_fwd)
         bwd_block, _ = timed_blocks(run_bwd)
