@@ -229,3 +229,31 @@ def test_tc64_streamed_kernel_ties_across_chunks():
         assert int((i1 != i2).sum()) == 0
     # chunk 1 holds bit-identical copies of chunk 0: their exact distances are equal, so the copy can never be chosen
     assert int(((i2[0] >= 256) & (i2[0] < 512)).sum()) == 0
+
+
+@pytest.mark.parametrize("K,L", [(256, 3), (1024, 4)])
+def test_tc64_streamed_kernel_in_cuda_graph(K, L):
+    """The D = 64 path allocates its operand-image scratch from the library's stream-ordered pool: captured into a CUDA
+    graph (allocation and free become graph nodes) the replays must equal eager launches on the same inputs."""
+    g = torch.Generator(device=DEV).manual_seed(K + L)
+    D, B = 64, 20000
+    cb = torch.stack([torch.randn(K, D, device=DEV, generator=g) * (0.6 ** l) for l in range(L)])
+    xs = torch.randn(B, D, device=DEV, generator=g)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        RF.quantize_forward(xs, cb, RF.MODE_ROTATION_TRICK, 0.25, 0.2)
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = RF.quantize_forward(xs, cb, RF.MODE_ROTATION_TRICK, 0.25, 0.2)
+    for _ in range(2):
+        x2 = torch.randn(B, D, device=DEV, generator=g)
+        xs.copy_(x2)
+        graph.replay()
+        torch.cuda.synchronize()
+        ref = RF.quantize_forward(x2, cb, RF.MODE_ROTATION_TRICK, 0.25, 0.2)
+        for a, b in zip(out, ref):
+            assert torch.equal(a, b)
+    assert _lib.lib().rq_debug_tc_timeout_flag() == 0
