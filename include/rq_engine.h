@@ -237,6 +237,12 @@ int rq_debug_tc_set_accumulator_dump(float* device_buf_128x256);
  * phases (prologue end, then per level: operand written, MMAs issued, accumulator ready, scan done,
  * level done) on subsequent launches (NULL disables). */
 int rq_debug_tc_set_timeline(long long* device_buf_32x64);
+/* Test hook: the fp32-grade tensor-core GEMM of the Gumbel-softmax path on its own (csrc/rq_gemm_split.cu):
+ * C[M, N] (+)= alpha * A[M, Kd] * B[N, Kd]^T, fp32 row-major device buffers with row strides lda / ldb / ldc (floats;
+ * lda, ldb multiples of 4, A and B 16-byte aligned).  atomic != 0 or k_splits > 1 adds into C with float atomics.
+ * Stands where the reference calls torch.matmul inside the Gumbel branch (modules/quantize.py:125-128 and its autograd). */
+int rq_debug_split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda,
+                        int64_t ldb, int64_t ldc, float alpha, int atomic, int k_splits, rq_stream_t stream);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

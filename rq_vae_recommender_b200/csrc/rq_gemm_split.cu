@@ -1,0 +1,228 @@
+// fp32-grade GEMM on the 5th-gen tensor cores: C[M, N] (+)= alpha * A[M, Kd] * B[N, Kd]^T, all operands fp32 row-major
+// with the contraction index contiguous ("K-major").  Used by the Gumbel-softmax path (rq_gumbel_tc.cu), whose softmax
+// needs logits at fp32 accuracy: every fp32 value v is cut into three bf16 planes v = v1 + v2 + v3 (8 + 8 + 8 significand
+// bits, both remainders exact in fp32) while its tile is staged into shared memory, and the product is the six bf16 MMAs
+// a1.b1 + a1.b2 + a2.b1 + a2.b2 + a1.b3 + a3.b1 accumulated in fp32 in TMEM: the dropped terms are below 2^-24 |a||b|,
+// i.e. the result is as good as an fp32 FMA chain (tests/test_gpu_gumbel.py checks it against float64).
+//
+// One CTA per 128 x NT output tile (and per K split): 256 threads stage a 64-wide K-block of A and B (global fp32 ->
+// registers -> three 128-byte-swizzled bf16 tiles each), one thread issues the 24 tcgen05.mma of the block, the next
+// block is staged when those have completed (single-buffered: the callers are bound by the [M, N] traffic to HBM or run
+// a handful of K-blocks per CTA).  Epilogue: TMEM -> registers -> 32-byte global stores, or float atomics for split-K.
+#include "rq_common.cuh"
+#include "rq_kernels.h"
+#include "rq_tc_ptx.cuh"
+
+namespace rq {
+
+namespace sg {
+constexpr int TM = 128;           // rows per tile (UMMA M)
+constexpr int KB = 64;            // contraction elements per staged block (one 128-byte swizzled bf16 row)
+constexpr int THREADS = 256;
+__device__ __forceinline__ uint32_t sw128_off(int r, int c) {
+    return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+}
+// three bf16 planes of four consecutive fp32 values: 8 bytes per plane
+__device__ __forceinline__ void split3_store(const float4& v, uint8_t* p1, uint8_t* p2, uint8_t* p3) {
+    const uint32_t h01 = ptx::pack_bf16x2(v.x, v.y), h23 = ptx::pack_bf16x2(v.z, v.w);
+    const float r0 = v.x - __uint_as_float(h01 << 16), r1 = v.y - __uint_as_float(h01 & 0xFFFF0000u);
+    const float r2 = v.z - __uint_as_float(h23 << 16), r3 = v.w - __uint_as_float(h23 & 0xFFFF0000u);
+    const uint32_t m01 = ptx::pack_bf16x2(r0, r1), m23 = ptx::pack_bf16x2(r2, r3);
+    const float s0 = r0 - __uint_as_float(m01 << 16), s1 = r1 - __uint_as_float(m01 & 0xFFFF0000u);
+    const float s2 = r2 - __uint_as_float(m23 << 16), s3 = r3 - __uint_as_float(m23 & 0xFFFF0000u);
+    const uint32_t l01 = ptx::pack_bf16x2(s0, s1), l23 = ptx::pack_bf16x2(s2, s3);
+    *reinterpret_cast<uint2*>(p1) = make_uint2(h01, h23);
+    *reinterpret_cast<uint2*>(p2) = make_uint2(m01, m23);
+    *reinterpret_cast<uint2*>(p3) = make_uint2(l01, l23);
+}
+}  // namespace sg
+
+struct SplitGemmParams {
+    const float* A;      // [M, Kd], row stride lda
+    const float* B;      // [N, Kd], row stride ldb
+    float* C;            // [M, N], row stride ldc
+    int64_t M, N, Kd, lda, ldb, ldc;
+    float alpha;
+    int atomic;          // 1: C += alpha * A B^T with float atomics (split-K, or accumulation into a live buffer)
+    int kb_per_split;    // K-blocks per blockIdx.z
+};
+
+template <int NT>
+__global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemmParams g) {
+    using namespace sg;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+    constexpr int A_PLANE = TM * 128, B_PLANE = NT * 128;
+    uint8_t* sA = smem;                           // [3][128 rows][64 bf16]
+    uint8_t* sB = smem + 3 * A_PLANE;             // [3][NT rows][64 bf16]
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 3 * A_PLANE + 3 * B_PLANE);
+    uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(mbar + 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t m0 = (int64_t)blockIdx.x * TM, n0 = (int64_t)blockIdx.y * NT;
+    const int64_t n_kb = (g.Kd + KB - 1) / KB;
+    const int64_t kb0 = (int64_t)blockIdx.z * g.kb_per_split;
+    const int64_t kb1 = (kb0 + g.kb_per_split < n_kb) ? kb0 + g.kb_per_split : n_kb;
+    if (kb0 >= kb1) return;
+
+    if (tid == 0) {
+        ptx::mbar_init(mbar, 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 1) ptx::tmem_alloc(tmem_base_s, NT < 32 ? 32 : NT);
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem_acc = *reinterpret_cast<volatile uint32_t*>(tmem_base_s);
+    // kind::f16 instruction descriptor, bf16 x bf16 -> fp32, K-major operands
+    const uint32_t idesc = ptx::make_idesc_bf16_f32(TM, NT);
+    bool timed_out = false;
+
+    for (int64_t kb = kb0; kb < kb1; ++kb) {
+        if (kb > kb0) {                                            // the tiles are still being read by the last block's MMAs
+            if (!ptx::mbar_wait(mbar, (uint32_t)((kb - kb0 - 1) & 1))) timed_out = true;
+            ptx::tc_fence_after_sync();
+        }
+        const int64_t k0 = kb * KB;
+        // ---- stage: 16 float4 per row, a warp reads two rows' 256 contiguous bytes per instruction ----------------------
+        for (int i = tid; i < TM * 16; i += THREADS) {
+            const int r = i >> 4, c4 = i & 15;
+            const int64_t row = m0 + r, k = k0 + c4 * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row < g.M) {
+                const float* src = g.A + row * g.lda + k;
+                if (k + 3 < g.Kd) v = __ldg(reinterpret_cast<const float4*>(src));
+                else {
+                    if (k < g.Kd) v.x = __ldg(src);
+                    if (k + 1 < g.Kd) v.y = __ldg(src + 1);
+                    if (k + 2 < g.Kd) v.z = __ldg(src + 2);
+                }
+            }
+            const uint32_t o = sw128_off(r, c4 >> 1) + (c4 & 1) * 8;
+            split3_store(v, sA + o, sA + A_PLANE + o, sA + 2 * A_PLANE + o);
+        }
+        for (int i = tid; i < NT * 16; i += THREADS) {
+            const int r = i >> 4, c4 = i & 15;
+            const int64_t row = n0 + r, k = k0 + c4 * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row < g.N) {
+                const float* src = g.B + row * g.ldb + k;
+                if (k + 3 < g.Kd) v = __ldg(reinterpret_cast<const float4*>(src));
+                else {
+                    if (k < g.Kd) v.x = __ldg(src);
+                    if (k + 1 < g.Kd) v.y = __ldg(src + 1);
+                    if (k + 2 < g.Kd) v.z = __ldg(src + 2);
+                }
+            }
+            const uint32_t o = sw128_off(r, c4 >> 1) + (c4 & 1) * 8;
+            split3_store(v, sB + o, sB + B_PLANE + o, sB + 2 * B_PLANE + o);
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::tc_fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            ptx::tc_fence_after_sync();
+            const uint32_t a0 = ptx::smem_u32(sA), b0 = ptx::smem_u32(sB);
+            // (A plane, B plane) of the six kept terms, smallest first: the tensor core's fp32 accumulation truncates, so
+            // the small corrections are summed among themselves before the leading product comes in
+            const int pa[6] = {2, 0, 1, 1, 0, 0};
+            const int pb[6] = {0, 2, 1, 0, 1, 0};
+#pragma unroll
+            for (int t = 0; t < 6; ++t) {
+#pragma unroll
+                for (int s = 0; s < 4; ++s) {                      // four K = 16 steps of 32 bytes
+                    const uint64_t ad = ptx::make_smem_desc(a0 + pa[t] * A_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
+                    const uint64_t bd = ptx::make_smem_desc(b0 + pb[t] * B_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
+                    ptx::umma_bf16(tmem_acc, ad, bd, idesc, (kb > kb0 || t > 0 || s > 0) ? 1u : 0u);
+                }
+            }
+            ptx::umma_commit(mbar);
+        }
+    }
+    if (!ptx::mbar_wait(mbar, (uint32_t)((kb1 - kb0 - 1) & 1))) timed_out = true;
+    ptx::tc_fence_after_sync();
+
+    // ---- epilogue: warp w reads TMEM lanes 32 (w & 3) .., columns of half (w >> 2) ----------------------------------------
+    {
+        const int q = warp & 3, h = warp >> 2;
+        const int64_t row = m0 + q * 32 + lane;
+        constexpr int HALF = NT / 2;
+        const uint32_t trow = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * HALF);
+#pragma unroll 1
+        for (int c = 0; c < HALF; c += 32) {
+            uint32_t v[32];
+            ptx::tmem_ld_32x32b_x32(trow + c, v);
+            ptx::tmem_ld_wait_for(v);
+            if (row < g.M) {
+                float* dst = g.C + row * g.ldc + n0 + h * HALF + c;
+                const int64_t ncol = g.N - (n0 + h * HALF + c);        // columns left in this row
+                if (!g.atomic && ncol >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 31) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        float o[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) o[u] = g.alpha * __uint_as_float(v[j + u]);
+                        ptx::st_global_v8(dst + j, o);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (j < ncol) {
+                            const float o = g.alpha * __uint_as_float(v[j]);
+                            if (g.atomic) atomicAdd(dst + j, o);
+                            else dst[j] = o;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    (void)timed_out;
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc(tmem_acc, NT < 32 ? 32 : NT);
+}
+
+// C[M, N] (+)= alpha * A[M, Kd] * B[N, Kd]^T.  k_splits > 1 (or atomic) accumulates with float atomics into C, which the
+// caller has initialised.  Rows of A and B must be 16-byte aligned (lda, ldb multiples of 4 floats).
+int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda, int64_t ldb,
+               int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st) {
+    if (M <= 0 || N <= 0 || Kd <= 0) return 0;
+    if ((lda & 3) || (ldb & 3) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) {
+        set_error("split_gemm: operand rows must be 16-byte aligned");
+        return RQ_ERR_INVALID_ARGUMENT;
+    }
+    SplitGemmParams g;
+    g.A = A; g.B = B; g.C = C; g.M = M; g.N = N; g.Kd = Kd; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+    g.alpha = alpha;
+    const int64_t n_kb = (Kd + sg::KB - 1) / sg::KB;
+    if (k_splits < 1) k_splits = 1;
+    if (k_splits > n_kb) k_splits = (int)n_kb;
+    g.kb_per_split = (int)((n_kb + k_splits - 1) / k_splits);
+    k_splits = (int)((n_kb + g.kb_per_split - 1) / g.kb_per_split);
+    g.atomic = (atomic || k_splits > 1) ? 1 : 0;
+    const unsigned gm = (unsigned)((M + sg::TM - 1) / sg::TM);
+    if (N > 64) {
+        constexpr int NT = 256;
+        const size_t smem = 3 * sg::TM * 128 + 3 * NT * 128 + 64 + 1024;
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_kernel<NT>, (int)smem));
+        dim3 grid(gm, (unsigned)((N + NT - 1) / NT), (unsigned)k_splits);
+        rq_split_gemm_kernel<NT><<<grid, sg::THREADS, smem, st>>>(g);
+    } else {
+        constexpr int NT = 64;
+        const size_t smem = 3 * sg::TM * 128 + 3 * NT * 128 + 64 + 1024;
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_kernel<NT>, (int)smem));
+        dim3 grid(gm, 1, (unsigned)k_splits);
+        rq_split_gemm_kernel<NT><<<grid, sg::THREADS, smem, st>>>(g);
+    }
+    RQ_LAUNCHED();
+    return 0;
+}
+
+}  // namespace rq
+
+// Test hook: the split-precision GEMM on its own (tests/test_gpu_gumbel.py compares it with float64).
+extern "C" int rq_debug_split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd,
+                                   int64_t lda, int64_t ldb, int64_t ldc, float alpha, int atomic, int k_splits,
+                                   rq_stream_t stream) {
+    return rq::split_gemm(A, B, C, M, N, Kd, lda, ldb, ldc, alpha, atomic, k_splits, (cudaStream_t)stream);
+}
