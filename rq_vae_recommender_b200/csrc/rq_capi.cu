@@ -77,6 +77,7 @@ extern "C" const char* rq_last_error(void) { return g_err; }
 extern "C" uint64_t rq_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int rq_tcgen05_supported(int D, int K, int L, int mode, int distance) {
+    if (mode == RQ_MODE_GUMBEL_SOFTMAX) return gumbel_tc_supported(D, K, L, distance) ? 1 : 0;
     return (tc_supported(D, K, L, mode, distance) || tc64_bigk_supported(D, K, L, mode, distance)) ? 1 : 0;
 }
 
@@ -102,6 +103,11 @@ extern "C" int rq_quantize_forward(const float* x, const float* codebooks, int64
     // the tcgen05 family stages the codebooks with TMA bulk copies (16-byte aligned source rows)
     const bool aligned = (((uintptr_t)codebooks & 15) == 0) && (((uintptr_t)x & 31) == 0);
     const bool tc_ok = tc_supported(D, K, L, mode, distance) && aligned;
+    // Gumbel-softmax: GEMM-shaped contractions on the tensor cores (rq_gumbel_tc.cu) once the batch is worth the
+    // [B, K] scratch; the thread-per-row family below serves small batches and the shapes outside D in {32, 64}
+    if (mode == RQ_MODE_GUMBEL_SOFTMAX && gumbel_tc_supported(D, K, L, distance) && (((uintptr_t)x & 15) == 0) &&
+        (((uintptr_t)codebooks & 15) == 0) && (impl == RQ_IMPL_TCGEN05 || (impl == RQ_IMPL_AUTO && B >= 4096)))
+        return quantize_forward_gumbel_tc(p, D, st);
     if (tc64_bigk_supported(D, K, L, mode, distance) && aligned && (impl == RQ_IMPL_TCGEN05 || (impl == RQ_IMPL_AUTO && B >= 2048)))
         return quantize_forward_tc64_bigk(p, st);
     if (impl == RQ_IMPL_TCGEN05) {

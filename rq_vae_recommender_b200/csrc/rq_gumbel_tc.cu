@@ -1,0 +1,241 @@
+// Gumbel-softmax estimator on the tensor cores (modules/quantize.py:124-129 + distributions/gumbel.py:7-17 of the
+// reference, and their autograd): level by level, the two GEMM-shaped contractions of the forward — x C^T and W C —
+// and the five of the backward run as fp32-grade tcgen05 products (rq_gemm_split.cu: three bf16 planes per value), the
+// [B, K] logits / weights live in one scratch matrix that the row kernels below rewrite in place, and the ids come
+// from the exact distance kernels of the other modes (one single-level ids-only launch per level).  The CUDA-core
+// family (rq_quantize_simt.cu / rq_gumbel_bwd.cu: one thread per row, 4 K D FMAs per row and level) stays as the
+// small-batch path and as the yardstick of the tests.
+//
+//   forward, per level     ids   = argmin dist(r, C)                         exact kernel, L = 1
+//                          S     = r C^T                                     GEMM  [B, D] x [K, D]^T
+//                          W     = softmax((-(|r|^2 + |c|^2 - 2 S) + g) / T) rows, in place; g from the given uniforms
+//                                                                            or the SIMT family's Philox counters
+//                          emb   = W C                                       GEMM  [B, K] x [D, K]^T
+//                          loss += (1 + beta) |r - emb|^2,  r <- r - emb      rows
+//   backward, per level (top down, G = d objective / d r_{l+1})
+//                          S, W, emb as above (recomputed from the saved residual)
+//                          de    = g_emb - G + 2 (emb - x) g_loss,  t = de . emb
+//                          dW    = de C^T                                    GEMM  [B, D] x [K, D]^T
+//                          dd    = -W (dW - t) / T   (in place), and W^T, dd^T for the codebook gradient
+//                          v     = dd C                                      GEMM  [B, K] x [D, K]^T
+//                          g_C  += W^T de - 2 dd^T x + 2 C * colsum(dd)       GEMMs [K, B] x [D, B]^T, split over B
+//                          G     = G + 2 beta (x - emb) g_loss + g_res - 2 v  (the 2 x sum_k dd_k term is zero: the rows
+//                                                                            of a softmax Jacobian sum to nothing)
+#include "rq_common.cuh"
+#include "rq_kernels.h"
+#include "rq_rowmath.cuh"
+
+namespace rq {
+
+int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda, int64_t ldb,
+               int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st);
+
+namespace gtc {
+
+// ||c||^2 in the canonical order of code_sqnorm, and C^T ([D, Kp], zero padded) for the GEMMs whose contraction runs
+// over the codes.  One thread per code.
+template <int D>
+__global__ void __launch_bounds__(256) codebook_prep_kernel(const float* __restrict__ cb, int K, int Kp, float* __restrict__ cc,
+                                                            float* __restrict__ ct) {
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    if (k >= Kp) return;
+    if (k < K) {
+        cc[k] = code_sqnorm<D>(cb + (int64_t)k * D);
+#pragma unroll 4
+        for (int j = 0; j < D; ++j) ct[(int64_t)j * Kp + k] = __ldg(cb + (int64_t)k * D + j);
+    } else {
+        cc[k] = 0.f;
+        for (int j = 0; j < D; ++j) ct[(int64_t)j * Kp + k] = 0.f;
+    }
+}
+
+struct RowParams {
+    float* S;            // [B, Kp]: in: r C^T, out: softmax weights
+    const float* r;      // [B, D] this level's residual
+    const float* cc;     // [Kp]
+    const float* gu;     // [B, K] this level's uniforms or nullptr (Philox)
+    int64_t B;
+    int K, Kp, level;
+    float inv_t;
+    uint64_t seed, offset;
+};
+
+// One warp per row, a lane owns the codes 4 (lane + 32 i) .. + 3: float4 accesses (512 contiguous bytes per warp
+// instruction) and one Philox call per four codes, with the SIMT family's counters (row, code / 4, level).
+template <int D>
+__global__ void __launch_bounds__(256) gumbel_softmax_rows_kernel(RowParams q) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= q.B) return;
+    // |r|^2, canonical chunk order (rq_rowmath.cuh): D / 8 chunks over the first lanes, combined by a balanced tree
+    float xx;
+    {
+        float part = 0.f;
+        if (lane < D / 8) {
+            float v[8];
+            const float4 a = __ldg(reinterpret_cast<const float4*>(q.r + row * D + lane * 8));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(q.r + row * D + lane * 8 + 4));
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+            part = chunk_dot<8>(v, v);
+        }
+#pragma unroll
+        for (int o = 1; o < D / 8; o <<= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        xx = __shfl_sync(0xffffffffu, part, 0);
+    }
+    float* Srow = q.S + row * q.Kp;
+    const float* gurow = q.gu ? q.gu + row * q.K : nullptr;
+    // pass 1: logits in place, row maximum
+    float m = -INFINITY;
+    for (int k = lane * 4; k < q.Kp; k += 128) {
+        float4 s = *reinterpret_cast<const float4*>(Srow + k);
+        const float4 c = __ldg(reinterpret_cast<const float4*>(q.cc + k));
+        float u[4];
+        if (gurow) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) u[t] = (k + t < q.K) ? __ldg(gurow + k + t) : 0.5f;
+        } else {
+            const uint4 rnd = philox4x32_10(make_uint4((uint32_t)row, (uint32_t)(row >> 32), (uint32_t)(k >> 2), (uint32_t)q.level),
+                                            make_uint2((uint32_t)(q.seed ^ q.offset), (uint32_t)((q.seed >> 32) ^ (q.offset >> 32))));
+            u[0] = u01(rnd.x); u[1] = u01(rnd.y); u[2] = u01(rnd.z); u[3] = u01(rnd.w);
+        }
+        float y[4];
+        const float sv[4] = {s.x, s.y, s.z, s.w}, cv[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const float d = (xx + cv[t]) - 2.f * sv[t];                       // quantize.py:108-112
+            y[t] = (k + t < q.K) ? (-d + gumbel_from_u(u[t])) * q.inv_t : -INFINITY;
+            m = fmaxf(m, y[t]);
+        }
+        *reinterpret_cast<float4*>(Srow + k) = make_float4(y[0], y[1], y[2], y[3]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    // pass 2: exp, row sum
+    float sum = 0.f;
+    for (int k = lane * 4; k < q.Kp; k += 128) {
+        float4 y = *reinterpret_cast<const float4*>(Srow + k);
+        y.x = __expf(y.x - m); y.y = __expf(y.y - m); y.z = __expf(y.z - m); y.w = __expf(y.w - m);
+        sum += (y.x + y.y) + (y.z + y.w);
+        *reinterpret_cast<float4*>(Srow + k) = y;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float inv = 1.0f / sum;
+    // pass 3: normalise (the row is L1 / L2 resident)
+    for (int k = lane * 4; k < q.Kp; k += 128) {
+        float4 y = *reinterpret_cast<const float4*>(Srow + k);
+        y.x *= inv; y.y *= inv; y.z *= inv; y.w *= inv;
+        *reinterpret_cast<float4*>(Srow + k) = y;
+    }
+}
+
+struct TailParams {
+    const float* r;      // [B, D]
+    const float* emb;    // [B, D]
+    float* res_out;      // [B, D] or nullptr: this level's residual output
+    float* r_next;       // [B, D] or nullptr
+    float* loss;         // [B] or nullptr
+    int64_t B;
+    float beta;
+    int first;
+};
+
+// D / 4 lanes per row, float4 each: the level's residual output, loss term and next residual (rqvae.py:126-129)
+template <int D>
+__global__ void __launch_bounds__(256) gumbel_level_tail_kernel(TailParams q) {
+    constexpr int LPR = D / 4;
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int64_t row = i / LPR;
+    const bool active = row < q.B;
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f), e = r;
+    if (active) {
+        r = __ldg(reinterpret_cast<const float4*>(q.r) + i);
+        e = __ldg(reinterpret_cast<const float4*>(q.emb) + i);
+    }
+    const float t0 = r.x - e.x, t1 = r.y - e.y, t2 = r.z - e.z, t3 = r.w - e.w;
+    float dsq = fmaf(t0, t0, fmaf(t1, t1, fmaf(t2, t2, t3 * t3)));
+#pragma unroll
+    for (int o = 1; o < LPR; o <<= 1) dsq += __shfl_xor_sync(0xffffffffu, dsq, o);
+    if (!active) return;
+    if (q.res_out) reinterpret_cast<float4*>(q.res_out)[i] = r;
+    if (q.r_next) reinterpret_cast<float4*>(q.r_next)[i] = make_float4(t0, t1, t2, t3);
+    if (q.loss && (i % LPR) == 0) {
+        const float lvl = dsq + q.beta * dsq;                                    // loss.py:40-42
+        q.loss[row] = q.first ? lvl : q.loss[row] + lvl;
+    }
+}
+
+}  // namespace gtc
+
+bool gumbel_tc_supported(int D, int K, int L, int distance) {
+    return (D == 32 || D == 64) && K >= 4 && L >= 1 && distance == RQ_DIST_L2;
+}
+
+template <int D>
+static int gumbel_forward_tc_impl(const FwdParams& p, cudaStream_t st) {
+    using namespace gtc;
+    const int64_t B = p.B;
+    const int K = p.K, Kp = (K + 3) & ~3;
+    const size_t bytes_S = (size_t)B * Kp * 4, bytes_row = (size_t)B * D * 4;
+    const size_t bytes_ct = (size_t)D * Kp * 4, bytes_cc = (size_t)Kp * 4;
+    // scratch: S | r ping | r pong | emb (when the caller wants none) | C^T | cc
+    const size_t total = bytes_S + 2 * bytes_row + (p.emb ? 0 : bytes_row) + bytes_ct + bytes_cc + 256;
+    uint8_t* scratch = (uint8_t*)engine_pool_alloc(total, st);
+    if (!scratch) {
+        set_error("rq_quantize_forward: out of device memory for the Gumbel-softmax scratch (%zu bytes)", total);
+        return (int)cudaErrorMemoryAllocation;
+    }
+    float* S = (float*)scratch;
+    float* rbuf[2] = {(float*)(scratch + bytes_S), (float*)(scratch + bytes_S + bytes_row)};
+    uint8_t* cur = scratch + bytes_S + 2 * bytes_row;
+    float* emb_scratch = nullptr;
+    if (!p.emb) { emb_scratch = (float*)cur; cur += bytes_row; }
+    float* ct = (float*)cur; cur += bytes_ct;
+    float* cc = (float*)cur;
+    int rc = 0;
+    const float* r_in = p.x;
+    for (int l = 0; l < p.L && rc == 0; ++l) {
+        const float* cbl = p.cb + (int64_t)l * K * D;
+        float* emb_l = p.emb ? p.emb + (int64_t)l * B * D : emb_scratch;
+        {   // ids: the exact single-level distance kernel on this level's residual (quantize.py:121)
+            FwdParams q;
+            q.x = r_in; q.cb = cbl; q.B = B; q.K = K; q.L = 1; q.mode = RQ_MODE_EVAL; q.dist = RQ_DIST_L2;
+            q.beta = p.beta; q.temp = 1.f; q.gu = nullptr; q.seed = 0; q.offset = 0;
+            q.emb = nullptr; q.res = nullptr; q.loss = nullptr; q.KC = 0;
+            q.ids = p.ids + (int64_t)l * B;
+            const bool aligned = (((uintptr_t)cbl & 15) == 0) && (((uintptr_t)r_in & 31) == 0);
+            if (aligned && (tc_supported(D, K, 1, RQ_MODE_EVAL, RQ_DIST_L2) || tc64_bigk_supported(D, K, 1, RQ_MODE_EVAL, RQ_DIST_L2)))
+                rc = quantize_forward_tc(q, D, st);
+            else
+                rc = quantize_forward_simt(q, D, st);
+            if (rc) break;
+        }
+        codebook_prep_kernel<D><<<(Kp + 255) / 256, 256, 0, st>>>(cbl, K, Kp, cc, ct);
+        RQ_LAUNCHED();
+        rc = split_gemm(r_in, cbl, S, B, K, D, D, D, Kp, 1.f, 0, 1, st);
+        if (rc) break;
+        RowParams q;
+        q.S = S; q.r = r_in; q.cc = cc; q.gu = p.gu ? p.gu + (int64_t)l * B * K : nullptr;
+        q.B = B; q.K = K; q.Kp = Kp; q.level = l; q.inv_t = 1.0f / p.temp; q.seed = p.seed; q.offset = p.offset;
+        gumbel_softmax_rows_kernel<D><<<(unsigned)((B + 7) / 8), 256, 0, st>>>(q);
+        RQ_LAUNCHED();
+        rc = split_gemm(S, ct, emb_l, B, D, K, Kp, Kp, D, 1.f, 0, 1, st);
+        if (rc) break;
+        TailParams t;
+        t.r = r_in; t.emb = emb_l; t.res_out = p.res ? p.res + (int64_t)l * B * D : nullptr;
+        t.r_next = (l + 1 < p.L) ? rbuf[l & 1] : nullptr;
+        t.loss = p.loss; t.B = B; t.beta = p.beta; t.first = (l == 0);
+        gumbel_level_tail_kernel<D><<<(unsigned)((B * (D / 4) + 255) / 256), 256, 0, st>>>(t);
+        RQ_LAUNCHED();
+        r_in = t.r_next;
+    }
+    cudaFreeAsync(scratch, st);
+    return rc;
+}
+
+int quantize_forward_gumbel_tc(const FwdParams& p, int D, cudaStream_t st) {
+    if (p.B == 0) return 0;
+    return D == 64 ? gumbel_forward_tc_impl<64>(p, st) : gumbel_forward_tc_impl<32>(p, st);
+}
+
+}  // namespace rq

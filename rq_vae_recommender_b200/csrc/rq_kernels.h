@@ -87,6 +87,9 @@ int tc64_timeout_flag();
 int tc64_bigk_timeout_flag();
 // K > 256 at D = 64: level-major composition of the d=64 kernel over 256-code chunks (rq_quantize_bigk.cu)
 bool tc64_bigk_supported(int D, int K, int L, int mode, int distance);
+// Gumbel-softmax on the tensor cores (rq_gumbel_tc.cu)
+bool gumbel_tc_supported(int D, int K, int L, int distance);
+int quantize_forward_gumbel_tc(const FwdParams& p, int D, cudaStream_t st);
 int quantize_forward_tc64_bigk(const FwdParams& p, cudaStream_t st);
 void* engine_pool_alloc(size_t bytes, cudaStream_t st);     // library-owned stream-ordered pool (rq_capi.cu)
 

@@ -100,3 +100,27 @@ def test_gumbel_philox_noise_is_reproduced_by_the_backward():
     gx2, gc2 = RF.quantize_backward(g_emb, None, g_loss, r2, i2, cbs, RF.MODE_GUMBEL_SOFTMAX, 0.25, T, gumbel_uniform=u)
     assert_close(gx1.cpu(), gx2.cpu(), "philox backward g_x", tol=1e-4)
     assert_close(gc1.cpu(), gc2.cpu(), "philox backward g_codebooks", tol=1e-4)
+
+
+# ---- tensor-core path (rq_gumbel_tc.cu) against the thread-per-row family, same C ABI, impl switch -----------------
+@pytest.mark.parametrize("B,D,K,L", [(5000, 64, 1024, 4), (4097, 32, 256, 3), (700, 64, 300, 2), (3000, 32, 1000, 2)])
+@pytest.mark.parametrize("noise", ["given", "philox"])
+def test_gumbel_forward_tensor_core_vs_simt(B, D, K, L, noise):
+    g = torch.Generator().manual_seed(B + K)
+    x = torch.randn(B, D, generator=g)
+    cbs = torch.stack(synthetic_codebooks(torch.randn(max(4 * K, 2048), D, generator=g), L, K, seed=3))
+    gu = torch.rand(L, B, K, generator=g).to(DEV) if noise == "given" else None
+    xd, cd = x.to(DEV), cbs.to(DEV)
+    kw = dict(gumbel_uniform=gu, seed=11, offset=5)
+    e1, r1, i1, l1 = RF.quantize_forward(xd, cd, RF.MODE_GUMBEL_SOFTMAX, 0.25, 0.2, impl=RF.IMPL_SIMT, **kw)
+    e2, r2, i2, l2 = RF.quantize_forward(xd, cd, RF.MODE_GUMBEL_SOFTMAX, 0.25, 0.2, impl=RF.IMPL_TCGEN05, **kw)
+    torch.cuda.synchronize()
+    # ids: both are exact argmins of the same fp32 distances, up to the summation order of |r|^2 + |c|^2 - 2 r.c
+    assert float((i1 != i2).float().mean()) < 1e-3
+    assert_close(e2, e1, "emb", tol=2e-4)
+    assert_close(r2, r1, "res", tol=2e-4)
+    assert_close(l2, l1, "loss", tol=2e-4)
+    # without the outputs a caller may not want
+    _, _, i3, _ = RF.quantize_forward(xd, cd, RF.MODE_GUMBEL_SOFTMAX, 0.25, 0.2, impl=RF.IMPL_TCGEN05,
+                                      want_embeddings=False, want_residuals=False, want_loss=False, **kw)
+    assert torch.equal(i3, i2)

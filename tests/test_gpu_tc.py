@@ -24,7 +24,8 @@ def test_tc_is_selected_for_the_headline_shape():
     assert _lib.lib().rq_tcgen05_supported(64, 256, 3, RF.MODE_EVAL, RF.DIST_L2) == 1      # ml32m shape
     assert _lib.lib().rq_tcgen05_supported(64, 256, 4, RF.MODE_EVAL, RF.DIST_L2) == 1      # level-major composition
     assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_ROTATION_TRICK, RF.DIST_L2) == 1   # config 5 shape
-    assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_GUMBEL_SOFTMAX, RF.DIST_L2) == 0
+    assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_GUMBEL_SOFTMAX, RF.DIST_L2) == 1   # rq_gumbel_tc.cu
+    assert _lib.lib().rq_tcgen05_supported(64, 1024, 4, RF.MODE_GUMBEL_SOFTMAX, RF.DIST_COSINE) == 0
     assert _lib.lib().rq_tcgen05_supported(32, 256, 3, RF.MODE_EVAL, RF.DIST_COSINE) == 0
 
 
