@@ -101,6 +101,7 @@ int rq_quantize_backward(const float* g_emb, const float* g_res, const float* g_
  * the stream so that programmatic dependent launch can overlap this kernel's launch with the forward's tail).
  * Honoured by the EVAL / STE / ROTATION_TRICK modes; GUMBEL_SOFTMAX overwrites. */
 #define RQ_BWD_ACCUMULATE 1
+#define RQ_BWD_THREAD_PER_ROW 2   /* Gumbel-softmax: keep the CUDA-core kernel whatever the batch size (A/B, tests) */
 int rq_quantize_backward_ex(const float* g_emb, const float* g_res, const float* g_loss,
                             const float* residuals, const int64_t* ids, const float* codebooks,
                             int64_t B, int D, int K, int L, int mode, float beta, float temperature,

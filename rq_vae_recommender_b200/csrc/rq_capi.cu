@@ -149,6 +149,13 @@ extern "C" int rq_quantize_backward_ex(const float* g_emb, const float* g_res, c
     cudaStream_t st = (cudaStream_t)stream;
     if (mode == RQ_MODE_GUMBEL_SOFTMAX) {
         RQ_CHECK_ARG(temperature > 0.f, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_backward: temperature must be > 0");
+        // the tensor-core path once the batch is worth its [B, K] scratch (as in the forward); RQ_BWD_THREAD_PER_ROW
+        // keeps the CUDA-core kernel (tests compare the two)
+        const bool ptr_ok = (((uintptr_t)residuals & 15) == 0) && (((uintptr_t)codebooks & 15) == 0) &&
+                            (!g_emb || ((uintptr_t)g_emb & 15) == 0) && (!g_res || ((uintptr_t)g_res & 15) == 0) &&
+                            (((uintptr_t)g_x & 15) == 0);
+        if (!(flags & RQ_BWD_THREAD_PER_ROW) && B >= 4096 && gumbel_tc_supported(D, K, L, RQ_DIST_L2) && ptr_ok)
+            return quantize_backward_gumbel_tc(p, D, temperature, gumbel_u, seed, offset, st);
         return quantize_backward_gumbel(p, D, temperature, gumbel_u, seed, offset, st);
     }
     return quantize_backward_simt(p, D, st);

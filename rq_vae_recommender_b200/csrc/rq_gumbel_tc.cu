@@ -165,6 +165,115 @@ __global__ void __launch_bounds__(256) gumbel_level_tail_kernel(TailParams q) {
     }
 }
 
+
+// ---- backward row kernels ---------------------------------------------------------------------------------------------
+struct DeParams {
+    const float* x;       // [B, D] saved residual of the level
+    const float* emb;     // [B, D] W C
+    const float* g_emb;   // [B, D] or nullptr
+    const float* g_res;   // [B, D] or nullptr
+    const float* g_loss;  // [B] or nullptr
+    float* G;             // [B, D] in: d objective / d r_{l+1}; out: G + 2 beta (x - emb) g_loss + g_res
+    float* de;            // [B, D] out
+    float* t;             // [B] out: de . emb
+    int64_t B;
+    float beta;
+};
+template <int D>
+__global__ void __launch_bounds__(256) gumbel_de_kernel(DeParams q) {
+    constexpr int LPR = D / 4;
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int64_t row = i / LPR;
+    const bool active = row < q.B;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f), e = x, ge = x, gr = x, G = x;
+    float gl = 0.f;
+    if (active) {
+        x = __ldg(reinterpret_cast<const float4*>(q.x) + i);
+        e = __ldg(reinterpret_cast<const float4*>(q.emb) + i);
+        if (q.g_emb) ge = __ldg(reinterpret_cast<const float4*>(q.g_emb) + i);
+        if (q.g_res) gr = __ldg(reinterpret_cast<const float4*>(q.g_res) + i);
+        G = reinterpret_cast<const float4*>(q.G)[i];
+        if (q.g_loss) gl = __ldg(q.g_loss + row);
+    }
+    float4 de;
+    de.x = (ge.x - G.x) + 2.f * (e.x - x.x) * gl; de.y = (ge.y - G.y) + 2.f * (e.y - x.y) * gl;
+    de.z = (ge.z - G.z) + 2.f * (e.z - x.z) * gl; de.w = (ge.w - G.w) + 2.f * (e.w - x.w) * gl;
+    float t = fmaf(de.x, e.x, fmaf(de.y, e.y, fmaf(de.z, e.z, de.w * e.w)));
+#pragma unroll
+    for (int o = 1; o < LPR; o <<= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (!active) return;
+    const float b2 = 2.f * q.beta * gl;
+    G.x += b2 * (x.x - e.x) + gr.x; G.y += b2 * (x.y - e.y) + gr.y;
+    G.z += b2 * (x.z - e.z) + gr.z; G.w += b2 * (x.w - e.w) + gr.w;
+    reinterpret_cast<float4*>(q.G)[i] = G;
+    reinterpret_cast<float4*>(q.de)[i] = de;
+    if ((i % LPR) == 0) q.t[row] = t;
+}
+
+// dd = -W (dW - t) / T, in place over dW; one warp per row
+__global__ void __launch_bounds__(256) gumbel_dd_rows_kernel(const float* __restrict__ W, float* __restrict__ dW,
+                                                             const float* __restrict__ t, int64_t B, int Kp, float inv_t) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= B) return;
+    const float tr = __ldg(t + row);
+    const float4* w4 = reinterpret_cast<const float4*>(W + row * Kp);
+    float4* d4 = reinterpret_cast<float4*>(dW + row * Kp);
+    for (int k = lane; k < Kp / 4; k += 32) {
+        const float4 w = __ldg(w4 + k);
+        float4 d = d4[k];
+        d.x = -(w.x * (d.x - tr)) * inv_t; d.y = -(w.y * (d.y - tr)) * inv_t;
+        d.z = -(w.z * (d.z - tr)) * inv_t; d.w = -(w.w * (d.w - tr)) * inv_t;
+        d4[k] = d;
+    }
+}
+
+// dst[c, r] = src[r, c] through 32 x 32 shared-memory tiles (src [R, C] row stride lds, dst [C, R] row stride ldd;
+// the columns r >= R of dst up to ldd are left untouched: the caller zeroes the padding once)
+__global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t R,
+                                                        int64_t C, int64_t lds, int64_t ldd) {
+    __shared__ float tile[32][33];
+    const int64_t r0 = (int64_t)blockIdx.x * 32, c0 = (int64_t)blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+        const int64_t r = r0 + ty + j, c = c0 + tx;
+        tile[ty + j][tx] = (r < R && c < C) ? __ldg(src + r * lds + c) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+        const int64_t c = c0 + ty + j, r = r0 + tx;
+        if (c < C && r < R) dst[c * ldd + r] = tile[tx][ty + j];
+    }
+}
+
+// g_C[k, :] += 2 C[k, :] * sum_b ddT[k, b]; one warp per code
+template <int D>
+__global__ void __launch_bounds__(256) gumbel_colsum_kernel(const float* __restrict__ ddt, int64_t B, int64_t ldb, int K,
+                                                            const float* __restrict__ cb, float* __restrict__ g_cb) {
+    const int lane = threadIdx.x & 31;
+    const int k = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (k >= K) return;
+    float s = 0.f;
+    for (int64_t b = lane; b < B; b += 32) s += __ldg(ddt + (int64_t)k * ldb + b);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int j = lane; j < D; j += 32) atomicAdd(g_cb + (int64_t)k * D + j, 2.f * __ldg(cb + (int64_t)k * D + j) * s);
+}
+
+// G <- G - 2 v (and g_x on the last level processed)
+__global__ void __launch_bounds__(256) gumbel_g_update_kernel(float* __restrict__ G, const float* __restrict__ v, int64_t n4,
+                                                              float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n4) return;
+    float4 g = reinterpret_cast<float4*>(G)[i];
+    const float4 w = __ldg(reinterpret_cast<const float4*>(v) + i);
+    g.x -= 2.f * w.x; g.y -= 2.f * w.y; g.z -= 2.f * w.z; g.w -= 2.f * w.w;
+    reinterpret_cast<float4*>(G)[i] = g;
+    if (out) reinterpret_cast<float4*>(out)[i] = g;
+}
+
 }  // namespace gtc
 
 bool gumbel_tc_supported(int D, int K, int L, int distance) {
@@ -236,6 +345,112 @@ static int gumbel_forward_tc_impl(const FwdParams& p, cudaStream_t st) {
 int quantize_forward_gumbel_tc(const FwdParams& p, int D, cudaStream_t st) {
     if (p.B == 0) return 0;
     return D == 64 ? gumbel_forward_tc_impl<64>(p, st) : gumbel_forward_tc_impl<32>(p, st);
+}
+
+template <int D>
+static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const float* gu, uint64_t seed, uint64_t offset,
+                                   cudaStream_t st) {
+    using namespace gtc;
+    const int64_t B = p.B, Bp = (B + 3) & ~(int64_t)3;
+    const int K = p.K, Kp = (K + 3) & ~3;
+    const size_t bytes_S = (size_t)B * Kp * 4, bytes_T = (size_t)K * Bp * 4, bytes_row = (size_t)B * D * 4;
+    const size_t bytes_rt = (size_t)D * Bp * 4, bytes_ct = (size_t)D * Kp * 4, bytes_cc = (size_t)Kp * 4;
+    // scratch: W | dW/dd | W^T | dd^T | emb | de | v | G | de^T | x^T | C^T | cc | t
+    const size_t total = 2 * bytes_S + 2 * bytes_T + 4 * bytes_row + 2 * bytes_rt + bytes_ct + bytes_cc + (size_t)B * 4 + 256;
+    uint8_t* scratch = (uint8_t*)engine_pool_alloc(total, st);
+    if (!scratch) {
+        set_error("rq_quantize_backward: out of device memory for the Gumbel-softmax scratch (%zu bytes)", total);
+        return (int)cudaErrorMemoryAllocation;
+    }
+    uint8_t* cur = scratch;
+    auto take = [&](size_t n) { float* q = (float*)cur; cur += n; return q; };
+    float* W = take(bytes_S);
+    float* dd = take(bytes_S);
+    float* Wt = take(bytes_T);
+    float* ddt = take(bytes_T);
+    float* emb = take(bytes_row);
+    float* de = take(bytes_row);
+    float* v = take(bytes_row);
+    float* G = take(bytes_row);
+    float* det = take(bytes_rt);
+    float* xt = take(bytes_rt);
+    float* ct = take(bytes_ct);
+    float* cc = take(bytes_cc);
+    float* t = take((size_t)B * 4);
+    int rc = 0;
+#define GTC_CUDA(call)                                                                   \
+    do { if (rc == 0) { cudaError_t e_ = (call); if (e_ != cudaSuccess) { set_error("rq_quantize_backward: %s", cudaGetErrorString(e_)); rc = (int)e_; } } } while (0)
+    GTC_CUDA(cudaMemsetAsync(G, 0, bytes_row, st));
+    // the padding columns b >= B of the transposed operands are read by the GEMMs' 16-byte loads: keep them zero
+    if (Bp != B) {
+        GTC_CUDA(cudaMemsetAsync(Wt, 0, 2 * bytes_T, st));
+        GTC_CUDA(cudaMemsetAsync(det, 0, 2 * bytes_rt, st));
+    }
+    GTC_CUDA(cudaMemsetAsync(p.g_cb, 0, (size_t)p.L * K * D * sizeof(float), st));      // this mode overwrites (rq_engine.h)
+    const unsigned rows8 = (unsigned)((B + 7) / 8), rowsq = (unsigned)((B * (D / 4) + 255) / 256);
+    const int64_t n_kb = (B + 63) / 64;
+    int splits = (int)((2 * (int64_t)sm_count() * 128 + K - 1) / K);          // ~2 CTAs per SM over the [K, D] output tiles
+    if (splits < 1) splits = 1;
+    if (splits > n_kb) splits = (int)n_kb;
+    for (int l = p.L - 1; l >= 0 && rc == 0; --l) {
+        const float* cbl = p.cb + (int64_t)l * K * D;
+        const float* x = p.res + (int64_t)l * B * D;
+        float* gcb = p.g_cb + (int64_t)l * K * D;
+        codebook_prep_kernel<D><<<(Kp + 255) / 256, 256, 0, st>>>(cbl, K, Kp, cc, ct);
+        RQ_LAUNCHED();
+        // forward recomputation: W and emb
+        if ((rc = split_gemm(x, cbl, W, B, K, D, D, D, Kp, 1.f, 0, 1, st))) break;
+        RowParams q;
+        q.S = W; q.r = x; q.cc = cc; q.gu = gu ? gu + (int64_t)l * B * K : nullptr;
+        q.B = B; q.K = K; q.Kp = Kp; q.level = l; q.inv_t = 1.0f / temperature; q.seed = seed; q.offset = offset;
+        gumbel_softmax_rows_kernel<D><<<rows8, 256, 0, st>>>(q);
+        RQ_LAUNCHED();
+        if ((rc = split_gemm(W, ct, emb, B, D, K, Kp, Kp, D, 1.f, 0, 1, st))) break;
+        // de, t, and the part of G that does not depend on the codes
+        DeParams dq;
+        dq.x = x; dq.emb = emb;
+        dq.g_emb = p.g_emb ? p.g_emb + (int64_t)l * B * D : nullptr;
+        dq.g_res = p.g_res ? p.g_res + (int64_t)l * B * D : nullptr;
+        dq.g_loss = p.g_loss; dq.G = G; dq.de = de; dq.t = t; dq.B = B; dq.beta = p.beta;
+        gumbel_de_kernel<D><<<rowsq, 256, 0, st>>>(dq);
+        RQ_LAUNCHED();
+        // dW = de C^T, dd in place
+        if ((rc = split_gemm(de, cbl, dd, B, K, D, D, D, Kp, 1.f, 0, 1, st))) break;
+        gumbel_dd_rows_kernel<<<rows8, 256, 0, st>>>(W, dd, t, B, Kp, 1.0f / temperature);
+        RQ_LAUNCHED();
+        // v = dd C
+        if ((rc = split_gemm(dd, ct, v, B, D, K, Kp, Kp, D, 1.f, 0, 1, st))) break;
+        // codebook gradient: W^T de - 2 dd^T x + 2 C colsum(dd), contraction over the rows
+        {
+            dim3 gT((unsigned)((B + 31) / 32), (unsigned)((K + 31) / 32));
+            transpose_kernel<<<gT, 256, 0, st>>>(W, Wt, B, K, Kp, Bp);
+            transpose_kernel<<<gT, 256, 0, st>>>(dd, ddt, B, K, Kp, Bp);
+            dim3 gR((unsigned)((B + 31) / 32), (unsigned)((D + 31) / 32));
+            transpose_kernel<<<gR, 256, 0, st>>>(de, det, B, D, D, Bp);
+            transpose_kernel<<<gR, 256, 0, st>>>(x, xt, B, D, D, Bp);
+            RQ_LAUNCHED();
+        }
+        if ((rc = split_gemm(Wt, det, gcb, K, D, B, Bp, Bp, D, 1.f, 1, splits, st))) break;
+        if ((rc = split_gemm(ddt, xt, gcb, K, D, B, Bp, Bp, D, -2.f, 1, splits, st))) break;
+        gumbel_colsum_kernel<D><<<(K + 7) / 8, 256, 0, st>>>(ddt, B, Bp, K, cbl, gcb);
+        RQ_LAUNCHED();
+        // G = G + ... - 2 v; the last level processed writes g_x
+        gumbel_g_update_kernel<<<rowsq, 256, 0, st>>>(G, v, B * (D / 4), l == 0 ? p.g_x : nullptr);
+        RQ_LAUNCHED();
+    }
+#undef GTC_CUDA
+    cudaFreeAsync(scratch, st);
+    return rc;
+}
+
+int quantize_backward_gumbel_tc(const BwdParams& p, int D, float temperature, const float* gu, uint64_t seed,
+                                uint64_t offset, cudaStream_t st) {
+    if (p.B == 0) {
+        RQ_CUDA(cudaMemsetAsync(p.g_cb, 0, (size_t)p.L * p.K * D * sizeof(float), st));
+        return 0;
+    }
+    return D == 64 ? gumbel_backward_tc_impl<64>(p, temperature, gu, seed, offset, st)
+                   : gumbel_backward_tc_impl<32>(p, temperature, gu, seed, offset, st);
 }
 
 }  // namespace rq

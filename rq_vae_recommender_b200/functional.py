@@ -62,7 +62,7 @@ def quantize_forward(x: torch.Tensor, codebooks: torch.Tensor, mode: int = MODE_
 def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, beta, temperature,
                       gumbel_uniform=None, seed: int = 0, offset: int = 0,
                       g_codebooks_out: Optional[torch.Tensor] = None,
-                      accumulate: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+                      accumulate: bool = False, thread_per_row: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
     """rq_quantize_backward: returns (g_x [B,D], g_codebooks [L,K,D]).  `g_codebooks_out` (contiguous fp32
     [L,K,D]) receives the codebook gradient in place — e.g. a persistent all-reduce bucket.  `accumulate=True` adds
     to what `g_codebooks_out` holds instead of overwriting it (gradient accumulation; with a buffer zeroed BEFORE the
@@ -92,7 +92,8 @@ def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, bet
         rc = L.lib().rq_quantize_backward_ex(L.ptr(g_emb), L.ptr(g_res), L.ptr(g_loss), L.ptr(residuals), L.ptr(ids),
                                              L.ptr(codebooks), B, D, K, Lv, int(mode), float(beta), float(temperature),
                                              L.ptr(gumbel_uniform), int(seed), int(offset), L.ptr(g_x), L.ptr(g_cb),
-                                             1 if accumulate else 0, L.stream_of(residuals))
+                                             (1 if accumulate else 0) | (2 if thread_per_row else 0),
+                                             L.stream_of(residuals))
     L.check(rc, "rq_quantize_backward")
     return g_x, g_cb
 

@@ -124,3 +124,27 @@ def test_gumbel_forward_tensor_core_vs_simt(B, D, K, L, noise):
     _, _, i3, _ = RF.quantize_forward(xd, cd, RF.MODE_GUMBEL_SOFTMAX, 0.25, 0.2, impl=RF.IMPL_TCGEN05,
                                       want_embeddings=False, want_residuals=False, want_loss=False, **kw)
     assert torch.equal(i3, i2)
+
+
+@pytest.mark.parametrize("B,D,K,L", [(5000, 64, 1024, 4), (4097, 32, 256, 3), (4100, 64, 300, 2), (4500, 32, 1000, 2)])
+@pytest.mark.parametrize("noise", ["given", "philox"])
+def test_gumbel_backward_tensor_core_vs_thread_per_row(B, D, K, L, noise):
+    """rq_quantize_backward in Gumbel mode: the GEMM formulation on the tensor cores against the CUDA-core kernel
+    (RQ_BWD_THREAD_PER_ROW), same saved residuals, every upstream gradient present."""
+    g = torch.Generator().manual_seed(B + K + 1)
+    x = torch.randn(B, D, generator=g)
+    cbs = torch.stack(synthetic_codebooks(torch.randn(max(4 * K, 2048), D, generator=g), L, K, seed=3))
+    gu = torch.rand(L, B, K, generator=g).to(DEV) if noise == "given" else None
+    xd, cd = x.to(DEV), cbs.to(DEV)
+    g_emb = torch.randn(L, B, D, generator=g).to(DEV)
+    g_res = (torch.randn(L, B, D, generator=g) * 0.1).to(DEV)
+    g_loss = torch.rand(B, generator=g).to(DEV)
+    _, res, ids, _ = RF.quantize_forward(xd, cd, RF.MODE_GUMBEL_SOFTMAX, 0.25, 0.2, gumbel_uniform=gu, seed=11, offset=5,
+                                         impl=RF.IMPL_SIMT)
+    args = (g_emb, g_res, g_loss, res, ids, cd, RF.MODE_GUMBEL_SOFTMAX, 0.25, 0.2)
+    kw = dict(gumbel_uniform=gu, seed=11, offset=5)
+    gx1, gc1 = RF.quantize_backward(*args, thread_per_row=True, **kw)
+    gx2, gc2 = RF.quantize_backward(*args, **kw)
+    torch.cuda.synchronize()
+    assert_close(gx2, gx1, "g_x", tol=2e-4)
+    assert_close(gc2, gc1, "g_codebooks", tol=2e-4)
