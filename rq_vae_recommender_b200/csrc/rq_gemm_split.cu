@@ -23,11 +23,16 @@ __device__ __forceinline__ uint32_t sw128_off(int r, int c) {
     return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
 }
 // three bf16 planes of four consecutive fp32 values: 8 bytes per plane
-__device__ __forceinline__ void split3_store(const float4& v, uint8_t* p1, uint8_t* p2, uint8_t* p3) {
+__device__ __forceinline__ void split3_store(const float4& v, uint8_t* p1, uint8_t* p2, uint8_t* p3, bool third = true) {
     const uint32_t h01 = ptx::pack_bf16x2(v.x, v.y), h23 = ptx::pack_bf16x2(v.z, v.w);
     const float r0 = v.x - __uint_as_float(h01 << 16), r1 = v.y - __uint_as_float(h01 & 0xFFFF0000u);
     const float r2 = v.z - __uint_as_float(h23 << 16), r3 = v.w - __uint_as_float(h23 & 0xFFFF0000u);
     const uint32_t m01 = ptx::pack_bf16x2(r0, r1), m23 = ptx::pack_bf16x2(r2, r3);
+    if (!third) {
+        *reinterpret_cast<uint2*>(p1) = make_uint2(h01, h23);
+        *reinterpret_cast<uint2*>(p2) = make_uint2(m01, m23);
+        return;
+    }
     const float s0 = r0 - __uint_as_float(m01 << 16), s1 = r1 - __uint_as_float(m01 & 0xFFFF0000u);
     const float s2 = r2 - __uint_as_float(m23 << 16), s3 = r3 - __uint_as_float(m23 & 0xFFFF0000u);
     const uint32_t l01 = ptx::pack_bf16x2(s0, s1), l23 = ptx::pack_bf16x2(s2, s3);
@@ -45,6 +50,7 @@ struct SplitGemmParams {
     float alpha;
     int atomic;          // 1: C += alpha * A B^T with float atomics (split-K, or accumulation into a live buffer)
     int kb_per_split;    // K-blocks per blockIdx.z
+    int terms;           // 6: three planes, fp32-grade (error ~2^-22 |a||b|); 3: two planes, a1.b1 + a1.b2 + a2.b1 (2^-16)
 };
 
 template <int NT>
@@ -98,7 +104,7 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
                 }
             }
             const uint32_t o = sw128_off(r, c4 >> 1) + (c4 & 1) * 8;
-            split3_store(v, sA + o, sA + A_PLANE + o, sA + 2 * A_PLANE + o);
+            split3_store(v, sA + o, sA + A_PLANE + o, sA + 2 * A_PLANE + o, g.terms == 6);
         }
         for (int i = tid; i < NT * 16; i += THREADS) {
             const int r = i >> 4, c4 = i & 15;
@@ -114,7 +120,7 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
                 }
             }
             const uint32_t o = sw128_off(r, c4 >> 1) + (c4 & 1) * 8;
-            split3_store(v, sB + o, sB + B_PLANE + o, sB + 2 * B_PLANE + o);
+            split3_store(v, sB + o, sB + B_PLANE + o, sB + 2 * B_PLANE + o, g.terms == 6);
         }
         ptx::fence_proxy_async_smem();
         ptx::tc_fence_before_sync();
@@ -128,11 +134,12 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
             const int pb[6] = {0, 2, 1, 0, 1, 0};
 #pragma unroll
             for (int t = 0; t < 6; ++t) {
+                if (g.terms != 6 && t < 3) continue;               // two planes: the last three products only
 #pragma unroll
                 for (int s = 0; s < 4; ++s) {                      // four K = 16 steps of 32 bytes
                     const uint64_t ad = ptx::make_smem_desc(a0 + pa[t] * A_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
                     const uint64_t bd = ptx::make_smem_desc(b0 + pb[t] * B_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
-                    ptx::umma_bf16(tmem_acc, ad, bd, idesc, (kb > kb0 || t > 0 || s > 0) ? 1u : 0u);
+                    ptx::umma_bf16(tmem_acc, ad, bd, idesc, (kb > kb0 || t > (g.terms == 6 ? 0 : 3) || s > 0) ? 1u : 0u);
                 }
             }
             ptx::umma_commit(mbar);
@@ -182,10 +189,143 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
     if (warp == 1) ptx::tmem_dealloc(tmem_acc, NT < 32 ? 32 : NT);
 }
 
+// The same product for Kd <= 64 (one K-block: the [B, D] x [K, D]^T logits of the Gumbel path) as a persistent kernel:
+// a CTA converts its 256-row B tile ONCE and walks over M tiles with two A buffers and two TMEM accumulators, so the
+// MMAs of tile i + 1 run under the epilogue (128 KB of stores) of tile i.  grid = (N tiles, CTAs per N tile).
+__global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(SplitGemmParams g) {
+    using namespace sg;
+    constexpr int NT = 256;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+    constexpr int A_PLANE = TM * 128, B_PLANE = NT * 128;
+    uint8_t* sB = smem;                                   // [3][256 rows][64 bf16]
+    uint8_t* sA = smem + 3 * B_PLANE;                     // [2 buffers][3][128 rows][64 bf16]
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 3 * B_PLANE + 6 * A_PLANE);     // [2]
+    uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(mbar + 2);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t n0 = (int64_t)blockIdx.x * NT;
+    const int64_t m_tiles = (g.M + TM - 1) / TM;
+    const int64_t n_mine = (m_tiles > (int64_t)blockIdx.y) ? (m_tiles - 1 - blockIdx.y) / gridDim.y + 1 : 0;
+    if (tid == 0) {
+        ptx::mbar_init(&mbar[0], 1);
+        ptx::mbar_init(&mbar[1], 1);
+        ptx::fence_mbar_init();
+    }
+    if (warp == 1) ptx::tmem_alloc(tmem_base_s, 512);
+    // B tile: converted once
+    for (int i = tid; i < NT * 16; i += THREADS) {
+        const int r = i >> 4, c4 = i & 15;
+        const int64_t row = n0 + r, k = c4 * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row < g.N) {
+            const float* src = g.B + row * g.ldb + k;
+            if (k + 3 < g.Kd) v = __ldg(reinterpret_cast<const float4*>(src));
+            else {
+                if (k < g.Kd) v.x = __ldg(src);
+                if (k + 1 < g.Kd) v.y = __ldg(src + 1);
+                if (k + 2 < g.Kd) v.z = __ldg(src + 2);
+            }
+        }
+        const uint32_t o = sw128_off(r, c4 >> 1) + (c4 & 1) * 8;
+        split3_store(v, sB + o, sB + B_PLANE + o, sB + 2 * B_PLANE + o, g.terms == 6);
+    }
+    ptx::fence_proxy_async_smem();
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    ptx::tc_fence_after_sync();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_base_s);
+    const uint32_t idesc = ptx::make_idesc_bf16_f32(TM, NT);
+    bool timed_out = false;
+
+    auto stage_a = [&](int64_t it) {
+        const int64_t m0 = ((int64_t)blockIdx.y + it * gridDim.y) * TM;
+        uint8_t* dstA = sA + (it & 1) * 3 * A_PLANE;
+        for (int i = tid; i < TM * 16; i += THREADS) {
+            const int r = i >> 4, c4 = i & 15;
+            const int64_t row = m0 + r, k = c4 * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row < g.M) {
+                const float* src = g.A + row * g.lda + k;
+                if (k + 3 < g.Kd) v = __ldg(reinterpret_cast<const float4*>(src));
+                else {
+                    if (k < g.Kd) v.x = __ldg(src);
+                    if (k + 1 < g.Kd) v.y = __ldg(src + 1);
+                    if (k + 2 < g.Kd) v.z = __ldg(src + 2);
+                }
+            }
+            const uint32_t o = sw128_off(r, c4 >> 1) + (c4 & 1) * 8;
+            split3_store(v, dstA + o, dstA + A_PLANE + o, dstA + 2 * A_PLANE + o, g.terms == 6);
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::tc_fence_before_sync();                 // this thread's tcgen05.ld of the accumulator about to be reused
+        __syncthreads();
+        if (tid == 0) {
+            ptx::tc_fence_after_sync();
+            const uint32_t a0 = ptx::smem_u32(dstA), b0 = ptx::smem_u32(sB);
+            const uint32_t acc = tmem_base + (uint32_t)((it & 1) * NT);
+            const int pa[6] = {2, 0, 1, 1, 0, 0};
+            const int pb[6] = {0, 2, 1, 0, 1, 0};
+            bool first = true;
+#pragma unroll
+            for (int t = 0; t < 6; ++t) {
+                if (g.terms != 6 && t < 3) continue;
+#pragma unroll
+                for (int s = 0; s < 4; ++s) {
+                    const uint64_t ad = ptx::make_smem_desc(a0 + pa[t] * A_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
+                    const uint64_t bd = ptx::make_smem_desc(b0 + pb[t] * B_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
+                    ptx::umma_bf16(acc, ad, bd, idesc, first ? 0u : 1u);
+                    first = false;
+                }
+            }
+            ptx::umma_commit(&mbar[it & 1]);
+        }
+    };
+
+    if (n_mine > 0) stage_a(0);
+    for (int64_t it = 0; it < n_mine; ++it) {
+        // the next tile's rows go in (other A buffer, other accumulator: both were released before the last barrier)
+        if (it + 1 < n_mine) stage_a(it + 1);
+        if (!ptx::mbar_wait(&mbar[it & 1], (uint32_t)((it >> 1) & 1))) timed_out = true;
+        ptx::tc_fence_after_sync();
+        const int64_t m0 = ((int64_t)blockIdx.y + it * gridDim.y) * TM;
+        const int q = warp & 3, h = warp >> 2;
+        const int64_t row = m0 + q * 32 + lane;
+        constexpr int HALF = NT / 2;
+        const uint32_t trow = tmem_base + (uint32_t)((it & 1) * NT) + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * HALF);
+#pragma unroll 1
+        for (int c = 0; c < HALF; c += 32) {
+            uint32_t v[32];
+            ptx::tmem_ld_32x32b_x32(trow + c, v);
+            ptx::tmem_ld_wait_for(v);
+            if (row < g.M) {
+                float* dst = g.C + row * g.ldc + n0 + h * HALF + c;
+                const int64_t ncol = g.N - (n0 + h * HALF + c);
+                if (ncol >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 31) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        float o[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) o[u] = g.alpha * __uint_as_float(v[j + u]);
+                        ptx::st_global_v8(dst + j, o);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncol) dst[j] = g.alpha * __uint_as_float(v[j]);
+                }
+            }
+        }
+    }
+    (void)timed_out;
+    ptx::tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc(tmem_base, 512);
+}
+
 // C[M, N] (+)= alpha * A[M, Kd] * B[N, Kd]^T.  k_splits > 1 (or atomic) accumulates with float atomics into C, which the
 // caller has initialised.  Rows of A and B must be 16-byte aligned (lda, ldb multiples of 4 floats).
 int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda, int64_t ldb,
-               int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st) {
+               int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st, int terms) {
     if (M <= 0 || N <= 0 || Kd <= 0) return 0;
     if ((lda & 3) || (ldb & 3) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) {
         set_error("split_gemm: operand rows must be 16-byte aligned");
@@ -194,6 +334,7 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
     SplitGemmParams g;
     g.A = A; g.B = B; g.C = C; g.M = M; g.N = N; g.Kd = Kd; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
     g.alpha = alpha;
+    g.terms = (terms == 3) ? 3 : 6;
     const int64_t n_kb = (Kd + sg::KB - 1) / sg::KB;
     if (k_splits < 1) k_splits = 1;
     if (k_splits > n_kb) k_splits = (int)n_kb;
@@ -201,7 +342,16 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
     k_splits = (int)((n_kb + g.kb_per_split - 1) / g.kb_per_split);
     g.atomic = (atomic || k_splits > 1) ? 1 : 0;
     const unsigned gm = (unsigned)((M + sg::TM - 1) / sg::TM);
-    if (N > 64) {
+    if (N > 64 && Kd <= sg::KB && !g.atomic) {
+        // one K-block: persistent CTAs with the B tile resident
+        const unsigned gn = (unsigned)((N + 255) / 256);
+        unsigned per = (unsigned)sm_count() / gn;
+        if (per < 1) per = 1;
+        if (per > gm) per = gm;
+        const size_t smem = 3 * 256 * 128 + 6 * sg::TM * 128 + 64 + 1024;
+        RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_bres_kernel, (int)smem));
+        rq_split_gemm_bres_kernel<<<dim3(gn, per), sg::THREADS, smem, st>>>(g);
+    } else if (N > 64) {
         constexpr int NT = 256;
         const size_t smem = 3 * sg::TM * 128 + 3 * NT * 128 + 64 + 1024;
         RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_kernel<NT>, (int)smem));
@@ -224,5 +374,7 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
 extern "C" int rq_debug_split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd,
                                    int64_t lda, int64_t ldb, int64_t ldc, float alpha, int atomic, int k_splits,
                                    rq_stream_t stream) {
-    return rq::split_gemm(A, B, C, M, N, Kd, lda, ldb, ldc, alpha, atomic, k_splits, (cudaStream_t)stream);
+    // k_splits < 0 selects the two-plane (three-product) form with |k_splits| splits
+    return rq::split_gemm(A, B, C, M, N, Kd, lda, ldb, ldc, alpha, atomic, k_splits < 0 ? -k_splits : k_splits,
+                          (cudaStream_t)stream, k_splits < 0 ? 3 : 6);
 }

@@ -28,7 +28,7 @@
 namespace rq {
 
 int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda, int64_t ldb,
-               int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st);
+               int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st, int terms = 6);
 
 namespace gtc {
 
@@ -84,10 +84,8 @@ __global__ void __launch_bounds__(256) gumbel_softmax_rows_kernel(RowParams q) {
     }
     float* Srow = q.S + row * q.Kp;
     const float* gurow = q.gu ? q.gu + row * q.K : nullptr;
-    // pass 1: logits in place, row maximum
-    float m = -INFINITY;
-    for (int k = lane * 4; k < q.Kp; k += 128) {
-        float4 s = *reinterpret_cast<const float4*>(Srow + k);
+    // logits of the four codes k .. k + 3 from the products s (quantize.py:108-112, 125-126)
+    auto logits4 = [&](int k, const float4& s, float (&y)[4]) {
         const float4 c = __ldg(reinterpret_cast<const float4*>(q.cc + k));
         float u[4];
         if (gurow) {
@@ -98,19 +96,56 @@ __global__ void __launch_bounds__(256) gumbel_softmax_rows_kernel(RowParams q) {
                                             make_uint2((uint32_t)(q.seed ^ q.offset), (uint32_t)((q.seed >> 32) ^ (q.offset >> 32))));
             u[0] = u01(rnd.x); u[1] = u01(rnd.y); u[2] = u01(rnd.z); u[3] = u01(rnd.w);
         }
-        float y[4];
         const float sv[4] = {s.x, s.y, s.z, s.w}, cv[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
-            const float d = (xx + cv[t]) - 2.f * sv[t];                       // quantize.py:108-112
+            const float d = (xx + cv[t]) - 2.f * sv[t];
             y[t] = (k + t < q.K) ? (-d + gumbel_from_u(u[t])) * q.inv_t : -INFINITY;
-            m = fmaxf(m, y[t]);
         }
+    };
+    if (q.Kp <= 1024) {
+        // the row fits the warp's registers (8 float4 per lane): one read and one write of the [B, K] matrix
+        float y[8][4];
+        float m = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int k = lane * 4 + 128 * i;
+            if (k < q.Kp) {
+                logits4(k, *reinterpret_cast<const float4*>(Srow + k), y[i]);
+                m = fmaxf(fmaxf(m, fmaxf(y[i][0], y[i][1])), fmaxf(y[i][2], y[i][3]));
+            } else {
+                y[i][0] = y[i][1] = y[i][2] = y[i][3] = -INFINITY;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t) y[i][t] = __expf(y[i][t] - m);
+            sum += (y[i][0] + y[i][1]) + (y[i][2] + y[i][3]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        const float inv = 1.0f / sum;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int k = lane * 4 + 128 * i;
+            if (k < q.Kp) *reinterpret_cast<float4*>(Srow + k) = make_float4(y[i][0] * inv, y[i][1] * inv, y[i][2] * inv, y[i][3] * inv);
+        }
+        return;
+    }
+    // longer rows: three passes in place (the row is L1 / L2 resident after the first)
+    float m = -INFINITY;
+    for (int k = lane * 4; k < q.Kp; k += 128) {
+        float y[4];
+        logits4(k, *reinterpret_cast<const float4*>(Srow + k), y);
+        m = fmaxf(fmaxf(m, fmaxf(y[0], y[1])), fmaxf(y[2], y[3]));
         *reinterpret_cast<float4*>(Srow + k) = make_float4(y[0], y[1], y[2], y[3]);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    // pass 2: exp, row sum
     float sum = 0.f;
     for (int k = lane * 4; k < q.Kp; k += 128) {
         float4 y = *reinterpret_cast<const float4*>(Srow + k);
@@ -121,7 +156,6 @@ __global__ void __launch_bounds__(256) gumbel_softmax_rows_kernel(RowParams q) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
     const float inv = 1.0f / sum;
-    // pass 3: normalise (the row is L1 / L2 resident)
     for (int k = lane * 4; k < q.Kp; k += 128) {
         float4 y = *reinterpret_cast<const float4*>(Srow + k);
         y.x *= inv; y.y *= inv; y.z *= inv; y.w *= inv;
@@ -328,7 +362,7 @@ static int gumbel_forward_tc_impl(const FwdParams& p, cudaStream_t st) {
         q.B = B; q.K = K; q.Kp = Kp; q.level = l; q.inv_t = 1.0f / p.temp; q.seed = p.seed; q.offset = p.offset;
         gumbel_softmax_rows_kernel<D><<<(unsigned)((B + 7) / 8), 256, 0, st>>>(q);
         RQ_LAUNCHED();
-        rc = split_gemm(S, ct, emb_l, B, D, K, Kp, Kp, D, 1.f, 0, 1, st);
+        rc = split_gemm(S, ct, emb_l, B, D, K, Kp, Kp, D, 1.f, 0, 1, st, 6);
         if (rc) break;
         TailParams t;
         t.r = r_in; t.emb = emb_l; t.res_out = p.res ? p.res + (int64_t)l * B * D : nullptr;
@@ -419,7 +453,7 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
         gumbel_dd_rows_kernel<<<rows8, 256, 0, st>>>(W, dd, t, B, Kp, 1.0f / temperature);
         RQ_LAUNCHED();
         // v = dd C
-        if ((rc = split_gemm(dd, ct, v, B, D, K, Kp, Kp, D, 1.f, 0, 1, st))) break;
+        if ((rc = split_gemm(dd, ct, v, B, D, K, Kp, Kp, D, 1.f, 0, 1, st, 3))) break;
         // codebook gradient: W^T de - 2 dd^T x + 2 C colsum(dd), contraction over the rows
         {
             dim3 gT((unsigned)((B + 31) / 32), (unsigned)((K + 31) / 32));
@@ -430,8 +464,8 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
             transpose_kernel<<<gR, 256, 0, st>>>(x, xt, B, D, D, Bp);
             RQ_LAUNCHED();
         }
-        if ((rc = split_gemm(Wt, det, gcb, K, D, B, Bp, Bp, D, 1.f, 1, splits, st))) break;
-        if ((rc = split_gemm(ddt, xt, gcb, K, D, B, Bp, Bp, D, -2.f, 1, splits, st))) break;
+        if ((rc = split_gemm(Wt, det, gcb, K, D, B, Bp, Bp, D, 1.f, 1, splits, st, 3))) break;
+        if ((rc = split_gemm(ddt, xt, gcb, K, D, B, Bp, Bp, D, -2.f, 1, splits, st, 3))) break;
         gumbel_colsum_kernel<D><<<(K + 7) / 8, 256, 0, st>>>(ddt, B, Bp, K, cbl, gcb);
         RQ_LAUNCHED();
         // G = G + ... - 2 v; the last level processed writes g_x
