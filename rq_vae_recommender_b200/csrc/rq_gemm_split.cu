@@ -57,22 +57,31 @@ __device__ __forceinline__ float4 load4_guarded(const float* base, int64_t row, 
 // Stages ROWS x 64 fp32 (rows row0.., columns k0..) as bf16 planes: ALL of a thread's loads are issued before the first
 // conversion, so a K-block costs one memory latency, not one per float4 (the first version: 8.7 us per block).
 template <int ROWS>
-__device__ __forceinline__ void stage_tile(const float* base, int64_t row0, int64_t rows, int64_t ld, int64_t k0, int64_t Kd,
-                                           uint8_t* planes, int plane_bytes, bool third, int tid) {
-    constexpr int PER = ROWS * 16 / THREADS;
-    float4 v[PER];
+__device__ __forceinline__ void tile_load(const float* base, int64_t row0, int64_t rows, int64_t ld, int64_t k0, int64_t Kd,
+                                          float4 (&v)[ROWS * 16 / THREADS], int tid) {
 #pragma unroll
-    for (int j = 0; j < PER; ++j) {
+    for (int j = 0; j < ROWS * 16 / THREADS; ++j) {
         const int i = tid + j * THREADS;
         v[j] = load4_guarded(base, row0 + (i >> 4), rows, ld, k0 + (i & 15) * 4, Kd);
     }
+}
+template <int ROWS>
+__device__ __forceinline__ void tile_store(const float4 (&v)[ROWS * 16 / THREADS], uint8_t* planes, int plane_bytes, bool third,
+                                           int tid) {
 #pragma unroll
-    for (int j = 0; j < PER; ++j) {
+    for (int j = 0; j < ROWS * 16 / THREADS; ++j) {
         const int i = tid + j * THREADS;
         const int r = i >> 4, c4 = i & 15;
         const uint32_t o = sw128_off(r, c4 >> 1) + (c4 & 1) * 8;
         split3_store(v[j], planes + o, planes + plane_bytes + o, planes + 2 * plane_bytes + o, third);
     }
+}
+template <int ROWS>
+__device__ __forceinline__ void stage_tile(const float* base, int64_t row0, int64_t rows, int64_t ld, int64_t k0, int64_t Kd,
+                                           uint8_t* planes, int plane_bytes, bool third, int tid) {
+    float4 v[ROWS * 16 / THREADS];
+    tile_load<ROWS>(base, row0, rows, ld, k0, Kd, v, tid);
+    tile_store<ROWS>(v, planes, plane_bytes, third, tid);
 }
 }  // namespace sg
 
@@ -117,6 +126,14 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
     const uint32_t idesc = ptx::make_idesc_bf16_f32(TM, NT);
     bool timed_out = false;
 
+    // The loads of block kb + 1 are issued right after the MMAs of block kb, so their latency runs under those MMAs and
+    // the wait for them (NT = 64: 12 float4 per thread in flight; the 256-wide tile has no registers to spare for it).
+    constexpr bool PIPE = (NT == 64);
+    float4 ra[TM * 16 / THREADS], rb[NT * 16 / THREADS];
+    if (PIPE) {
+        tile_load<TM>(g.A, m0, g.M, g.lda, kb0 * KB, g.Kd, ra, tid);
+        tile_load<NT>(g.B, n0, g.N, g.ldb, kb0 * KB, g.Kd, rb, tid);
+    }
     for (int64_t kb = kb0; kb < kb1; ++kb) {
         if (kb > kb0) {                                            // the tiles are still being read by the last block's MMAs
             if (!ptx::mbar_wait(mbar, (uint32_t)((kb - kb0 - 1) & 1))) timed_out = true;
@@ -124,8 +141,13 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
         }
         const int64_t k0 = kb * KB;
         // ---- stage: 16 float4 per row, a warp reads two rows' 256 contiguous bytes per instruction ----------------------
-        stage_tile<TM>(g.A, m0, g.M, g.lda, k0, g.Kd, sA, A_PLANE, g.terms == 6, tid);
-        stage_tile<NT>(g.B, n0, g.N, g.ldb, k0, g.Kd, sB, B_PLANE, g.terms == 6, tid);
+        if (PIPE) {
+            tile_store<TM>(ra, sA, A_PLANE, g.terms == 6, tid);
+            tile_store<NT>(rb, sB, B_PLANE, g.terms == 6, tid);
+        } else {
+            stage_tile<TM>(g.A, m0, g.M, g.lda, k0, g.Kd, sA, A_PLANE, g.terms == 6, tid);
+            stage_tile<NT>(g.B, n0, g.N, g.ldb, k0, g.Kd, sB, B_PLANE, g.terms == 6, tid);
+        }
         ptx::fence_proxy_async_smem();
         ptx::tc_fence_before_sync();
         __syncthreads();
@@ -147,6 +169,10 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
                 }
             }
             ptx::umma_commit(mbar);
+        }
+        if (PIPE && kb + 1 < kb1) {
+            tile_load<TM>(g.A, m0, g.M, g.lda, k0 + KB, g.Kd, ra, tid);
+            tile_load<NT>(g.B, n0, g.N, g.ldb, k0 + KB, g.Kd, rb, tid);
         }
     }
     if (!ptx::mbar_wait(mbar, (uint32_t)((kb1 - kb0 - 1) & 1))) timed_out = true;

@@ -244,24 +244,6 @@ __global__ void __launch_bounds__(256) gumbel_de_kernel(DeParams q) {
     if ((i % LPR) == 0) q.t[row] = t;
 }
 
-// dd = -W (dW - t) / T, in place over dW; one warp per row
-__global__ void __launch_bounds__(256) gumbel_dd_rows_kernel(const float* __restrict__ W, float* __restrict__ dW,
-                                                             const float* __restrict__ t, int64_t B, int Kp, float inv_t) {
-    const int lane = threadIdx.x & 31;
-    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (row >= B) return;
-    const float tr = __ldg(t + row);
-    const float4* w4 = reinterpret_cast<const float4*>(W + row * Kp);
-    float4* d4 = reinterpret_cast<float4*>(dW + row * Kp);
-    for (int k = lane; k < Kp / 4; k += 32) {
-        const float4 w = __ldg(w4 + k);
-        float4 d = d4[k];
-        d.x = -(w.x * (d.x - tr)) * inv_t; d.y = -(w.y * (d.y - tr)) * inv_t;
-        d.z = -(w.z * (d.z - tr)) * inv_t; d.w = -(w.w * (d.w - tr)) * inv_t;
-        d4[k] = d;
-    }
-}
-
 // dst[c, r] = src[r, c] through 32 x 32 shared-memory tiles (src [R, C] row stride lds, dst [C, R] row stride ldd;
 // the columns r >= R of dst up to ldd are left untouched: the caller zeroes the padding once)
 __global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t R,
@@ -282,18 +264,63 @@ __global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict_
     }
 }
 
-// g_C[k, :] += 2 C[k, :] * sum_b ddT[k, b]; one warp per code
-template <int D>
-__global__ void __launch_bounds__(256) gumbel_colsum_kernel(const float* __restrict__ ddt, int64_t B, int64_t ldb, int K,
-                                                            const float* __restrict__ cb, float* __restrict__ g_cb) {
-    const int lane = threadIdx.x & 31;
-    const int k = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (k >= K) return;
-    float s = 0.f;
-    for (int64_t b = lane; b < B; b += 32) s += __ldg(ddt + (int64_t)k * ldb + b);
+// One pass over the [B, K] matrices of a level's backward: dd = -W (dW - t) / T written in place over dW (the operand
+// of v = dd C), and — through 32 x 32 shared-memory tiles — W^T and dd^T (the operands of the codebook-gradient
+// products, whose contraction runs over the rows) plus the column sums of dd (one atomic per tile column).
+__global__ void __launch_bounds__(256) gumbel_dd_transpose_kernel(const float* __restrict__ W, float* __restrict__ dW,
+                                                                  const float* __restrict__ t, int64_t B, int K, int Kp,
+                                                                  float inv_t, float* __restrict__ Wt, float* __restrict__ ddt,
+                                                                  int64_t Bp, float* __restrict__ csum) {
+    __shared__ float tw[32][33], td[32][33];
+    const int c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    float colsum[4] = {0.f, 0.f, 0.f, 0.f};           // of columns c0 + ty + 8 j, over this block's 256 rows (lane 0 keeps them)
+    for (int sub = 0; sub < 8; ++sub) {
+        const int64_t r0 = ((int64_t)blockIdx.x * 8 + sub) * 32;
+        if (r0 >= B) break;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    for (int j = lane; j < D; j += 32) atomicAdd(g_cb + (int64_t)k * D + j, 2.f * __ldg(cb + (int64_t)k * D + j) * s);
+        for (int j = 0; j < 32; j += 8) {
+            const int64_t r = r0 + ty + j;
+            const int c = c0 + tx;
+            float w = 0.f, d = 0.f;
+            if (r < B && c < K) {
+                w = __ldg(W + r * Kp + c);
+                d = -(w * (dW[r * Kp + c] - __ldg(t + r))) * inv_t;
+                dW[r * Kp + c] = d;
+            }
+            tw[ty + j][tx] = w;
+            td[ty + j][tx] = d;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+            const int c = c0 + ty + j;
+            const int64_t r = r0 + tx;
+            const float d = td[tx][ty + j];
+            if (c < K && r < B) {
+                Wt[(int64_t)c * Bp + r] = tw[tx][ty + j];
+                ddt[(int64_t)c * Bp + r] = d;
+            }
+            float s = d;                               // rows outside B hold zeros
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            colsum[j >> 3] += s;
+        }
+        __syncthreads();
+    }
+    if (tx == 0) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (c0 + ty + 8 * j < K) atomicAdd(csum + c0 + ty + 8 * j, colsum[j]);
+    }
+}
+
+// g_C[k, :] += 2 C[k, :] * colsum(dd)[k]
+__global__ void __launch_bounds__(256) gumbel_colsum_apply_kernel(const float* __restrict__ csum, const float* __restrict__ cb,
+                                                                  float* __restrict__ g_cb, int K, int D) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= K * D) return;
+    atomicAdd(g_cb + i, 2.f * __ldg(cb + i) * __ldg(csum + i / D));
 }
 
 // G <- G - 2 v (and g_x on the last level processed)
@@ -390,7 +417,7 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
     const size_t bytes_S = (size_t)B * Kp * 4, bytes_T = (size_t)K * Bp * 4, bytes_row = (size_t)B * D * 4;
     const size_t bytes_rt = (size_t)D * Bp * 4, bytes_ct = (size_t)D * Kp * 4, bytes_cc = (size_t)Kp * 4;
     // scratch: W | dW/dd | W^T | dd^T | emb | de | v | G | de^T | x^T | C^T | cc | t
-    const size_t total = 2 * bytes_S + 2 * bytes_T + 4 * bytes_row + 2 * bytes_rt + bytes_ct + bytes_cc + (size_t)B * 4 + 256;
+    const size_t total = 2 * bytes_S + 2 * bytes_T + 4 * bytes_row + 2 * bytes_rt + bytes_ct + 2 * bytes_cc + (size_t)Bp * 4 + 256;
     uint8_t* scratch = (uint8_t*)engine_pool_alloc(total, st);
     if (!scratch) {
         set_error("rq_quantize_backward: out of device memory for the Gumbel-softmax scratch (%zu bytes)", total);
@@ -410,7 +437,8 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
     float* xt = take(bytes_rt);
     float* ct = take(bytes_ct);
     float* cc = take(bytes_cc);
-    float* t = take((size_t)B * 4);
+    float* t = take((size_t)Bp * 4);
+    float* csum = take(bytes_cc);
     int rc = 0;
 #define GTC_CUDA(call)                                                                   \
     do { if (rc == 0) { cudaError_t e_ = (call); if (e_ != cudaSuccess) { set_error("rq_quantize_backward: %s", cudaGetErrorString(e_)); rc = (int)e_; } } } while (0)
@@ -450,23 +478,22 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
         RQ_LAUNCHED();
         // dW = de C^T, dd in place
         if ((rc = split_gemm(de, cbl, dd, B, K, D, D, D, Kp, 1.f, 0, 1, st))) break;
-        gumbel_dd_rows_kernel<<<rows8, 256, 0, st>>>(W, dd, t, B, Kp, 1.0f / temperature);
-        RQ_LAUNCHED();
-        // v = dd C
-        if ((rc = split_gemm(dd, ct, v, B, D, K, Kp, Kp, D, 1.f, 0, 1, st, 3))) break;
-        // codebook gradient: W^T de - 2 dd^T x + 2 C colsum(dd), contraction over the rows
+        GTC_CUDA(cudaMemsetAsync(csum, 0, bytes_cc, st));
+        if (rc) break;
         {
-            dim3 gT((unsigned)((B + 31) / 32), (unsigned)((K + 31) / 32));
-            transpose_kernel<<<gT, 256, 0, st>>>(W, Wt, B, K, Kp, Bp);
-            transpose_kernel<<<gT, 256, 0, st>>>(dd, ddt, B, K, Kp, Bp);
+            dim3 gT((unsigned)((B + 255) / 256), (unsigned)((K + 31) / 32));
+            gumbel_dd_transpose_kernel<<<gT, 256, 0, st>>>(W, dd, t, B, K, Kp, 1.0f / temperature, Wt, ddt, Bp, csum);
             dim3 gR((unsigned)((B + 31) / 32), (unsigned)((D + 31) / 32));
             transpose_kernel<<<gR, 256, 0, st>>>(de, det, B, D, D, Bp);
             transpose_kernel<<<gR, 256, 0, st>>>(x, xt, B, D, D, Bp);
             RQ_LAUNCHED();
         }
+        // v = dd C
+        if ((rc = split_gemm(dd, ct, v, B, D, K, Kp, Kp, D, 1.f, 0, 1, st, 3))) break;
+        // codebook gradient: W^T de - 2 dd^T x + 2 C colsum(dd), contraction over the rows
         if ((rc = split_gemm(Wt, det, gcb, K, D, B, Bp, Bp, D, 1.f, 1, splits, st, 3))) break;
         if ((rc = split_gemm(ddt, xt, gcb, K, D, B, Bp, Bp, D, -2.f, 1, splits, st, 3))) break;
-        gumbel_colsum_kernel<D><<<(K + 7) / 8, 256, 0, st>>>(ddt, B, Bp, K, cbl, gcb);
+        gumbel_colsum_apply_kernel<<<(K * D + 255) / 256, 256, 0, st>>>(csum, cbl, gcb, K, D);
         RQ_LAUNCHED();
         // G = G + ... - 2 v; the last level processed writes g_x
         gumbel_g_update_kernel<<<rowsq, 256, 0, st>>>(G, v, B * (D / 4), l == 0 ? p.g_x : nullptr);
