@@ -100,7 +100,10 @@ __global__ void __launch_bounds__(256) gumbel_softmax_rows_kernel(RowParams q) {
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const float d = (xx + cv[t]) - 2.f * sv[t];
-            y[t] = (k + t < q.K) ? (-d + gumbel_from_u(u[t])) * q.inv_t : -INFINITY;
+            // gumbel.py:9-10; the outer log in its fast form: its argument lies in [1e-20, 47] and what matters is the
+            // ABSOLUTE error of g (2e-7 for MUFU.LG2 near 1), the inner one stays accurate (u -> 1 makes -log u tiny)
+            const float g = -__logf(-logf(u[t] + 1e-20f) + 1e-20f);
+            y[t] = (k + t < q.K) ? (-d + g) * q.inv_t : -INFINITY;
         }
     };
     if (q.Kp <= 1024) {
@@ -203,7 +206,8 @@ __global__ void __launch_bounds__(256) gumbel_level_tail_kernel(TailParams q) {
 // ---- backward row kernels ---------------------------------------------------------------------------------------------
 struct DeParams {
     const float* x;       // [B, D] saved residual of the level
-    const float* emb;     // [B, D] W C
+    const float* emb;     // [B, D] W C, or nullptr: emb = x - x_next (the saved residuals of two consecutive levels)
+    const float* x_next;  // [B, D] residual of level l + 1 (used when emb is nullptr)
     const float* g_emb;   // [B, D] or nullptr
     const float* g_res;   // [B, D] or nullptr
     const float* g_loss;  // [B] or nullptr
@@ -223,7 +227,11 @@ __global__ void __launch_bounds__(256) gumbel_de_kernel(DeParams q) {
     float gl = 0.f;
     if (active) {
         x = __ldg(reinterpret_cast<const float4*>(q.x) + i);
-        e = __ldg(reinterpret_cast<const float4*>(q.emb) + i);
+        if (q.emb) e = __ldg(reinterpret_cast<const float4*>(q.emb) + i);
+        else {
+            const float4 n = __ldg(reinterpret_cast<const float4*>(q.x_next) + i);          // rqvae.py:129: r_next = r - emb
+            e = make_float4(x.x - n.x, x.y - n.y, x.z - n.z, x.w - n.w);
+        }
         if (q.g_emb) ge = __ldg(reinterpret_cast<const float4*>(q.g_emb) + i);
         if (q.g_res) gr = __ldg(reinterpret_cast<const float4*>(q.g_res) + i);
         G = reinterpret_cast<const float4*>(q.G)[i];
@@ -467,10 +475,13 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
         q.B = B; q.K = K; q.Kp = Kp; q.level = l; q.inv_t = 1.0f / temperature; q.seed = seed; q.offset = offset;
         gumbel_softmax_rows_kernel<D><<<rows8, 256, 0, st>>>(q);
         RQ_LAUNCHED();
-        if ((rc = split_gemm(W, ct, emb, B, D, K, Kp, Kp, D, 1.f, 0, 1, st))) break;
+        // emb = W C is needed for de and t: below the last level it is the difference of two saved residuals
+        const bool have_next = (l + 1 < p.L);
+        if (!have_next && (rc = split_gemm(W, ct, emb, B, D, K, Kp, Kp, D, 1.f, 0, 1, st))) break;
         // de, t, and the part of G that does not depend on the codes
         DeParams dq;
-        dq.x = x; dq.emb = emb;
+        dq.x = x; dq.emb = have_next ? nullptr : emb;
+        dq.x_next = have_next ? p.res + (int64_t)(l + 1) * B * D : nullptr;
         dq.g_emb = p.g_emb ? p.g_emb + (int64_t)l * B * D : nullptr;
         dq.g_res = p.g_res ? p.g_res + (int64_t)l * B * D : nullptr;
         dq.g_loss = p.g_loss; dq.G = G; dq.de = de; dq.t = t; dq.B = B; dq.beta = p.beta;
