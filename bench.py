@@ -265,7 +265,8 @@ def side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss
     (2) ids-only tokenisation of this rank's shard of a 100M-item d=64 corpus (SURVEY 8d protocol: a resident 4M-item
     chunk cycled, ids written into the shard's [3, N/G] table; no collective), barrier + max over ranks;
     (3) 10 sharded k-means iterations over 10M x 32 points, K = 256 (assign + accumulate, all-reduce of sums / counts /
-    changed count over the ranks, update).  Returns the `extra` entries."""
+    changed count over the ranks, update); (4) the configs[4] shape (4 x 1024, d = 64), rotation-trick and Gumbel-softmax
+    steps, eager launches.  Returns the `extra` entries."""
     out = {}
     # ---- (1) parity: slot 0's 65,536 rows, forward + backward, engine vs oracle/rq_oracle.py ------------------------
     if rank == 0:
@@ -366,6 +367,33 @@ def side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss
                          "hbm_frac": ((hi - lo) * 4 * D / (ms * 1e-3) / 1e9) / hbm,
                          "collective": None if world == 1 else "NCCL all_reduce of [K*D + K + 1] fp64 per iteration"}
     del pts, assign
+    # ---- (4) configs[4]: 4 x 1024 codes, d = 64, 65,536 items per GPU: rotation-trick and Gumbel-softmax steps -------------
+    Bc, Dc, Kc, Lc = 65536, 64, 1024, 4
+    g5 = torch.Generator(device=dev).manual_seed(13 + rank)
+    x5 = torch.randn(Bc, Dc, device=dev, generator=g5)
+    cb5 = torch.stack([torch.randn(Kc, Dc, device=dev, generator=g5) * (0.6 ** l) for l in range(Lc)])
+    ge5 = torch.randn(Lc, Bc, Dc, device=dev, generator=g5) * 0.01
+    gl5 = torch.full((Bc,), 1.0 / Bc, device=dev)
+
+    def c5_step(m):
+        emb, res, ids, loss = RF.quantize_forward(x5, cb5, m, BETA, TEMP, seed=1, offset=2)
+        RF.quantize_backward(ge5, None, gl5, res, ids, cb5, m, BETA, TEMP, seed=1, offset=2)
+    for name, m in (("c5_rotation", RF.MODE_ROTATION_TRICK), ("c5_gumbel", RF.MODE_GUMBEL_SOFTMAX)):
+        c5_step(m)
+        c5_step(m)
+        fence()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(5):
+            c5_step(m)
+        b.record()
+        fence()
+        ms = maxed(a.elapsed_time(b)) / 5
+        out[name] = {"shape": "4 x 1024 codes, d = 64, 65,536 items per GPU, forward + backward", "ms_per_step": ms,
+                     "items_per_s": Bc * world / (ms * 1e-3),
+                     "path": "tcgen05 (streamed code chunks)" if m == RF.MODE_ROTATION_TRICK else
+                             "tcgen05 (fp32-grade split-bf16 GEMMs, Philox noise)"}
+    del x5, cb5, ge5, gl5
     return out
 
 
