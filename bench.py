@@ -376,8 +376,10 @@ def side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss
     gl5 = torch.full((Bc,), 1.0 / Bc, device=dev)
 
     def c5_step(m):
-        emb, res, ids, loss = RF.quantize_forward(x5, cb5, m, BETA, TEMP, seed=1, offset=2)
-        RF.quantize_backward(ge5, None, gl5, res, ids, cb5, m, BETA, TEMP, seed=1, offset=2)
+        # what the autograd Function does: the Gumbel forward keeps its softmax weights for the backward
+        w = RF.gumbel_weights_buffer(x5, cb5, m)
+        emb, res, ids, loss = RF.quantize_forward(x5, cb5, m, BETA, TEMP, seed=1, offset=2, gumbel_weights_out=w)
+        RF.quantize_backward(ge5, None, gl5, res, ids, cb5, m, BETA, TEMP, seed=1, offset=2, gumbel_weights=w)
     for name, m in (("c5_rotation", RF.MODE_ROTATION_TRICK), ("c5_gumbel", RF.MODE_GUMBEL_SOFTMAX)):
         c5_step(m)
         c5_step(m)
@@ -392,7 +394,7 @@ def side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss
         out[name] = {"shape": "4 x 1024 codes, d = 64, 65,536 items per GPU, forward + backward", "ms_per_step": ms,
                      "items_per_s": Bc * world / (ms * 1e-3),
                      "path": "tcgen05 (streamed code chunks)" if m == RF.MODE_ROTATION_TRICK else
-                             "tcgen05 (fp32-grade split-bf16 GEMMs, Philox noise)"}
+                             "tcgen05 (fp32-grade split-bf16 GEMMs, Philox noise, softmax weights kept for the backward)"}
     del x5, cb5, ge5, gl5
     return out
 

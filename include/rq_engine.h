@@ -83,6 +83,21 @@ int rq_quantize_forward(const float* x, const float* codebooks, int64_t B, int D
                         int impl, rq_stream_t stream);
 
 /*
+ * The same with one more output for the Gumbel-softmax pair on the tensor cores: gumbel_weights [L, B, Kp], Kp = K
+ * rounded up to a multiple of 4 — the softmax weights W of every level (what autograd keeps alive in the reference:
+ * the output of F.softmax, quantize.py:127).  Handing the buffer back to rq_quantize_backward_ws saves the backward the
+ * recomputation of the logits product and of the softmax (a fifth of the step at 4 x 1024 codes).  NULL, another mode,
+ * or a launch that the thread-per-row kernels serve (see rq_gumbel_weights_saved) = rq_quantize_forward.
+ */
+int rq_quantize_forward_ws(const float* x, const float* codebooks, int64_t B, int D, int K, int L,
+                           int mode, int distance, float beta, float temperature,
+                           const float* gumbel_u, uint64_t seed, uint64_t offset,
+                           float* emb_out, float* residuals, int64_t* ids, float* loss,
+                           float* gumbel_weights, int impl, rq_stream_t stream);
+/* 1 if rq_quantize_forward_ws with these arguments fills gumbel_weights (the tensor-core Gumbel path is taken). */
+int rq_gumbel_weights_saved(int64_t B, int D, int K, int L, int mode, int distance, int impl);
+
+/*
  * Fused backward of the above (the reference relies on autograd).
  *   g_emb [L,B,D], g_res [L,B,D], g_loss [B]  upstream gradients (any may be NULL = zero)
  *   residuals, ids                             saved from the forward
@@ -228,6 +243,13 @@ int rq_debug_peer_timeout_flag(void);   /* 1 once a rank failed to arrive at a b
 int rq_semantic_ids_host(const float* x_host, const float* codebooks, int64_t B, int D, int K, int L,
                          int distance, int64_t* ids_host, float* loss_host, int impl,
                          rq_stream_t stream);
+
+/* rq_quantize_backward_ex with the softmax weights rq_quantize_forward_ws saved (NULL = recompute them). */
+int rq_quantize_backward_ws(const float* g_emb, const float* g_res, const float* g_loss,
+                            const float* residuals, const int64_t* ids, const float* codebooks,
+                            int64_t B, int D, int K, int L, int mode, float beta, float temperature,
+                            const float* gumbel_u, uint64_t seed, uint64_t offset,
+                            float* g_x, float* g_codebooks, const float* gumbel_weights, int flags, rq_stream_t stream);
 
 /* Test hooks of the tcgen05 family: 1 if any mbarrier wait timed out since load (synchronises the
  * device); and a [128][256] fp32 device buffer that receives tile 0 / level 0's raw accumulator

@@ -28,6 +28,13 @@ SIGNATURES = {
     "rq_quantize_forward": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_float,
                                     c_float, c_void_p, c_uint64, c_uint64, c_void_p, c_void_p, c_void_p,
                                     c_void_p, c_int, c_void_p]),
+    "rq_quantize_forward_ws": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_float,
+                                       c_float, c_void_p, c_uint64, c_uint64, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p, c_int, c_void_p]),
+    "rq_gumbel_weights_saved": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int, c_int]),
+    "rq_quantize_backward_ws": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                        c_int, c_int, c_int, c_float, c_float, c_void_p, c_uint64, c_uint64,
+                                        c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "rq_quantize_backward": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                                      c_int, c_int, c_int, c_float, c_float, c_void_p, c_uint64, c_uint64,
                                      c_void_p, c_void_p, c_void_p]),

@@ -81,10 +81,27 @@ extern "C" int rq_tcgen05_supported(int D, int K, int L, int mode, int distance)
     return (tc_supported(D, K, L, mode, distance) || tc64_bigk_supported(D, K, L, mode, distance)) ? 1 : 0;
 }
 
+// the Gumbel-softmax launch goes to the tensor-core path (rq_gumbel_tc.cu)
+static bool gumbel_tc_taken(int64_t B, int D, int K, int L, int mode, int distance, int impl) {
+    return mode == RQ_MODE_GUMBEL_SOFTMAX && gumbel_tc_supported(D, K, L, distance) &&
+           (impl == RQ_IMPL_TCGEN05 || (impl == RQ_IMPL_AUTO && B >= 4096));
+}
+extern "C" int rq_gumbel_weights_saved(int64_t B, int D, int K, int L, int mode, int distance, int impl) {
+    return gumbel_tc_taken(B, D, K, L, mode, distance, impl) ? 1 : 0;
+}
+
 extern "C" int rq_quantize_forward(const float* x, const float* codebooks, int64_t B, int D, int K, int L, int mode,
                                    int distance, float beta, float temperature, const float* gumbel_u,
                                    uint64_t seed, uint64_t offset, float* emb_out, float* residuals, int64_t* ids,
                                    float* loss, int impl, rq_stream_t stream) {
+    return rq_quantize_forward_ws(x, codebooks, B, D, K, L, mode, distance, beta, temperature, gumbel_u, seed, offset,
+                                  emb_out, residuals, ids, loss, nullptr, impl, stream);
+}
+
+extern "C" int rq_quantize_forward_ws(const float* x, const float* codebooks, int64_t B, int D, int K, int L, int mode,
+                                      int distance, float beta, float temperature, const float* gumbel_u,
+                                      uint64_t seed, uint64_t offset, float* emb_out, float* residuals, int64_t* ids,
+                                      float* loss, float* gumbel_weights, int impl, rq_stream_t stream) {
     RQ_CHECK_ARG(B >= 0 && K >= 1 && L >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_forward: need B >= 0, K >= 1, L >= 1");
     RQ_CHECK_ARG(pow2_dim(D), RQ_ERR_UNSUPPORTED_SHAPE, "rq_quantize_forward: unsupported embed_dim D=%d (4..128, power of 2)", D);
     RQ_CHECK_ARG(mode >= RQ_MODE_EVAL && mode <= RQ_MODE_ROTATION_TRICK, RQ_ERR_INVALID_ARGUMENT,
@@ -105,9 +122,11 @@ extern "C" int rq_quantize_forward(const float* x, const float* codebooks, int64
     const bool tc_ok = tc_supported(D, K, L, mode, distance) && aligned;
     // Gumbel-softmax: GEMM-shaped contractions on the tensor cores (rq_gumbel_tc.cu) once the batch is worth the
     // [B, K] scratch; the thread-per-row family below serves small batches and the shapes outside D in {32, 64}
-    if (mode == RQ_MODE_GUMBEL_SOFTMAX && gumbel_tc_supported(D, K, L, distance) && (((uintptr_t)x & 15) == 0) &&
-        (((uintptr_t)codebooks & 15) == 0) && (impl == RQ_IMPL_TCGEN05 || (impl == RQ_IMPL_AUTO && B >= 4096)))
-        return quantize_forward_gumbel_tc(p, D, st);
+    if (gumbel_tc_taken(B, D, K, L, mode, distance, impl)) {
+        RQ_CHECK_ARG((((uintptr_t)x & 15) == 0) && (((uintptr_t)codebooks & 15) == 0) && (((uintptr_t)gumbel_weights & 15) == 0),
+                     RQ_ERR_INVALID_ARGUMENT, "rq_quantize_forward: Gumbel-softmax on the tensor cores needs 16-byte aligned x, codebooks and weights");
+        return quantize_forward_gumbel_tc(p, D, st, gumbel_weights);
+    }
     if (tc64_bigk_supported(D, K, L, mode, distance) && aligned && (impl == RQ_IMPL_TCGEN05 || (impl == RQ_IMPL_AUTO && B >= 2048)))
         return quantize_forward_tc64_bigk(p, st);
     if (impl == RQ_IMPL_TCGEN05) {
@@ -135,6 +154,15 @@ extern "C" int rq_quantize_backward_ex(const float* g_emb, const float* g_res, c
                                        int D, int K, int L, int mode, float beta, float temperature,
                                        const float* gumbel_u, uint64_t seed, uint64_t offset, float* g_x,
                                        float* g_codebooks, int flags, rq_stream_t stream) {
+    return rq_quantize_backward_ws(g_emb, g_res, g_loss, residuals, ids, codebooks, B, D, K, L, mode, beta, temperature,
+                                   gumbel_u, seed, offset, g_x, g_codebooks, nullptr, flags, stream);
+}
+
+extern "C" int rq_quantize_backward_ws(const float* g_emb, const float* g_res, const float* g_loss,
+                                       const float* residuals, const int64_t* ids, const float* codebooks, int64_t B,
+                                       int D, int K, int L, int mode, float beta, float temperature,
+                                       const float* gumbel_u, uint64_t seed, uint64_t offset, float* g_x,
+                                       float* g_codebooks, const float* gumbel_weights, int flags, rq_stream_t stream) {
     RQ_CHECK_ARG(B >= 0 && K >= 1 && L >= 1, RQ_ERR_INVALID_ARGUMENT, "rq_quantize_backward: need B >= 0, K >= 1, L >= 1");
     RQ_CHECK_ARG(pow2_dim(D), RQ_ERR_UNSUPPORTED_SHAPE, "rq_quantize_backward: unsupported embed_dim D=%d", D);
     RQ_CHECK_ARG(mode >= RQ_MODE_EVAL && mode <= RQ_MODE_ROTATION_TRICK, RQ_ERR_INVALID_ARGUMENT,
@@ -154,8 +182,12 @@ extern "C" int rq_quantize_backward_ex(const float* g_emb, const float* g_res, c
         const bool ptr_ok = (((uintptr_t)residuals & 15) == 0) && (((uintptr_t)codebooks & 15) == 0) &&
                             (!g_emb || ((uintptr_t)g_emb & 15) == 0) && (!g_res || ((uintptr_t)g_res & 15) == 0) &&
                             (((uintptr_t)g_x & 15) == 0);
-        if (!(flags & RQ_BWD_THREAD_PER_ROW) && B >= 4096 && gumbel_tc_supported(D, K, L, RQ_DIST_L2) && ptr_ok)
-            return quantize_backward_gumbel_tc(p, D, temperature, gumbel_u, seed, offset, st);
+        // saved weights exist only when the forward took the tensor-core path, whatever the batch size
+        if (!(flags & RQ_BWD_THREAD_PER_ROW) && (B >= 4096 || gumbel_weights) && gumbel_tc_supported(D, K, L, RQ_DIST_L2) &&
+            ptr_ok && (((uintptr_t)gumbel_weights & 15) == 0))
+            return quantize_backward_gumbel_tc(p, D, temperature, gumbel_u, seed, offset, st, gumbel_weights);
+        RQ_CHECK_ARG(!gumbel_weights, RQ_ERR_INVALID_ARGUMENT,
+                     "rq_quantize_backward: saved Gumbel weights are only consumed by the tensor-core path");
         return quantize_backward_gumbel(p, D, temperature, gumbel_u, seed, offset, st);
     }
     return quantize_backward_simt(p, D, st);

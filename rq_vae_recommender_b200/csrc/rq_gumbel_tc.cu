@@ -350,20 +350,21 @@ bool gumbel_tc_supported(int D, int K, int L, int distance) {
 }
 
 template <int D>
-static int gumbel_forward_tc_impl(const FwdParams& p, cudaStream_t st) {
+static int gumbel_forward_tc_impl(const FwdParams& p, cudaStream_t st, float* weights_out) {
     using namespace gtc;
     const int64_t B = p.B;
     const int K = p.K, Kp = (K + 3) & ~3;
     const size_t bytes_S = (size_t)B * Kp * 4, bytes_row = (size_t)B * D * 4;
     const size_t bytes_ct = (size_t)D * Kp * 4, bytes_cc = (size_t)Kp * 4;
     // scratch: S | r ping | r pong | emb (when the caller wants none) | C^T | cc
+    // (the [B, Kp] matrix of a level is the caller's weights buffer when there is one: the backward gets W for free)
     const size_t total = bytes_S + 2 * bytes_row + (p.emb ? 0 : bytes_row) + bytes_ct + bytes_cc + 256;
     uint8_t* scratch = (uint8_t*)engine_pool_alloc(total, st);
     if (!scratch) {
         set_error("rq_quantize_forward: out of device memory for the Gumbel-softmax scratch (%zu bytes)", total);
         return (int)cudaErrorMemoryAllocation;
     }
-    float* S = (float*)scratch;
+    float* S0 = (float*)scratch;
     float* rbuf[2] = {(float*)(scratch + bytes_S), (float*)(scratch + bytes_S + bytes_row)};
     uint8_t* cur = scratch + bytes_S + 2 * bytes_row;
     float* emb_scratch = nullptr;
@@ -375,6 +376,7 @@ static int gumbel_forward_tc_impl(const FwdParams& p, cudaStream_t st) {
     for (int l = 0; l < p.L && rc == 0; ++l) {
         const float* cbl = p.cb + (int64_t)l * K * D;
         float* emb_l = p.emb ? p.emb + (int64_t)l * B * D : emb_scratch;
+        float* S = weights_out ? weights_out + (int64_t)l * B * Kp : S0;
         {   // ids: the exact single-level distance kernel on this level's residual (quantize.py:121)
             FwdParams q;
             q.x = r_in; q.cb = cbl; q.B = B; q.K = K; q.L = 1; q.mode = RQ_MODE_EVAL; q.dist = RQ_DIST_L2;
@@ -411,14 +413,14 @@ static int gumbel_forward_tc_impl(const FwdParams& p, cudaStream_t st) {
     return rc;
 }
 
-int quantize_forward_gumbel_tc(const FwdParams& p, int D, cudaStream_t st) {
+int quantize_forward_gumbel_tc(const FwdParams& p, int D, cudaStream_t st, float* weights_out) {
     if (p.B == 0) return 0;
-    return D == 64 ? gumbel_forward_tc_impl<64>(p, st) : gumbel_forward_tc_impl<32>(p, st);
+    return D == 64 ? gumbel_forward_tc_impl<64>(p, st, weights_out) : gumbel_forward_tc_impl<32>(p, st, weights_out);
 }
 
 template <int D>
 static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const float* gu, uint64_t seed, uint64_t offset,
-                                   cudaStream_t st) {
+                                   cudaStream_t st, const float* weights) {
     using namespace gtc;
     const int64_t B = p.B, Bp = (B + 3) & ~(int64_t)3;
     const int K = p.K, Kp = (K + 3) & ~3;
@@ -433,7 +435,7 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
     }
     uint8_t* cur = scratch;
     auto take = [&](size_t n) { float* q = (float*)cur; cur += n; return q; };
-    float* W = take(bytes_S);
+    float* Wbuf = take(bytes_S);
     float* dd = take(bytes_S);
     float* Wt = take(bytes_T);
     float* ddt = take(bytes_T);
@@ -468,13 +470,16 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
         float* gcb = p.g_cb + (int64_t)l * K * D;
         codebook_prep_kernel<D><<<(Kp + 255) / 256, 256, 0, st>>>(cbl, K, Kp, cc, ct);
         RQ_LAUNCHED();
-        // forward recomputation: W and emb
-        if ((rc = split_gemm(x, cbl, W, B, K, D, D, D, Kp, 1.f, 0, 1, st))) break;
-        RowParams q;
-        q.S = W; q.r = x; q.cc = cc; q.gu = gu ? gu + (int64_t)l * B * K : nullptr;
-        q.B = B; q.K = K; q.Kp = Kp; q.level = l; q.inv_t = 1.0f / temperature; q.seed = seed; q.offset = offset;
-        gumbel_softmax_rows_kernel<D><<<rows8, 256, 0, st>>>(q);
-        RQ_LAUNCHED();
+        // W: saved by the forward, or recomputed (logits product + softmax rows)
+        const float* W = weights ? weights + (int64_t)l * B * Kp : Wbuf;
+        if (!weights) {
+            if ((rc = split_gemm(x, cbl, Wbuf, B, K, D, D, D, Kp, 1.f, 0, 1, st))) break;
+            RowParams q;
+            q.S = Wbuf; q.r = x; q.cc = cc; q.gu = gu ? gu + (int64_t)l * B * K : nullptr;
+            q.B = B; q.K = K; q.Kp = Kp; q.level = l; q.inv_t = 1.0f / temperature; q.seed = seed; q.offset = offset;
+            gumbel_softmax_rows_kernel<D><<<rows8, 256, 0, st>>>(q);
+            RQ_LAUNCHED();
+        }
         // emb = W C is needed for de and t: below the last level it is the difference of two saved residuals
         const bool have_next = (l + 1 < p.L);
         if (!have_next && (rc = split_gemm(W, ct, emb, B, D, K, Kp, Kp, D, 1.f, 0, 1, st))) break;
@@ -516,13 +521,13 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
 }
 
 int quantize_backward_gumbel_tc(const BwdParams& p, int D, float temperature, const float* gu, uint64_t seed,
-                                uint64_t offset, cudaStream_t st) {
+                                uint64_t offset, cudaStream_t st, const float* weights) {
     if (p.B == 0) {
         RQ_CUDA(cudaMemsetAsync(p.g_cb, 0, (size_t)p.L * p.K * D * sizeof(float), st));
         return 0;
     }
-    return D == 64 ? gumbel_backward_tc_impl<64>(p, temperature, gu, seed, offset, st)
-                   : gumbel_backward_tc_impl<32>(p, temperature, gu, seed, offset, st);
+    return D == 64 ? gumbel_backward_tc_impl<64>(p, temperature, gu, seed, offset, st, weights)
+                   : gumbel_backward_tc_impl<32>(p, temperature, gu, seed, offset, st, weights);
 }
 
 }  // namespace rq

@@ -89,9 +89,9 @@ int tc64_bigk_timeout_flag();
 bool tc64_bigk_supported(int D, int K, int L, int mode, int distance);
 // Gumbel-softmax on the tensor cores (rq_gumbel_tc.cu)
 bool gumbel_tc_supported(int D, int K, int L, int distance);
-int quantize_forward_gumbel_tc(const FwdParams& p, int D, cudaStream_t st);
+int quantize_forward_gumbel_tc(const FwdParams& p, int D, cudaStream_t st, float* weights_out = nullptr);
 int quantize_backward_gumbel_tc(const BwdParams& p, int D, float temperature, const float* gu, uint64_t seed,
-                                uint64_t offset, cudaStream_t st);
+                                uint64_t offset, cudaStream_t st, const float* weights = nullptr);
 int quantize_forward_tc64_bigk(const FwdParams& p, cudaStream_t st);
 void* engine_pool_alloc(size_t bytes, cudaStream_t st);     // library-owned stream-ordered pool (rq_capi.cu)
 

@@ -7,6 +7,8 @@ from __future__ import annotations
 
 from typing import Optional, Tuple
 
+import os
+
 import torch
 
 from . import _lib as L
@@ -29,11 +31,13 @@ def quantize_forward(x: torch.Tensor, codebooks: torch.Tensor, mode: int = MODE_
                      temperature: float = 0.2, distance: int = DIST_L2,
                      gumbel_uniform: Optional[torch.Tensor] = None, seed: int = 0, offset: int = 0,
                      want_embeddings: bool = True, want_residuals: bool = True, want_loss: bool = True,
-                     impl: int = IMPL_AUTO):
+                     impl: int = IMPL_AUTO, gumbel_weights_out: Optional[torch.Tensor] = None):
     """Fused L-level residual quantisation (rq_quantize_forward).
 
     x [B,D] fp32, codebooks [L,K,D] fp32 (effective).  Returns (emb [L,B,D]|None,
-    residuals [L,B,D]|None, ids [L,B] int64, loss [B]|None)."""
+    residuals [L,B,D]|None, ids [L,B] int64, loss [B]|None).  `gumbel_weights_out` ([L, B, Kp] fp32 from
+    `gumbel_weights_buffer`) receives the softmax weights of a Gumbel-softmax launch on the tensor cores, for
+    `quantize_backward(..., gumbel_weights=)`."""
     x = _f32c(x, "x")
     codebooks = _f32c(codebooks, "codebooks")
     if x.dim() != 2 or codebooks.dim() != 3:
@@ -51,18 +55,31 @@ def quantize_forward(x: torch.Tensor, codebooks: torch.Tensor, mode: int = MODE_
         res = torch.empty((Lv, B, D), device=dev, dtype=torch.float32) if want_residuals else None
         ids = torch.empty((Lv, B), device=dev, dtype=torch.int64)
         loss = torch.empty((B,), device=dev, dtype=torch.float32) if want_loss else None
-        rc = L.lib().rq_quantize_forward(L.ptr(x), L.ptr(codebooks), B, D, K, Lv, int(mode), int(distance),
-                                         float(beta), float(temperature), L.ptr(gumbel_uniform), int(seed),
-                                         int(offset), L.ptr(emb), L.ptr(res), L.ptr(ids), L.ptr(loss), int(impl),
-                                         L.stream_of(x))
+        rc = L.lib().rq_quantize_forward_ws(L.ptr(x), L.ptr(codebooks), B, D, K, Lv, int(mode), int(distance),
+                                            float(beta), float(temperature), L.ptr(gumbel_uniform), int(seed),
+                                            int(offset), L.ptr(emb), L.ptr(res), L.ptr(ids), L.ptr(loss),
+                                            L.ptr(gumbel_weights_out), int(impl), L.stream_of(x))
     L.check(rc, "rq_quantize_forward")
     return emb, res, ids, loss
+
+
+def gumbel_weights_buffer(x: torch.Tensor, codebooks: torch.Tensor, mode: int, distance: int = DIST_L2,
+                          impl: int = IMPL_AUTO) -> Optional[torch.Tensor]:
+    """The [L, B, Kp] buffer `quantize_forward(..., gumbel_weights_out=)` fills when the launch takes the tensor-core
+    Gumbel-softmax path (rq_gumbel_weights_saved), else None.  What autograd keeps alive in the reference: the output of
+    F.softmax (modules/quantize.py:127), 4 B K bytes per level."""
+    B, D = x.shape
+    Lv, K, _ = codebooks.shape
+    if not L.lib().rq_gumbel_weights_saved(B, D, K, Lv, int(mode), int(distance), int(impl)):
+        return None
+    return torch.empty((Lv, B, (K + 3) & ~3), device=x.device, dtype=torch.float32)
 
 
 def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, beta, temperature,
                       gumbel_uniform=None, seed: int = 0, offset: int = 0,
                       g_codebooks_out: Optional[torch.Tensor] = None,
-                      accumulate: bool = False, thread_per_row: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+                      accumulate: bool = False, thread_per_row: bool = False,
+                      gumbel_weights: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """rq_quantize_backward: returns (g_x [B,D], g_codebooks [L,K,D]).  `g_codebooks_out` (contiguous fp32
     [L,K,D]) receives the codebook gradient in place — e.g. a persistent all-reduce bucket.  `accumulate=True` adds
     to what `g_codebooks_out` holds instead of overwriting it (gradient accumulation; with a buffer zeroed BEFORE the
@@ -89,9 +106,14 @@ def quantize_backward(g_emb, g_res, g_loss, residuals, ids, codebooks, mode, bet
                 raise L.RqEngineError(f"g_codebooks_out must be contiguous [L,K,D]={Lv, K, D}")
         if accumulate and g_codebooks_out is None:
             raise L.RqEngineError("quantize_backward: accumulate=True needs g_codebooks_out")
-        rc = L.lib().rq_quantize_backward_ex(L.ptr(g_emb), L.ptr(g_res), L.ptr(g_loss), L.ptr(residuals), L.ptr(ids),
+        if gumbel_weights is not None:
+            gumbel_weights = L.require_cuda(gumbel_weights, "gumbel_weights", torch.float32)
+            if tuple(gumbel_weights.shape) != (Lv, B, (K + 3) & ~3) or not gumbel_weights.is_contiguous():
+                raise L.RqEngineError(f"gumbel_weights must be contiguous [L,B,Kp]={Lv, B, (K + 3) & ~3}")
+        rc = L.lib().rq_quantize_backward_ws(L.ptr(g_emb), L.ptr(g_res), L.ptr(g_loss), L.ptr(residuals), L.ptr(ids),
                                              L.ptr(codebooks), B, D, K, Lv, int(mode), float(beta), float(temperature),
                                              L.ptr(gumbel_uniform), int(seed), int(offset), L.ptr(g_x), L.ptr(g_cb),
+                                             L.ptr(gumbel_weights),
                                              (1 if accumulate else 0) | (2 if thread_per_row else 0),
                                              L.stream_of(residuals))
     L.check(rc, "rq_quantize_backward")
@@ -107,8 +129,14 @@ class ResidualQuantizeFn(torch.autograd.Function):
         # the codebook gradient is zeroed HERE, ahead of the forward kernel: nothing but the caller's own kernels then
         # sits between the fused forward and the fused backward, whose launch PDL overlaps with its predecessor's tail
         ctx.g_cb = torch.zeros_like(codebooks) if mode != MODE_GUMBEL_SOFTMAX else None
+        # Gumbel-softmax on the tensor cores: the softmax weights are kept for the backward, as autograd keeps the output
+        # of F.softmax in the reference (RQ_GUMBEL_RECOMPUTE=1 trades them for a recomputation: 4 B K bytes per level)
+        w_buf = None
+        if mode == MODE_GUMBEL_SOFTMAX and not os.environ.get("RQ_GUMBEL_RECOMPUTE"):
+            w_buf = gumbel_weights_buffer(x, codebooks, mode, distance, impl)
         emb, res, ids, loss = quantize_forward(x, codebooks, mode, beta, temperature, distance, gumbel_uniform,
-                                               seed, offset, True, True, True, impl)
+                                               seed, offset, True, True, True, impl, gumbel_weights_out=w_buf)
+        ctx.gumbel_w = w_buf
         ctx.save_for_backward(res, ids, codebooks, gumbel_uniform if gumbel_uniform is not None else x.new_empty(0))
         ctx.cfg = (mode, beta, temperature, gumbel_uniform is not None, seed, offset)
         ctx.mark_non_differentiable(ids)
@@ -122,9 +150,10 @@ class ResidualQuantizeFn(torch.autograd.Function):
         res, ids, codebooks, gu = ctx.saved_tensors
         mode, beta, temperature, has_gu, seed, offset = ctx.cfg
         g_cb_buf, ctx.g_cb = ctx.g_cb, None
+        w_buf, ctx.gumbel_w = ctx.gumbel_w, None
         g_x, g_cb = quantize_backward(g_emb, g_res, g_loss, res, ids, codebooks, mode, beta, temperature,
                                       gu if has_gu else None, seed, offset, g_codebooks_out=g_cb_buf,
-                                      accumulate=g_cb_buf is not None)
+                                      accumulate=g_cb_buf is not None, gumbel_weights=w_buf)
         return g_x, g_cb, None, None, None, None, None, None, None, None
 
 

@@ -148,3 +148,31 @@ def test_gumbel_backward_tensor_core_vs_thread_per_row(B, D, K, L, noise):
     torch.cuda.synchronize()
     assert_close(gx2, gx1, "g_x", tol=2e-4)
     assert_close(gc2, gc1, "g_codebooks", tol=2e-4)
+
+
+@pytest.mark.parametrize("B,D,K,L", [(5000, 64, 1024, 4), (4097, 32, 254, 3)])
+def test_gumbel_saved_weights_equal_recomputation(B, D, K, L):
+    """rq_quantize_forward_ws / rq_quantize_backward_ws: the backward fed with the forward's softmax weights returns
+    what the recomputing backward returns (same kernels downstream of W), and the autograd Function uses them."""
+    g = torch.Generator().manual_seed(B + K + 2)
+    x = torch.randn(B, D, generator=g).to(DEV)
+    cbs = torch.stack(synthetic_codebooks(torch.randn(max(4 * K, 2048), D, generator=g), L, K, seed=3)).to(DEV)
+    g_emb = torch.randn(L, B, D, generator=g).to(DEV)
+    g_loss = torch.rand(B, generator=g).to(DEV)
+    M = RF.MODE_GUMBEL_SOFTMAX
+    w = RF.gumbel_weights_buffer(x, cbs, M)
+    assert w is not None and tuple(w.shape) == (L, B, (K + 3) & ~3)
+    emb, res, ids, loss = RF.quantize_forward(x, cbs, M, 0.25, 0.2, seed=4, offset=9, gumbel_weights_out=w)
+    assert_close(w[:, :, :K].sum(-1).cpu(), torch.ones(L, B), "rows of W sum to one", tol=1e-5)
+    args = (g_emb, None, g_loss, res, ids, cbs, M, 0.25, 0.2)
+    gx1, gc1 = RF.quantize_backward(*args, seed=4, offset=9)
+    gx2, gc2 = RF.quantize_backward(*args, seed=4, offset=9, gumbel_weights=w)
+    assert_close(gx2, gx1, "g_x", tol=1e-5)
+    assert_close(gc2, gc1, "g_codebooks", tol=1e-5)
+    # through autograd
+    xr, cr = x.clone().requires_grad_(True), cbs.clone().requires_grad_(True)
+    e, r, i, l = RF.residual_quantize(xr, cr, M, 0.25, 0.2, RF.DIST_L2, None, 4, 9)
+    ((e * g_emb).sum() + (l * g_loss).sum()).backward()
+    assert_close(xr.grad, gx1, "autograd g_x", tol=1e-5)
+    assert_close(cr.grad, gc1, "autograd g_codebooks", tol=1e-5)
+    assert RF.gumbel_weights_buffer(x[:100], cbs, M) is None            # small batches: thread-per-row kernels, nothing saved

@@ -27,9 +27,12 @@ for (B, D, K, L) in ((65536, 64, 1024, 4), (65536, 32, 256, 3), (16384, 64, 1024
     M = RF.MODE_GUMBEL_SOFTMAX
     emb, res, ids, loss = RF.quantize_forward(x, cb, M, 0.25, 0.2, seed=1, offset=2)
     out = []
-    for name, impl, tpr in (("tensor cores", RF.IMPL_TCGEN05, False), ("thread per row", RF.IMPL_SIMT, True)):
-        f = timed(lambda: RF.quantize_forward(x, cb, M, 0.25, 0.2, seed=1, offset=2, impl=impl))
+    w = RF.gumbel_weights_buffer(x, cb, M, impl=RF.IMPL_TCGEN05)
+    RF.quantize_forward(x, cb, M, 0.25, 0.2, seed=1, offset=2, impl=RF.IMPL_TCGEN05, gumbel_weights_out=w)
+    for name, impl, tpr, ww in (("tensor cores, weights kept", RF.IMPL_TCGEN05, False, w), ("tensor cores, recompute", RF.IMPL_TCGEN05, False, None),
+                                ("thread per row", RF.IMPL_SIMT, True, None)):
+        f = timed(lambda: RF.quantize_forward(x, cb, M, 0.25, 0.2, seed=1, offset=2, impl=impl, gumbel_weights_out=ww))
         b = timed(lambda: RF.quantize_backward(g_emb, None, g_loss, res, ids, cb, M, 0.25, 0.2, seed=1, offset=2,
-                                               thread_per_row=tpr))
+                                               thread_per_row=tpr, gumbel_weights=ww))
         out.append(f"{name}: fwd {f:.3f} + bwd {b:.3f} = {f + b:.3f} ms ({B / (f + b) / 1e3:.1f} M items/s)")
     print(f"B={B} D={D} K={K} L={L}  " + " | ".join(out))
