@@ -247,7 +247,9 @@ static cudaMemPool_t host_entry_pool() {
         props.location.id = dev;
         cudaMemPool_t pool = nullptr;
         if (cudaMemPoolCreate(&pool, &props) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-        uint64_t keep = 1ull << 30;                     // up to 1 GiB stays cached between calls
+        // up to 4 GiB stays cached between calls: the Gumbel-softmax backward's [B, K] scratch is 1.1 GB at 65,536 x 1,024
+        // and would otherwise be handed back to the driver at every synchronisation
+        uint64_t keep = 4ull << 30;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
         pools[dev] = pool;
     }
