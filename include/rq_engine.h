@@ -267,6 +267,28 @@ int rq_debug_tc_set_timeline(long long* device_buf_32x64);
 int rq_debug_split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda,
                         int64_t ldb, int64_t ldc, float alpha, int atomic, int k_splits, rq_stream_t stream);
 
+/* ---- encoder layer ---------------------------------------------------------------------------
+ * y[rows, out] = act(x[rows, in] * weight[out, in]^T): one bias-free Linear of the reference's MLP
+ * (modules/encoder.py:17-32, reached from RqVae.encode, modules/rqvae.py:117-118) with its activation fused into the
+ * GEMM epilogue.  fp32 row-major contiguous device buffers, 16-byte aligned; in / out multiples of 4.  The product is
+ * computed in TF32 on the tensor cores - the precision the reference selects for these matmuls
+ * (torch.set_float32_matmul_precision('high'), modules/rqvae.py:19).
+ *   RQ_ACT_NONE    plain Linear (the last layer when normalize=False)
+ *   RQ_ACT_SILU    Linear + nn.SiLU (encoder.py:22-23)
+ *   RQ_ACT_L2NORM  Linear + L2NormalizationLayer (encoder.py:27, modules/normalize.py:9-13: x / max(|x|, 1e-12)); out <= 64
+ * OR-ing RQ_ACT_TF32_OUT into act (NONE / SILU only) rounds every output to the nearest value with a 10-bit significand:
+ * the next layer's tensor-core product then reads its operand without the truncation it would otherwise apply, which
+ * makes a chain of layers unbiased (round-to-nearest) where back-to-back TF32 GEMMs truncate.  Use it for hidden
+ * activations that only the next rq_encoder_layer call consumes.
+ * rq_encoder_layer_supported returns 1 when rq_encoder_layer accepts the shape. */
+#define RQ_ACT_NONE 0
+#define RQ_ACT_SILU 1
+#define RQ_ACT_L2NORM 2
+#define RQ_ACT_TF32_OUT 0x10
+int rq_encoder_layer_supported(int64_t rows, int in_features, int out_features, int act);
+int rq_encoder_layer(const float* x, const float* weight, float* y, int64_t rows, int in_features, int out_features,
+                     int act, rq_stream_t stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

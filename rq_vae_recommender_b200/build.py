@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "librqengine.so")
 OBJ = os.path.join(HERE, "build")
-SOURCES = ["rq_capi.cu", "rq_quantize_simt.cu", "rq_quantize_tc.cu", "rq_quantize_tc32.cu", "rq_quantize_tc64.cu", "rq_quantize_bigk.cu", "rq_quantize_bwd.cu", "rq_gumbel_bwd.cu", "rq_gemm_split.cu", "rq_gumbel_tc.cu", "rq_kmeans.cu",
+SOURCES = ["rq_capi.cu", "rq_quantize_simt.cu", "rq_quantize_tc.cu", "rq_quantize_tc32.cu", "rq_quantize_tc64.cu", "rq_quantize_bigk.cu", "rq_quantize_bwd.cu", "rq_gumbel_bwd.cu", "rq_gemm_split.cu", "rq_gumbel_tc.cu", "rq_linear_tf32.cu", "rq_kmeans.cu",
            "rq_tokenizer.cu", "rq_peer.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr",

@@ -95,4 +95,9 @@ int quantize_backward_gumbel_tc(const BwdParams& p, int D, float temperature, co
 int quantize_forward_tc64_bigk(const FwdParams& p, cudaStream_t st);
 void* engine_pool_alloc(size_t bytes, cudaStream_t st);     // library-owned stream-ordered pool (rq_capi.cu)
 
+// rq_linear_tf32.cu: one encoder layer, Y = act(X W^T) in TF32 with the activation fused (act: RQ_ACT_*)
+bool linear_tf32_supported(int64_t M, int N, int Kd, int act);
+int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, int Kd, int act, cudaStream_t st);
+int linear_tf32_timeout_flag();
+
 }  // namespace rq

@@ -283,7 +283,7 @@ int quantize_forward_tc32(const FwdParams& p, cudaStream_t st) {
 extern "C" int rq_debug_tc_timeout_flag(void) {
     int v = 0;
     if (rq::d_err) cudaMemcpy(&v, rq::d_err, sizeof(int), cudaMemcpyDeviceToHost);
-    return v | rq::tc32_timeout_flag() | rq::tc64_timeout_flag() | rq::tc64_bigk_timeout_flag();
+    return v | rq::tc32_timeout_flag() | rq::tc64_timeout_flag() | rq::tc64_bigk_timeout_flag() | rq::linear_tf32_timeout_flag();
 }
 extern "C" int rq_debug_tc_set_accumulator_dump(float* device_buf_128x256) {
     rq::tc32_set_accumulator_dump(device_buf_128x256);

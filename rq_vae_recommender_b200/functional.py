@@ -317,3 +317,29 @@ def gather_tokens(table: torch.Tensor, item_ids: torch.Tensor, seq_mask: Optiona
 
 
 from . import ops as _ops  # noqa: E402  (torch.library registration; imports this module back)
+
+
+ACT_NONE, ACT_SILU, ACT_L2NORM, ACT_TF32_OUT = 0, 1, 2, 0x10
+
+
+def encoder_layer_supported(rows: int, in_features: int, out_features: int, act: int) -> bool:
+    return bool(L.lib().rq_encoder_layer_supported(int(rows), int(in_features), int(out_features), int(act)))
+
+
+def encoder_layer(x: torch.Tensor, weight: torch.Tensor, act: int = ACT_NONE, out: Optional[torch.Tensor] = None):
+    """act(x @ weight.T) for one bias-free Linear of the MLP (rq_encoder_layer; modules/encoder.py:17-32): TF32 tensor-core
+    product with SiLU / the final L2 normalisation fused.  x [rows, in], weight [out, in] fp32 CUDA; no autograd."""
+    x = _f32c(x, "x")
+    weight = _f32c(weight, "weight")
+    if x.dim() != 2 or weight.dim() != 2 or x.shape[1] != weight.shape[1]:
+        raise L.RqEngineError(f"encoder_layer: x {tuple(x.shape)} and weight {tuple(weight.shape)} do not match")
+    rows, n_in = x.shape
+    n_out = weight.shape[0]
+    if out is None:
+        out = torch.empty((rows, n_out), device=x.device, dtype=torch.float32)
+    elif out.shape != (rows, n_out) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != x.device:
+        raise L.RqEngineError("encoder_layer: out must be a contiguous fp32 [rows, out_features] tensor on x's device")
+    with torch.cuda.device(x.device):
+        rc = L.lib().rq_encoder_layer(L.ptr(x), L.ptr(weight), L.ptr(out), rows, n_in, n_out, int(act), L.stream_of(x))
+    L.check(rc, "rq_encoder_layer")
+    return out
