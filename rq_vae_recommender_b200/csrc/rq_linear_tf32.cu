@@ -6,13 +6,15 @@
 // memory by TMA and into the MMA untouched: no conversion pass, no staging through registers.
 //
 // Persistent CTAs of ten warps:
-//   warp 0 (one lane)  TMA producer: 128 x 32 fp32 box of X and NT x 32 box of W per K-block into a ring of stages
+//   warp 0 (one lane)  TMA producer: 256 x 32 fp32 box of X and NT x 32 box of W per K-block into a ring of stages
 //                      (128-byte swizzle = the UMMA K-major SW128 layout; rows/columns outside the matrix arrive as 0);
-//   warp 1 (one lane)  issues 4 tcgen05.mma (K = 8 each) per K-block into one of two TMEM accumulators, commits the
-//                      stage back to the producer and, after the last K-block, the accumulator to the epilogue;
-//   warps 2-9          epilogue (two warps per TMEM lane quadrant, alternate 32-column chunks): tcgen05.ld, activation,
-//                      16-byte stores (thread = output row),
-//                      then hand the accumulator back - the next tile's MMAs run under this tile's epilogue.
+//   warp 1 (one lane)  issues 2 x 4 tcgen05.mma (K = 8 each; the two 128-row halves of X against the same W stage) per
+//                      K-block into a pair of TMEM accumulators, commits the stage back to the producer and, after the
+//                      last K-block, the pair to the epilogue.  A 256-row tile doubles the flops per byte staged, which
+//                      is what the ring depth needs: 128-row tiles left the tensor pipe 32 % busy waiting for data;
+//   warps 2-9          epilogue, one warp per TMEM lane quadrant and half: tcgen05.ld 32 columns at a time, activation,
+//                      a swizzled 4 KB staging tile per warp and a TMA store of it, then hand the pair back.  Tiles up to 128 columns wide keep
+//                      two accumulator pairs in TMEM, so the next tile's MMAs run under this tile's epilogue.
 // Tiles are numbered with the N index fastest, so the CTAs that share an X tile run at the same time and the second
 // read of it is an L2 hit.
 //
@@ -27,17 +29,18 @@
 namespace rq {
 
 namespace lt {
-constexpr int TM = 128;            // rows per tile (UMMA M)
+constexpr int TM = 256;            // rows per tile: two UMMA M = 128 halves that share every W stage
 constexpr int KB = 32;             // fp32 contraction elements per K-block: one 128-byte swizzled row
 constexpr int THREADS = 320;          // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quadrant)
 constexpr int MAX_STAGES = 8;
-constexpr int A_STAGE = TM * KB * 4;                                   // 16 KB
+constexpr int A_STAGE = TM * KB * 4;                                   // 32 KB: one TMA box, halves 16 KB apart
+constexpr int OUT_STAGE = 8 * 32 * 128;                                // the epilogue warps' staging tiles
 __host__ __device__ constexpr int b_stage_bytes(int NT) { return (NT * KB * 4 + 1023) & ~1023; }
 
 struct Params {
     float* C;
     int64_t M, ldc;
-    int N, Kd, NT, n_tiles_n, stages, act, round_out;
+    int N, Kd, NT, n_tiles_n, stages, act, round_out, nbuf;
     int64_t tiles;
     int* timeout_flag;
 };
@@ -63,12 +66,14 @@ __device__ __forceinline__ float round_tf32(float v) {
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
-rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w, Params p) {
+rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                      const __grid_constant__ CUtensorMap map_c, Params p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int b_stage = b_stage_bytes(p.NT);
     const int stage_bytes = A_STAGE + b_stage;
-    Bars* bars = reinterpret_cast<Bars*>(smem + (size_t)p.stages * stage_bytes);
+    uint8_t* out_stage = smem + (size_t)p.stages * stage_bytes;                    // 8 epilogue warps x 4 KB
+    Bars* bars = reinterpret_cast<Bars*>(out_stage + OUT_STAGE);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nkb = (p.Kd + KB - 1) / KB;
 
@@ -85,6 +90,7 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         ptx::fence_mbar_init();
         ptx::prefetch_tensormap(&map_a);
         ptx::prefetch_tensormap(&map_w);
+        ptx::prefetch_tensormap(&map_c);
     }
     if (warp == 1) ptx::tmem_alloc(&bars->tmem_base, 512);
     ptx::tc_fence_before_sync();
@@ -110,11 +116,12 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = ptx::make_idesc_tf32_f32(TM, p.NT);
+            const uint32_t idesc = ptx::make_idesc_tf32_f32(128, p.NT);
             uint32_t it = 0, tcount = 0;
             for (int64_t tile = blockIdx.x; tile < p.tiles && !bars->abort; tile += gridDim.x, ++tcount) {
-                const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
+                const uint32_t buf = tcount % p.nbuf, aph = (tcount / p.nbuf) & 1;
                 if (!ptx::mbar_wait(&bars->acc_empty[buf], aph ^ 1)) { bars->abort = 1; break; }
+                const uint32_t acc = tmem + buf * 2 * p.NT;
                 ptx::tc_fence_after_sync();
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int s = it % p.stages;
@@ -124,9 +131,12 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
                     const uint32_t a0 = ptx::smem_u32(smem + (size_t)s * stage_bytes), b0 = a0 + A_STAGE;
 #pragma unroll
                     for (int k4 = 0; k4 < KB / 8; ++k4) {
-                        const uint64_t ad = ptx::make_smem_desc(a0 + k4 * 32, 16, 1024, ptx::kLayoutSw128);
                         const uint64_t bd = ptx::make_smem_desc(b0 + k4 * 32, 16, 1024, ptx::kLayoutSw128);
-                        ptx::umma_tf32(tmem + buf * 256, ad, bd, idesc, (kb | k4) != 0);
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const uint64_t ad = ptx::make_smem_desc(a0 + h * (A_STAGE / 2) + k4 * 32, 16, 1024, ptx::kLayoutSw128);
+                            ptx::umma_tf32(acc + h * p.NT, ad, bd, idesc, (kb | k4) != 0);
+                        }
                     }
                     ptx::umma_commit(&bars->empty[s]);
                 }
@@ -135,22 +145,37 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         }
     } else {
         const int q = warp & 3;                                  // the TMEM lane quadrant this warp may read
-        const int half = (warp - 2) >> 2;                        // even / odd 32-column chunks of the tile
+        const int half = (warp - 2) >> 2;                        // which 128-row half (accumulator) of the tile
+        uint8_t* my_out = out_stage + (warp - 2) * 4096;
         uint32_t tcount = 0;
         for (int64_t tile = blockIdx.x; tile < p.tiles && !bars->abort; tile += gridDim.x, ++tcount) {
-            const uint32_t buf = tcount & 1, aph = (tcount >> 1) & 1;
-            const int64_t row = (tile / p.n_tiles_n) * TM + q * 32 + lane;
+            const uint32_t buf = tcount % p.nbuf, aph = (tcount / p.nbuf) & 1;
+            const int64_t row = (tile / p.n_tiles_n) * TM + half * 128 + q * 32 + lane;
             const int n0 = (int)(tile % p.n_tiles_n) * p.NT;
             if (!ptx::mbar_wait(&bars->acc_full[buf], aph)) { bars->abort = 1; break; }
             ptx::tc_fence_after_sync();
-            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + buf * 256;
-            float* crow = p.C + row * p.ldc + n0;
+            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + buf * 2 * p.NT + half * p.NT;
             const int ncols = min(p.NT, p.N - n0);
-            if (p.act == RQ_ACT_L2NORM && half) {                // the row-wise norm is one thread's job: half 0 does it
-                ptx::tc_fence_before_sync();
+            const int row0 = (int)(tile / p.n_tiles_n) * TM + half * 128 + q * 32;       // this warp's first row
+            // one 32-row x 32-column chunk: registers -> this warp's 4 KB staging tile (128-byte rows, 16-byte pieces
+            // XOR-swizzled by the row so that the 32 lanes' v4 stores are conflict-free) -> one TMA store, which writes
+            // whole 128-byte lines and clips at the matrix edge.  (Thread-per-row st.global hit 32 lines per instruction
+            // and left the epilogue warps waiting on the store queue.)
+            auto put_chunk = [&](const float (&v)[32], int c0) {
+                if (lane == 0) ptx::bulk_wait_group_read0();                 // the previous chunk has left the staging tile
                 __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&bars->acc_empty[buf]);
-            } else if (p.act == RQ_ACT_L2NORM) {                 // the whole row is in this tile (N <= 64, host-checked)
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<float4*>(my_out + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                ptx::fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    ptx::tma_store_2d(&map_c, n0 + c0, row0, my_out);
+                    ptx::bulk_commit_group();
+                }
+            };
+            if (p.act == RQ_ACT_L2NORM) {                        // the whole row is in this tile (N <= 64, host-checked)
                 uint32_t r0[32], r1[32];
                 ptx::tmem_ld_32x32b_x32(tbase, r0);
                 if (p.NT > 32) ptx::tmem_ld_32x32b_x32(tbase + 32, r1);
@@ -170,46 +195,39 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
                 for (int j = 0; j < 32; ++j)
                     if (32 + j < ncols) ss = fmaf(__uint_as_float(r1[j]), __uint_as_float(r1[j]), ss);
                 const float inv = 1.f / fmaxf(sqrtf(ss), 1e-12f);         // F.normalize(p=2, eps=1e-12)
-                if (row < p.M) {
+                float v[32];
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4)
-                        if (j + 3 < ncols)
-                            ptx::st_global_v4(crow + j, make_float4(__uint_as_float(r0[j]) * inv, __uint_as_float(r0[j + 1]) * inv,
-                                                                    __uint_as_float(r0[j + 2]) * inv, __uint_as_float(r0[j + 3]) * inv));
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r0[j]) * inv;
+                put_chunk(v, 0);
+                if (ncols > 32) {
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4)
-                        if (32 + j + 3 < ncols)
-                            ptx::st_global_v4(crow + 32 + j, make_float4(__uint_as_float(r1[j]) * inv, __uint_as_float(r1[j + 1]) * inv,
-                                                                         __uint_as_float(r1[j + 2]) * inv, __uint_as_float(r1[j + 3]) * inv));
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r1[j]) * inv;
+                    put_chunk(v, 32);
                 }
             } else {
-                if (half * 32 >= p.NT) {                         // a one-chunk tile: nothing for the odd half
-                    ptx::tc_fence_before_sync();
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(&bars->acc_empty[buf]);
-                }
-                for (int c0 = half * 32; c0 < p.NT; c0 += 64) {
+                for (int c0 = 0; c0 < p.NT; c0 += 32) {
                     uint32_t r[32];
                     ptx::tmem_ld_32x32b_x32(tbase + c0, r);
                     ptx::tmem_ld_wait_for(r);
-                    if (c0 + 64 >= p.NT) {                       // this warp's last read of the accumulator: give it back
+                    if (c0 + 32 >= p.NT) {                       // this warp's last read of the accumulator: give it back
                         ptx::tc_fence_before_sync();
                         __syncwarp();
                         if (lane == 0) ptx::mbar_arrive(&bars->acc_empty[buf]);
                     }
-                    if (row < p.M) {
+                    if (c0 >= ncols) continue;
+                    float v[32];
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                                   __uint_as_float(r[j + 3]));
-                            if (p.act == RQ_ACT_SILU) v = make_float4(silu(v.x), silu(v.y), silu(v.z), silu(v.w));
-                            if (p.round_out) v = make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
-                            if (c0 + j + 3 < ncols) ptx::st_global_v4(crow + c0 + j, v);
-                        }
+                    for (int j = 0; j < 32; ++j) {
+                        float t = __uint_as_float(r[j]);
+                        if (p.act == RQ_ACT_SILU) t = silu(t);
+                        if (p.round_out) t = round_tf32(t);
+                        v[j] = t;
                     }
+                    put_chunk(v, c0);
                 }
             }
         }
+        if (lane == 0) ptx::bulk_wait_group0();                  // every store of this warp has landed
     }
     __syncwarp();
     ptx::tc_fence_before_sync();
@@ -237,6 +255,7 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 // [rows, cols] fp32 row-major (leading dimension ld floats), boxes of box_rows x 32 floats, 128-byte swizzle
 static bool make_map(CUtensorMap* m, const float* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+    if (ld % 4) return false;
     EncodeTiledFn fn = encode_tiled_fn();
     if (!fn) return false;
     const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -268,15 +287,19 @@ int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, 
     RQ_CHECK_ARG(!((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(Y)) & 15),
                  RQ_ERR_INVALID_ARGUMENT, "encoder layer: x, weight and y must be 16-byte aligned");
     Params p{};
-    p.NT = N >= 256 ? 256 : ((N + 15) & ~15);
+    // 256-wide tiles when the layer is MMA-heavy (one accumulator pair fills TMEM); otherwise <= 128 so that two pairs fit
+    // and the epilogue of one tile runs under the MMAs of the next
+    p.NT = N >= 512 ? 256 : (N >= 128 ? 128 : ((N + 15) & ~15));
+    p.nbuf = 2 * p.NT <= 256 ? 2 : 1;
     p.n_tiles_n = (N + p.NT - 1) / p.NT;
     p.C = Y; p.M = M; p.ldc = N; p.N = N; p.Kd = Kd; p.act = act & ~RQ_ACT_TF32_OUT; p.round_out = (act & RQ_ACT_TF32_OUT) ? 1 : 0;
     p.tiles = ((M + TM - 1) / TM) * p.n_tiles_n;
     const int stage_bytes = A_STAGE + b_stage_bytes(p.NT);
-    p.stages = std::min<int>(MAX_STAGES, (200 * 1024) / stage_bytes);
-    const size_t smem = (size_t)p.stages * stage_bytes + sizeof(Bars) + 1024;
-    CUtensorMap ma, mw;
-    RQ_CHECK_ARG(make_map(&ma, X, M, Kd, Kd, TM) && make_map(&mw, W, N, Kd, Kd, p.NT), (int)cudaErrorInvalidValue,
+    p.stages = std::min<int>(MAX_STAGES, (224 * 1024 - OUT_STAGE) / stage_bytes);
+    const size_t smem = (size_t)p.stages * stage_bytes + OUT_STAGE + sizeof(Bars) + 1024;
+    CUtensorMap ma, mw, mc;
+    RQ_CHECK_ARG(make_map(&ma, X, M, Kd, Kd, TM) && make_map(&mw, W, N, Kd, Kd, p.NT) && make_map(&mc, Y, M, N, N, 32),
+                 (int)cudaErrorInvalidValue,
                  "encoder layer: cuTensorMapEncodeTiled failed (rows=%lld in=%d out=%d)", (long long)M, Kd, N);
     RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_linear_tf32_kernel, (int)smem));
     if (!g_timeout_flag) {
@@ -285,7 +308,7 @@ int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, 
     }
     p.timeout_flag = g_timeout_flag;
     const int grid = (int)std::min<int64_t>(p.tiles, sm_count());
-    rq_linear_tf32_kernel<<<grid, THREADS, smem, st>>>(ma, mw, p);
+    rq_linear_tf32_kernel<<<grid, THREADS, smem, st>>>(ma, mw, mc, p);
     RQ_LAUNCHED();
     return 0;
 }
