@@ -40,7 +40,7 @@ __host__ __device__ constexpr int b_stage_bytes(int NT) { return (NT * KB * 4 + 
 struct Params {
     float* C;
     int64_t M, ldc;
-    int N, Kd, NT, n_tiles_n, stages, act, round_out, nbuf;
+    int N, Kd, NT, n_tiles_n, stages, act, round_out, nbuf, halves;
     int64_t tiles;
     int* timeout_flag;
 };
@@ -71,7 +71,8 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int b_stage = b_stage_bytes(p.NT);
-    const int stage_bytes = A_STAGE + b_stage;
+    const int a_stage = p.halves * (A_STAGE / 2), tile_rows = p.halves * 128;
+    const int stage_bytes = a_stage + b_stage;
     uint8_t* out_stage = smem + (size_t)p.stages * stage_bytes;                    // 8 epilogue warps x 4 KB
     Bars* bars = reinterpret_cast<Bars*>(out_stage + OUT_STAGE);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -84,7 +85,7 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         }
         for (int b = 0; b < 2; ++b) {
             ptx::mbar_init(&bars->acc_full[b], 1);
-            ptx::mbar_init(&bars->acc_empty[b], 8);           // one arrival per epilogue warp
+            ptx::mbar_init(&bars->acc_empty[b], 4 * p.halves);   // one arrival per working epilogue warp
         }
         bars->abort = 0;
         ptx::fence_mbar_init();
@@ -102,15 +103,15 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         if (lane == 0) {
             uint32_t it = 0;
             for (int64_t tile = blockIdx.x; tile < p.tiles && !bars->abort; tile += gridDim.x) {
-                const int m0 = (int)(tile / p.n_tiles_n) * TM, n0 = (int)(tile % p.n_tiles_n) * p.NT;
+                const int m0 = (int)(tile / p.n_tiles_n) * tile_rows, n0 = (int)(tile % p.n_tiles_n) * p.NT;
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int s = it % p.stages;
                     const uint32_t ph = (it / p.stages) & 1;
                     if (!ptx::mbar_wait(&bars->empty[s], ph ^ 1)) { bars->abort = 1; break; }
                     uint8_t* sa = smem + (size_t)s * stage_bytes;
-                    ptx::mbar_arrive_expect_tx(&bars->full[s], (uint32_t)(A_STAGE + p.NT * KB * 4));
+                    ptx::mbar_arrive_expect_tx(&bars->full[s], (uint32_t)(a_stage + p.NT * KB * 4));
                     ptx::tma_load_2d(sa, &map_a, kb * KB, m0, &bars->full[s]);
-                    ptx::tma_load_2d(sa + A_STAGE, &map_w, kb * KB, n0, &bars->full[s]);
+                    ptx::tma_load_2d(sa + a_stage, &map_w, kb * KB, n0, &bars->full[s]);
                 }
             }
         }
@@ -121,19 +122,20 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
             for (int64_t tile = blockIdx.x; tile < p.tiles && !bars->abort; tile += gridDim.x, ++tcount) {
                 const uint32_t buf = tcount % p.nbuf, aph = (tcount / p.nbuf) & 1;
                 if (!ptx::mbar_wait(&bars->acc_empty[buf], aph ^ 1)) { bars->abort = 1; break; }
-                const uint32_t acc = tmem + buf * 2 * p.NT;
+                const uint32_t acc = tmem + buf * p.halves * p.NT;
                 ptx::tc_fence_after_sync();
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int s = it % p.stages;
                     const uint32_t ph = (it / p.stages) & 1;
                     if (!ptx::mbar_wait(&bars->full[s], ph)) { bars->abort = 1; break; }
                     ptx::tc_fence_after_sync();
-                    const uint32_t a0 = ptx::smem_u32(smem + (size_t)s * stage_bytes), b0 = a0 + A_STAGE;
+                    const uint32_t a0 = ptx::smem_u32(smem + (size_t)s * stage_bytes), b0 = a0 + a_stage;
 #pragma unroll
                     for (int k4 = 0; k4 < KB / 8; ++k4) {
                         const uint64_t bd = ptx::make_smem_desc(b0 + k4 * 32, 16, 1024, ptx::kLayoutSw128);
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
+                            if (h >= p.halves) break;
                             const uint64_t ad = ptx::make_smem_desc(a0 + h * (A_STAGE / 2) + k4 * 32, 16, 1024, ptx::kLayoutSw128);
                             ptx::umma_tf32(acc + h * p.NT, ad, bd, idesc, (kb | k4) != 0);
                         }
@@ -148,15 +150,14 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         const int half = (warp - 2) >> 2;                        // which 128-row half (accumulator) of the tile
         uint8_t* my_out = out_stage + (warp - 2) * 4096;
         uint32_t tcount = 0;
-        for (int64_t tile = blockIdx.x; tile < p.tiles && !bars->abort; tile += gridDim.x, ++tcount) {
+        for (int64_t tile = blockIdx.x; tile < p.tiles && !bars->abort && half < p.halves; tile += gridDim.x, ++tcount) {
             const uint32_t buf = tcount % p.nbuf, aph = (tcount / p.nbuf) & 1;
-            const int64_t row = (tile / p.n_tiles_n) * TM + half * 128 + q * 32 + lane;
             const int n0 = (int)(tile % p.n_tiles_n) * p.NT;
             if (!ptx::mbar_wait(&bars->acc_full[buf], aph)) { bars->abort = 1; break; }
             ptx::tc_fence_after_sync();
-            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + buf * 2 * p.NT + half * p.NT;
+            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + buf * p.halves * p.NT + half * p.NT;
             const int ncols = min(p.NT, p.N - n0);
-            const int row0 = (int)(tile / p.n_tiles_n) * TM + half * 128 + q * 32;       // this warp's first row
+            const int row0 = (int)(tile / p.n_tiles_n) * tile_rows + half * 128 + q * 32;   // this warp's first row
             // one 32-row x 32-column chunk: registers -> this warp's 4 KB staging tile (128-byte rows, 16-byte pieces
             // XOR-swizzled by the row so that the 32 lanes' v4 stores are conflict-free) -> one TMA store, which writes
             // whole 128-byte lines and clips at the matrix edge.  (Thread-per-row st.global hit 32 lines per instruction
@@ -290,15 +291,20 @@ int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, 
     // 256-wide tiles when the layer is MMA-heavy (one accumulator pair fills TMEM); otherwise <= 128 so that two pairs fit
     // and the epilogue of one tile runs under the MMAs of the next
     p.NT = N >= 512 ? 256 : (N >= 128 ? 128 : ((N + 15) & ~15));
-    p.nbuf = 2 * p.NT <= 256 ? 2 : 1;
+#ifdef RQ_EXPERIMENTS
+    if (const char* e = getenv("RQ_LIN_NT")) p.NT = std::min(atoi(e), (N + 15) & ~15);
+#endif
+    p.halves = 2;                            // 128-row tiles measured 15-60 % slower at every encoder shape
+    p.nbuf = p.halves * p.NT <= 256 ? 2 : 1;
     p.n_tiles_n = (N + p.NT - 1) / p.NT;
     p.C = Y; p.M = M; p.ldc = N; p.N = N; p.Kd = Kd; p.act = act & ~RQ_ACT_TF32_OUT; p.round_out = (act & RQ_ACT_TF32_OUT) ? 1 : 0;
-    p.tiles = ((M + TM - 1) / TM) * p.n_tiles_n;
-    const int stage_bytes = A_STAGE + b_stage_bytes(p.NT);
+    const int tile_rows = 128 * p.halves;
+    p.tiles = ((M + tile_rows - 1) / tile_rows) * p.n_tiles_n;
+    const int stage_bytes = p.halves * (A_STAGE / 2) + b_stage_bytes(p.NT);
     p.stages = std::min<int>(MAX_STAGES, (224 * 1024 - OUT_STAGE) / stage_bytes);
     const size_t smem = (size_t)p.stages * stage_bytes + OUT_STAGE + sizeof(Bars) + 1024;
     CUtensorMap ma, mw, mc;
-    RQ_CHECK_ARG(make_map(&ma, X, M, Kd, Kd, TM) && make_map(&mw, W, N, Kd, Kd, p.NT) && make_map(&mc, Y, M, N, N, 32),
+    RQ_CHECK_ARG(make_map(&ma, X, M, Kd, Kd, tile_rows) && make_map(&mw, W, N, Kd, Kd, p.NT) && make_map(&mc, Y, M, N, N, 32),
                  (int)cudaErrorInvalidValue,
                  "encoder layer: cuTensorMapEncodeTiled failed (rows=%lld in=%d out=%d)", (long long)M, Kd, N);
     RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_linear_tf32_kernel, (int)smem));
@@ -307,7 +313,11 @@ int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, 
         RQ_CUDA(cudaMemset(g_timeout_flag, 0, sizeof(int)));
     }
     p.timeout_flag = g_timeout_flag;
-    const int grid = (int)std::min<int64_t>(p.tiles, sm_count());
+    int grid = (int)std::min<int64_t>(p.tiles, sm_count());
+#ifdef RQ_EXPERIMENTS
+    if (const char* e = getenv("RQ_LIN_GRID")) grid = std::min(grid, atoi(e));
+    if (const char* e = getenv("RQ_LIN_STAGES")) p.stages = std::min(p.stages, atoi(e));
+#endif
     rq_linear_tf32_kernel<<<grid, THREADS, smem, st>>>(ma, mw, mc, p);
     RQ_LAUNCHED();
     return 0;

@@ -21,7 +21,7 @@ def timed(fn, n=5):
 
 
 ONLY = os.environ.get("LAYER")
-for n_in, n_out, act in ((768, 512, 1), (512, 256, 1), (256, 128, 1), (128, 64, 0), (128, 32, 0), (128, 32, 2)):
+for n_in, n_out, act in ((768, 512, 1), (768, 512, 0), (768, 256, 0), (768, 128, 0), (1536, 512, 0), (512, 256, 1), (256, 128, 1), (128, 64, 0), (128, 32, 0), (128, 32, 2)):
     if ONLY and ONLY != f"{n_in}x{n_out}":
         continue
     x = torch.randn(M, n_in, device=dev)
