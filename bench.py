@@ -396,6 +396,52 @@ def side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss
                      "path": "tcgen05 (streamed code chunks)" if m == RF.MODE_ROTATION_TRICK else
                              "tcgen05 (fp32-grade split-bf16 GEMMs, Philox noise, softmax weights kept for the backward)"}
     del x5, cb5, ge5, gl5
+
+    # device-resident 768-d -> semantic ids through the module a user calls (RqVae.get_semantic_ids): the
+    # reference encoder 768-512-256-128-32 + 3 x 256 codes, 262,144 resident items per GPU, with the matmul precision
+    # the reference sets ('high' = TF32).  `engine` runs the Linear layers on rq_encoder_layer (SiLU fused), `torch` is
+    # the same module with RQ_ENCODER_TORCH=1 (cuBLAS TF32 + separate SiLU kernels).
+    prev_prec = torch.get_float32_matmul_precision()
+    prev_env = os.environ.get("RQ_ENCODER_TORCH")
+    try:
+        torch.set_float32_matmul_precision("high")
+        torch.manual_seed(5)
+        model = R.RqVae(input_dim=768, embed_dim=D, hidden_dims=[512, 256, 128], codebook_size=K,
+                        codebook_kmeans_init=False, codebook_mode=R.QuantizeForwardMode.ROTATION_TRICK, n_layers=L,
+                        n_cat_features=0).to(dev).eval()
+        with torch.no_grad():
+            for l, layer in enumerate(model.layers):
+                layer.embedding.weight.copy_(cbs[l])
+        Ne = 1 << 18
+        xe = torch.nn.functional.normalize(torch.randn(Ne, 768, device=dev, generator=g5), dim=-1)
+        enc = {}
+        for which in ("engine", "torch"):
+            os.environ["RQ_ENCODER_TORCH"] = "0" if which == "engine" else "1"
+            with torch.no_grad():
+                for fn_name, fn in (("ids", lambda: model.get_semantic_ids(xe)), ("encoder", lambda: model.encode(xe))):
+                    fn(); fn()
+                    fence()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    for _ in range(5):
+                        fn()
+                    b.record()
+                    fence()
+                    enc[(which, fn_name)] = maxed(a.elapsed_time(b)) / 5
+        out["encode_resident"] = {
+            "shape": f"768-512-256-128-{D} encoder + {L} x {K} codes, {Ne} resident items per GPU, matmul precision 'high' (TF32)",
+            "items_per_s": Ne * world / (enc[("engine", "ids")] * 1e-3),
+            "ms": {"ids_engine_encoder": enc[("engine", "ids")], "ids_torch_encoder": enc[("torch", "ids")],
+                   "encoder_engine": enc[("engine", "encoder")], "encoder_torch": enc[("torch", "encoder")]},
+            "roofline_row_items_per_s": 1.35e9,
+            "path": "rq_encoder_layer (TMA + tcgen05 kind::tf32, SiLU fused) x 4, then the fused quantiser"}
+        del model, xe
+    finally:
+        torch.set_float32_matmul_precision(prev_prec)
+        if prev_env is None:
+            os.environ.pop("RQ_ENCODER_TORCH", None)
+        else:
+            os.environ["RQ_ENCODER_TORCH"] = prev_env
     return out
 
 
