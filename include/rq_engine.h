@@ -285,6 +285,10 @@ int rq_debug_split_gemm(const float* A, const float* B, float* C, int64_t M, int
 #define RQ_ACT_SILU 1
 #define RQ_ACT_L2NORM 2
 #define RQ_ACT_TF32_OUT 0x10
+/* Run the layer on CTA pairs (clusters of two, tcgen05 cta_group::2, each CTA staging half of the weight tile) when
+ * out is a multiple of 256 >= 512 and rows >= 512; ignored otherwise.  Same results; measured no faster than the
+ * default single-CTA schedule on B200, kept selectable for other shapes. */
+#define RQ_ACT_CTA_PAIR 0x20
 int rq_encoder_layer_supported(int64_t rows, int in_features, int out_features, int act);
 int rq_encoder_layer(const float* x, const float* weight, float* y, int64_t rows, int in_features, int out_features,
                      int act, rq_stream_t stream);

@@ -319,7 +319,7 @@ def gather_tokens(table: torch.Tensor, item_ids: torch.Tensor, seq_mask: Optiona
 from . import ops as _ops  # noqa: E402  (torch.library registration; imports this module back)
 
 
-ACT_NONE, ACT_SILU, ACT_L2NORM, ACT_TF32_OUT = 0, 1, 2, 0x10
+ACT_NONE, ACT_SILU, ACT_L2NORM, ACT_TF32_OUT, ACT_CTA_PAIR = 0, 1, 2, 0x10, 0x20
 
 
 def encoder_layer_supported(rows: int, in_features: int, out_features: int, act: int) -> bool:

@@ -32,7 +32,8 @@ def _ref(x, w, act):
 
 
 SHAPES = [(1000, 768, 512), (4096, 512, 256), (333, 256, 128), (5000, 128, 32), (129, 128, 64), (1, 768, 512),
-          (257, 100, 24), (2048, 36, 300), (640, 128, 16)]
+          (257, 100, 24), (2048, 36, 300), (640, 128, 16),
+          (8192, 768, 512), (5000, 256, 768), (4097, 64, 1024), (70000, 128, 512)]
 
 
 @pytest.mark.parametrize("rows,n_in,n_out", SHAPES)
@@ -67,6 +68,25 @@ def test_encoder_layer_tf32_precision(rows, n_in, n_out, act):
         err = ((y.double() - ref).abs() / bound).max().item()
         assert err < 2.0 ** -10, err
     assert torch.isfinite(y).all()
+
+
+@pytest.mark.parametrize("rows,n_in,n_out", [(8192, 768, 512), (5000, 256, 768), (4097, 64, 1024), (70000, 128, 512),
+                                              (513, 96, 512)])
+def test_encoder_layer_cta_pair_schedule(rows, n_in, n_out):
+    """ACT_CTA_PAIR: clusters of two CTAs, cta_group::2 MMAs, each CTA staging half of the weight tile - same result as
+    the default schedule bit for bit (same products, same accumulation order), ragged row tails included."""
+    g = torch.Generator(device=DEV).manual_seed(rows + n_in)
+    x = torch.randn(rows, n_in, device=DEV, generator=g)
+    w = torch.randn(n_out, n_in, device=DEV, generator=g) / n_in ** 0.5
+    for act in (RF.ACT_NONE, RF.ACT_SILU | RF.ACT_TF32_OUT):
+        y1 = RF.encoder_layer(x, w, act)
+        y2 = RF.encoder_layer(x, w, act | RF.ACT_CTA_PAIR)
+        assert torch.equal(y1, y2)
+    xe, we = _tf32_exact(x), _tf32_exact(w)
+    y = RF.encoder_layer(xe, we, RF.ACT_CTA_PAIR)
+    bound = xe.double().norm(dim=1, keepdim=True) * we.double().norm(dim=1)[None, :]
+    assert ((y.double() - _ref(xe, we, RF.ACT_NONE)).abs() / bound).max().item() < 2e-6
+    assert _lib.lib().rq_debug_tc_timeout_flag() == 0
 
 
 def test_encoder_layer_rejects_bad_shapes():

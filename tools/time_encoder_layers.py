@@ -27,7 +27,7 @@ for n_in, n_out, act in ((768, 512, 1), (768, 512, 0), (768, 256, 0), (768, 128,
     x = torch.randn(M, n_in, device=dev)
     w = torch.randn(n_out, n_in, device=dev) / n_in ** 0.5
     y = torch.empty(M, n_out, device=dev)
-    te = timed(lambda: RF.encoder_layer(x, w, act, out=y))
+    te = timed(lambda: RF.encoder_layer(x, w, act | (RF.ACT_CTA_PAIR if os.environ.get('ENC_PAIR') else 0), out=y))
     if act == 1:
         tt = timed(lambda: torch.nn.functional.silu(x @ w.t()))
     elif act == 2:
