@@ -46,7 +46,6 @@ struct Params {
     int st_mode;                       // 0: TMA store of the staging tile, 1: coalesced st.global from it
     int noload;                        // RQ_EXPERIMENTS what-if: stage contents are loaded once, then only the barriers cycle
     int64_t tiles;
-    int* timeout_flag;
     unsigned long long* dbg;           // RQ_EXPERIMENTS: cycle counters of block 0
 };
 struct Bars {
@@ -54,6 +53,10 @@ struct Bars {
     uint32_t tmem_base;
     volatile int abort;
 };
+
+// raised when a barrier wait gave up (rq_debug_tc_timeout_flag); a file-scope word, so a launch allocates nothing and
+// can be captured into a CUDA graph from its first call on
+__device__ int g_linear_timeout = 0;
 
 // v * sigmoid(v) as two MUFU ops (ex2, rcp: 2^-22-grade, far below the TF32 product error) and no branches: the first
 // version's correctly rounded reciprocal cost 19 instructions per element and made the epilogue warps the bottleneck.
@@ -367,7 +370,7 @@ rq_linear_tf32_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         if (PAIR) ptx::tmem_dealloc_pair(tmem, 512);
         else ptx::tmem_dealloc(tmem, 512);
     }
-    if (tid == 0 && bars->abort && p.timeout_flag) *p.timeout_flag = 1;
+    if (tid == 0 && bars->abort) g_linear_timeout = 1;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -397,7 +400,6 @@ static bool make_map(CUtensorMap* m, const float* base, int64_t rows, int64_t co
               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
-static int* g_timeout_flag = nullptr;
 }  // namespace lt
 
 bool linear_tf32_supported(int64_t M, int N, int Kd, int act_flags) {
@@ -450,11 +452,6 @@ int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, 
     RQ_CHECK_ARG(make_map(&ma, X, M, Kd, Kd, tile_rows) && make_map(&mw, W, N, Kd, Kd, b_rows) && make_map(&mc, Y, M, N, N, 32),
                  (int)cudaErrorInvalidValue,
                  "encoder layer: cuTensorMapEncodeTiled failed (rows=%lld in=%d out=%d)", (long long)M, Kd, N);
-    if (!g_timeout_flag) {
-        RQ_CUDA(cudaMalloc(&g_timeout_flag, sizeof(int)));
-        RQ_CUDA(cudaMemset(g_timeout_flag, 0, sizeof(int)));
-    }
-    p.timeout_flag = g_timeout_flag;
 #ifdef RQ_EXPERIMENTS
     static unsigned long long* dbg = nullptr;
     if (getenv("RQ_LIN_STATS")) {
@@ -501,7 +498,7 @@ int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, 
 }
 int linear_tf32_timeout_flag() {
     int v = 0;
-    if (lt::g_timeout_flag) cudaMemcpy(&v, lt::g_timeout_flag, sizeof(int), cudaMemcpyDeviceToHost);
+    cudaMemcpyFromSymbol(&v, lt::g_linear_timeout, sizeof(int));
     return v;
 }
 

@@ -146,3 +146,35 @@ def test_tf32_out_flag_rounds_to_grid():
     assert torch.equal(y, _tf32_exact(y)) and (y.view(torch.int32) & 0x1FFF).eq(0).all()
     y0 = RF.encoder_layer(x, w, RF.ACT_SILU)
     assert torch.equal(y, _tf32_exact(y0))
+
+
+def test_encoder_chain_captures_into_a_cuda_graph():
+    """The four layers of the reference encoder captured into one CUDA graph on a fresh stream (nothing on the launch
+    path allocates or synchronises) and replayed on new inputs: same bits as the eager calls."""
+    torch.manual_seed(11)
+    dims = [768, 512, 256, 128, 32]
+    ws = [_tf32_exact(torch.randn(dims[i + 1], dims[i], device=DEV) / dims[i] ** 0.5) for i in range(4)]
+    x = torch.randn(6000, 768, device=DEV)
+    bufs = [torch.empty(6000, d, device=DEV) for d in dims[1:]]
+
+    def chain():
+        h = x
+        for i, w in enumerate(ws):
+            act = (RF.ACT_SILU | RF.ACT_TF32_OUT) if i < 3 else RF.ACT_L2NORM
+            h = RF.encoder_layer(h, w, act, out=bufs[i])
+        return h
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        chain()                                             # warm-up outside the capture (function attributes)
+    torch.cuda.current_stream().wait_stream(side)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        chain()
+    x.copy_(torch.randn(6000, 768, device=DEV))
+    g.replay()
+    got = bufs[3].clone()
+    want = chain().clone()
+    assert torch.equal(got, want)
+    assert torch.allclose(got.norm(dim=1), torch.ones(6000, device=DEV), atol=1e-5)
