@@ -420,9 +420,11 @@ int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, 
     RQ_CHECK_ARG(!((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(Y)) & 15),
                  RQ_ERR_INVALID_ARGUMENT, "encoder layer: x, weight and y must be 16-byte aligned");
     Params p{};
-    // 256-wide tiles when the layer is MMA-heavy (one accumulator pair fills TMEM); otherwise <= 128 so that two pairs fit
-    // and the epilogue of one tile runs under the MMAs of the next
-    p.NT = N >= 512 ? 256 : (N >= 128 ? 128 : ((N + 15) & ~15));
+    // 256-wide tiles whenever the layer has 256 columns: a kind::tf32 MMA costs ~120 cycles at N = 128 as at N = 256
+    // (measured: 192 MMAs per tile take 23k cycles either way), so halving N halves the tensor rate; that outweighs
+    // the serialised epilogue (one accumulator pair fills TMEM).  Narrower layers are HBM-bound: <= 128 columns, two
+    // accumulator pairs, the epilogue of one tile under the MMAs of the next.
+    p.NT = N >= 256 ? 256 : (N >= 128 ? 128 : ((N + 15) & ~15));
 #ifdef RQ_EXPERIMENTS
     if (const char* e = getenv("RQ_LIN_NT")) p.NT = std::min(atoi(e), (N + 15) & ~15);
 #endif
