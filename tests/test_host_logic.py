@@ -251,3 +251,24 @@ def test_bench_reference_arm_prints_exactly_one_json_line():
     r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
                        capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_mlp_engine_plan_is_cuda_inference_only():
+    """The encoder-layer kernel is taken only for CUDA fp32 inference with TF32 matmuls allowed; on CPU (and under
+    autograd) the MLP is the reference's nn.Sequential (modules/encoder.py:17-36), bit for bit."""
+    import torch
+    from rq_vae_recommender_b200.modules.encoder import MLP
+    torch.manual_seed(0)
+    mlp = MLP(48, [32, 16], 8, normalize=True).eval()
+    x = torch.randn(5, 48)
+    prev = torch.get_float32_matmul_precision()
+    try:
+        torch.set_float32_matmul_precision("high")
+        with torch.no_grad():
+            assert mlp._engine_plan(x) is None
+            y = mlp(x)
+            assert torch.equal(y, mlp.mlp(x))
+    finally:
+        torch.set_float32_matmul_precision(prev)
+    assert [k for k in mlp.state_dict()] == ["mlp.0.weight", "mlp.2.weight", "mlp.4.weight"]
+    assert "_tf32_weights" not in mlp.state_dict()
