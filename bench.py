@@ -436,6 +436,8 @@ def side_legs(torch, dist, R, RF, dev, rank, world, xs_h, cbs_h, g_emb_h, g_loss
             "roofline_row_items_per_s": 1.35e9,
             "path": "rq_encoder_layer (TMA + tcgen05 kind::tf32, SiLU fused) x 4, then the fused quantiser"}
         del model, xe
+    except Exception as exc:                     # a side leg never takes the headline line down with it; the error is the result
+        out["encode_resident"] = {"error": f"{type(exc).__name__}: {exc}"}
     finally:
         torch.set_float32_matmul_precision(prev_prec)
         if prev_env is None:
