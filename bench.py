@@ -477,6 +477,10 @@ def run_engine(args):
         # the exchange kernel runs beside the persistent grids, which otherwise fill every SM's register file
         R.parallel.reserve_sms_for_collectives(4 if use_peer else 8)
     R.lib()
+    # one process per GPU: the pinned staging buffers of the e2e leg go on the GPU's own NUMA node (no CPU affinity is
+    # touched); RQ_BENCH_NUMA=0 leaves the placement to the kernel's default policy
+    import contextlib
+    near_gpu = R.parallel.host_memory_near_gpu(dev) if os.environ.get("RQ_BENCH_NUMA", "1") != "0" else contextlib.nullcontext()
 
     xs_h, cbs_h, g_emb_h, g_loss_h = make_inputs(torch, dev, N_SLOTS, seed=100 + rank)
     xs = [t.to(dev) for t in xs_h]
@@ -727,7 +731,8 @@ def run_engine(args):
         for l in range(L):
             model.layers[l].embedding.weight.copy_(cbs[l])
     model.train()
-    xs_pin = [t.pin_memory() for t in xs_h]
+    with near_gpu:
+        xs_pin = [t.pin_memory() for t in xs_h]
 
     g_embs_bdl = [g.permute(1, 2, 0) for g in g_embs]                           # views, [B,D,L] like the output
 
@@ -748,8 +753,9 @@ def run_engine(args):
     # Batches arrive through the package's DevicePrefetcher (data/utils.py): the H2D copy of step i+1 runs on its
     # own stream, straight into the static input of the step that will consume it, while step i is quantised.
     lat_static = [torch.empty(B_PER_GPU, D, device=dev).requires_grad_(True) for _ in range(E2E_SLOTS)]
-    loss_pin = [torch.empty(B_PER_GPU, dtype=torch.float32).pin_memory() for _ in range(E2E_SLOTS)]
-    ids_pin = [torch.empty((L, B_PER_GPU), dtype=torch.int64).pin_memory() for _ in range(E2E_SLOTS)]
+    with near_gpu:
+        loss_pin = [torch.empty(B_PER_GPU, dtype=torch.float32).pin_memory() for _ in range(E2E_SLOTS)]
+        ids_pin = [torch.empty((L, B_PER_GPU), dtype=torch.int64).pin_memory() for _ in range(E2E_SLOTS)]
     done = [torch.cuda.Event() for _ in range(E2E_SLOTS)]
 
     def module_step(s):
@@ -934,6 +940,7 @@ def run_engine(args):
                       "ids_only_items_per_s": B_PER_GPU / (ids_only_ms * 1e-3),
                       "fwd_items_per_s": B_PER_GPU / (fwd_ms * 1e-3),
                       "tcgen05": bool(R.lib().rq_tcgen05_supported(D, K, L, mode, 1)), "launch_mode": launch_mode, "e2e_call": e2e_mode,
+                      "pinned_on_numa_node": getattr(near_gpu, "node", None),
                       "grad_exchange": (None if world == 1 else ("rq_peer_allreduce_f32 (peer memory, " + ("in the step graph)" if peer_inline else "side stream beside the graphs)"))
                                         if peer is not None else "NCCL all_reduce, async beside the graphs"),
                       "e2e_result_checked": e2e_ok, "e2e_compiled": e2e_compiled, "timing": timing, **extras},

@@ -2,7 +2,7 @@
 encoder replicated, items split into contiguous blocks.  Tokenisation needs no data-path
 collective; k-means and the codebook gradient use one all-reduce: torch.distributed / NCCL, or the engine's own
 one-shot kernel over peer-mapped memory (`PeerAllReduce`)."""
-from typing import Tuple
+from typing import Optional, Tuple
 
 import torch
 
@@ -14,6 +14,60 @@ def reserve_sms_for_collectives(n_sms: int = 8) -> None:
     RQ_SM_RESERVE once)."""
     import os
     os.environ["RQ_SM_RESERVE"] = str(int(n_sms))
+
+
+def gpu_numa_node(device=None) -> Optional[int]:
+    """NUMA node the GPU hangs off (sysfs: its PCI function's `numa_node`), or None when the platform exposes none."""
+    try:
+        idx = torch.cuda.current_device() if device is None else torch.device(device).index
+        if idx is None:
+            idx = torch.cuda.current_device()
+        pr = torch.cuda.get_device_properties(idx)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        return node if node >= 0 else None
+    except (OSError, ValueError, AttributeError, RuntimeError, AssertionError):
+        return None
+
+
+class host_memory_near_gpu:
+    """Context manager: host memory allocated inside the block by the calling thread (pinned staging buffers:
+    `tensor.pin_memory()`, `cudaHostAlloc`) is placed on the GPU's own NUMA node (`set_mempolicy(MPOL_PREFERRED)`),
+    so that the per-step H2D / D2H copies of a one-process-per-GPU job do not cross the inter-socket link.  CPU
+    affinity is left alone.  `.node` is the node used, None when nothing was changed (no NUMA information, or a
+    platform without the syscall)."""
+    _SYSCALL = {"x86_64": 238, "aarch64": 237}
+    _MPOL_DEFAULT, _MPOL_PREFERRED = 0, 1
+
+    def __init__(self, device=None):
+        self.node = gpu_numa_node(device)
+        self._libc = None
+
+    def _set(self, mode: int, node: Optional[int]) -> bool:
+        import ctypes
+        import platform
+        nr = self._SYSCALL.get(platform.machine())
+        if nr is None:
+            return False
+        if self._libc is None:
+            self._libc = ctypes.CDLL(None, use_errno=True)
+        if node is None:
+            return self._libc.syscall(nr, mode, None, 0) == 0
+        words = node // 64 + 1
+        mask = (ctypes.c_ulong * words)()
+        mask[node // 64] = 1 << (node % 64)
+        return self._libc.syscall(nr, mode, mask, words * 64 + 1) == 0
+
+    def __enter__(self):
+        if self.node is not None and not self._set(self._MPOL_PREFERRED, self.node):
+            self.node = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.node is not None:
+            self._set(self._MPOL_DEFAULT, None)
+        return False
 
 
 def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
