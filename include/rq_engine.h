@@ -266,6 +266,11 @@ int rq_debug_tc_set_timeline(long long* device_buf_32x64);
  * Stands where the reference calls torch.matmul inside the Gumbel branch (modules/quantize.py:125-128 and its autograd). */
 int rq_debug_split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda,
                         int64_t ldb, int64_t ldc, float alpha, int atomic, int k_splits, rq_stream_t stream);
+/* The same product with both operands given transposed, At[Kd, M] and Bt[Kd, N] (row strides ldat / ldbt), N <= 64: the
+ * shape of the Gumbel backward's codebook gradients (W^T de, dd^T x over the batch), staged MN-major so that no transposed
+ * copy of the [B, K] matrices is written. */
+int rq_debug_split_gemm_tn(const float* At, const float* Bt, float* C, int64_t M, int64_t N, int64_t Kd, int64_t ldat,
+                           int64_t ldbt, int64_t ldc, float alpha, int atomic, int k_splits, rq_stream_t stream);
 
 /* ---- encoder layer ---------------------------------------------------------------------------
  * y[rows, out] = act(x[rows, in] * weight[out, in]^T): one bias-free Linear of the reference's MLP

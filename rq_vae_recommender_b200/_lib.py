@@ -69,6 +69,8 @@ SIGNATURES = {
     "rq_debug_tc_set_timeline": (c_int, [c_void_p]),
     "rq_debug_split_gemm": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
                                     c_float, c_int, c_int, c_void_p]),
+    "rq_debug_split_gemm_tn": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
+                                       c_float, c_int, c_int, c_void_p]),
     "rq_encoder_layer_supported": (c_int, [c_int64, c_int, c_int, c_int]),
     "rq_encoder_layer": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "rq_semantic_ids_host": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,

@@ -83,6 +83,32 @@ __device__ __forceinline__ void stage_tile(const float* base, int64_t row0, int6
     tile_load<ROWS>(base, row0, rows, ld, k0, Kd, v, tid);
     tile_store<ROWS>(v, planes, plane_bytes, third, tid);
 }
+// ---- operands given transposed: T[Kd, R] row-major, R (= M or N) contiguous ("MN-major") --------------------------------
+// The tile keeps that orientation in shared memory: 64-element (128-byte) swizzle atoms along R, 8 k-rows per 1024-byte
+// group, the 16-byte piece index XORed with k & 7 (UMMA canonical MN-major SW128: LBO = 8192 bytes from one atom column to
+// the next, SBO = 1024 bytes from one group of 8 k to the next).  No transposed copy of the matrix has to exist in HBM.
+__device__ __forceinline__ uint32_t mn128_off(int k, int c) {
+    return (uint32_t)((c >> 6) * 8192 + (k >> 3) * 1024 + (k & 7) * 128 + ((((c & 63) >> 3) ^ (k & 7)) << 4) + ((c & 7) << 1));
+}
+template <int COLS>
+__device__ __forceinline__ void tile_load_t(const float* base, int64_t col0, int64_t cols, int64_t ld, int64_t k0, int64_t Kd,
+                                            float4 (&v)[COLS * 16 / THREADS], int tid) {
+#pragma unroll
+    for (int j = 0; j < COLS * 16 / THREADS; ++j) {
+        const int i = tid + j * THREADS;
+        v[j] = load4_guarded(base, k0 + i / (COLS / 4), Kd, ld, col0 + (i % (COLS / 4)) * 4, cols);
+    }
+}
+template <int COLS>
+__device__ __forceinline__ void tile_store_t(const float4 (&v)[COLS * 16 / THREADS], uint8_t* planes, int plane_bytes, bool third,
+                                             int tid) {
+#pragma unroll
+    for (int j = 0; j < COLS * 16 / THREADS; ++j) {
+        const int i = tid + j * THREADS;
+        const uint32_t o = mn128_off(i / (COLS / 4), (i % (COLS / 4)) * 4);
+        split3_store(v[j], planes + o, planes + plane_bytes + o, planes + 2 * plane_bytes + o, third);
+    }
+}
 }  // namespace sg
 
 struct SplitGemmParams {
@@ -96,7 +122,8 @@ struct SplitGemmParams {
     int terms;           // 6: three planes, fp32-grade (error ~2^-22 |a||b|); 3: two planes, a1.b1 + a1.b2 + a2.b1 (2^-16)
 };
 
-template <int NT>
+// TRANS: A is given as At[Kd, M] and B as Bt[Kd, N] (lda / ldb are their row strides), see mn128_off.
+template <int NT, bool TRANS = false>
 __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemmParams g) {
     using namespace sg;
     extern __shared__ uint8_t smem_raw[];
@@ -123,14 +150,17 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
     ptx::tc_fence_after_sync();
     const uint32_t tmem_acc = *reinterpret_cast<volatile uint32_t*>(tmem_base_s);
     // kind::f16 instruction descriptor, bf16 x bf16 -> fp32, K-major operands
-    const uint32_t idesc = ptx::make_idesc_bf16_f32(TM, NT);
+    const uint32_t idesc = ptx::make_idesc_bf16_f32(TM, NT) | (TRANS ? (1u << 15) | (1u << 16) : 0u);   // a_major, b_major = MN
     bool timed_out = false;
 
     // The loads of block kb + 1 are issued right after the MMAs of block kb, so their latency runs under those MMAs and
     // the wait for them (NT = 64: 12 float4 per thread in flight; the 256-wide tile has no registers to spare for it).
     constexpr bool PIPE = (NT == 64);
     float4 ra[TM * 16 / THREADS], rb[NT * 16 / THREADS];
-    if (PIPE) {
+    if (PIPE && TRANS) {
+        tile_load_t<TM>(g.A, m0, g.M, g.lda, kb0 * KB, g.Kd, ra, tid);
+        tile_load_t<NT>(g.B, n0, g.N, g.ldb, kb0 * KB, g.Kd, rb, tid);
+    } else if (PIPE) {
         tile_load<TM>(g.A, m0, g.M, g.lda, kb0 * KB, g.Kd, ra, tid);
         tile_load<NT>(g.B, n0, g.N, g.ldb, kb0 * KB, g.Kd, rb, tid);
     }
@@ -141,7 +171,10 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
         }
         const int64_t k0 = kb * KB;
         // ---- stage: 16 float4 per row, a warp reads two rows' 256 contiguous bytes per instruction ----------------------
-        if (PIPE) {
+        if (PIPE && TRANS) {
+            tile_store_t<TM>(ra, sA, A_PLANE, g.terms == 6, tid);
+            tile_store_t<NT>(rb, sB, B_PLANE, g.terms == 6, tid);
+        } else if (PIPE) {
             tile_store<TM>(ra, sA, A_PLANE, g.terms == 6, tid);
             tile_store<NT>(rb, sB, B_PLANE, g.terms == 6, tid);
         } else {
@@ -163,14 +196,20 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
                 if (g.terms != 6 && t < 3) continue;               // two planes: the last three products only
 #pragma unroll
                 for (int s = 0; s < 4; ++s) {                      // four K = 16 steps of 32 bytes
-                    const uint64_t ad = ptx::make_smem_desc(a0 + pa[t] * A_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
-                    const uint64_t bd = ptx::make_smem_desc(b0 + pb[t] * B_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
+                    // a K = 16 step is 32 bytes along a K-major row, two 1024-byte groups of 8 k in the MN-major tile
+                    const uint64_t ad = TRANS ? ptx::make_smem_desc(a0 + pa[t] * A_PLANE + s * 2048, 8192, 1024, ptx::kLayoutSw128)
+                                              : ptx::make_smem_desc(a0 + pa[t] * A_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
+                    const uint64_t bd = TRANS ? ptx::make_smem_desc(b0 + pb[t] * B_PLANE + s * 2048, 8192, 1024, ptx::kLayoutSw128)
+                                              : ptx::make_smem_desc(b0 + pb[t] * B_PLANE + s * 32, 16, 1024, ptx::kLayoutSw128);
                     ptx::umma_bf16(tmem_acc, ad, bd, idesc, (kb > kb0 || t > (g.terms == 6 ? 0 : 3) || s > 0) ? 1u : 0u);
                 }
             }
             ptx::umma_commit(mbar);
         }
-        if (PIPE && kb + 1 < kb1) {
+        if (PIPE && TRANS && kb + 1 < kb1) {
+            tile_load_t<TM>(g.A, m0, g.M, g.lda, k0 + KB, g.Kd, ra, tid);
+            tile_load_t<NT>(g.B, n0, g.N, g.ldb, k0 + KB, g.Kd, rb, tid);
+        } else if (PIPE && kb + 1 < kb1) {
             tile_load<TM>(g.A, m0, g.M, g.lda, k0 + KB, g.Kd, ra, tid);
             tile_load<NT>(g.B, n0, g.N, g.ldb, k0 + KB, g.Kd, rb, tid);
         }
@@ -375,7 +414,49 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
     return 0;
 }
 
+// C[M, N] (+)= alpha * At[Kd, M]^T * Bt[Kd, N]: both operands given with the contraction index as their ROW index (the
+// shape of the Gumbel backward's codebook gradients, W^T de and dd^T x over the batch).  N <= 64; ldat, ldbt multiples of 4.
+int split_gemm_tn(const float* At, const float* Bt, float* C, int64_t M, int64_t N, int64_t Kd, int64_t ldat, int64_t ldbt,
+                  int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st, int terms) {
+    if (M <= 0 || N <= 0 || Kd <= 0) return 0;
+    if (N > 64 || (ldat & 3) || (ldbt & 3) || ((uintptr_t)At & 15) || ((uintptr_t)Bt & 15)) {
+        set_error("split_gemm_tn: N <= 64 and 16-byte aligned operand rows required");
+        return RQ_ERR_INVALID_ARGUMENT;
+    }
+    SplitGemmParams g;
+    g.A = At; g.B = Bt; g.C = C; g.M = M; g.N = N; g.Kd = Kd; g.lda = ldat; g.ldb = ldbt; g.ldc = ldc;
+    g.alpha = alpha;
+    g.terms = (terms == 3) ? 3 : 6;
+    const int64_t n_kb = (Kd + sg::KB - 1) / sg::KB;
+    if (k_splits < 1) k_splits = 1;
+    if (k_splits > n_kb) k_splits = (int)n_kb;
+    g.kb_per_split = (int)((n_kb + k_splits - 1) / k_splits);
+    k_splits = (int)((n_kb + g.kb_per_split - 1) / g.kb_per_split);
+    g.atomic = (atomic || k_splits > 1) ? 1 : 0;
+    constexpr int NT = 64;
+    const size_t smem = 3 * sg::TM * 128 + 3 * NT * 128 + 64 + 1024;
+    RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_kernel<NT, true>, (int)smem));
+    static bool carve_set = false;
+    if (!carve_set) {
+        cudaFuncSetAttribute((const void*)rq_split_gemm_kernel<NT, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared);
+        carve_set = true;
+    }
+    dim3 grid((unsigned)((M + sg::TM - 1) / sg::TM), 1, (unsigned)k_splits);
+    rq_split_gemm_kernel<NT, true><<<grid, sg::THREADS, smem, st>>>(g);
+    RQ_LAUNCHED();
+    return 0;
+}
+
 }  // namespace rq
+
+// the same with both operands transposed in memory (k_splits < 0: two-plane form)
+extern "C" int rq_debug_split_gemm_tn(const float* At, const float* Bt, float* C, int64_t M, int64_t N, int64_t Kd,
+                                      int64_t ldat, int64_t ldbt, int64_t ldc, float alpha, int atomic, int k_splits,
+                                      rq_stream_t stream) {
+    return rq::split_gemm_tn(At, Bt, C, M, N, Kd, ldat, ldbt, ldc, alpha, atomic, k_splits < 0 ? -k_splits : k_splits,
+                             (cudaStream_t)stream, k_splits < 0 ? 3 : 6);
+}
 
 // Test hook: the split-precision GEMM on its own (tests/test_gpu_gumbel.py compares it with float64).
 extern "C" int rq_debug_split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd,

@@ -29,6 +29,8 @@ namespace rq {
 
 int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda, int64_t ldb,
                int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st, int terms = 6);
+int split_gemm_tn(const float* At, const float* Bt, float* C, int64_t M, int64_t N, int64_t Kd, int64_t ldat, int64_t ldbt,
+                  int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st, int terms = 6);
 
 namespace gtc {
 
@@ -252,75 +254,44 @@ __global__ void __launch_bounds__(256) gumbel_de_kernel(DeParams q) {
     if ((i % LPR) == 0) q.t[row] = t;
 }
 
-// dst[c, r] = src[r, c] through 32 x 32 shared-memory tiles (src [R, C] row stride lds, dst [C, R] row stride ldd;
-// the columns r >= R of dst up to ldd are left untouched: the caller zeroes the padding once)
-__global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t R,
-                                                        int64_t C, int64_t lds, int64_t ldd) {
-    __shared__ float tile[32][33];
-    const int64_t r0 = (int64_t)blockIdx.x * 32, c0 = (int64_t)blockIdx.y * 32;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+// dd = -W (dW - t) / T in place over dW, and colsum(dd) (one atomic per block and column).  Thread = four columns,
+// a block walks 256 rows; the codebook-gradient GEMMs read W and dd as they lie (split_gemm_tn), so nothing is transposed.
+__global__ void __launch_bounds__(256) gumbel_dd_kernel(const float* __restrict__ W, float* __restrict__ dW,
+                                                        const float* __restrict__ t, int64_t B, int K, int Kp, float inv_t,
+                                                        float* __restrict__ csum) {
+    const int c = (blockIdx.y * 256 + threadIdx.x) * 4;
+    if (c >= Kp) return;
+    const int64_t r0 = (int64_t)blockIdx.x * 256;
+    const int64_t r1 = r0 + 256 < B ? r0 + 256 : B;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    auto one = [&](int64_t r, const float4& w, const float4& d, float tr) {
+        float4 o;
+        o.x = (c + 0 < K) ? -(w.x * (d.x - tr)) * inv_t : 0.f;
+        o.y = (c + 1 < K) ? -(w.y * (d.y - tr)) * inv_t : 0.f;
+        o.z = (c + 2 < K) ? -(w.z * (d.z - tr)) * inv_t : 0.f;
+        o.w = (c + 3 < K) ? -(w.w * (d.w - tr)) * inv_t : 0.f;
+        *reinterpret_cast<float4*>(dW + r * Kp + c) = o;
+        acc[0] += o.x; acc[1] += o.y; acc[2] += o.z; acc[3] += o.w;
+    };
+    int64_t r = r0;
+    for (; r + 4 <= r1; r += 4) {
+        float4 w[4], d[4];
+        float tr[4];
 #pragma unroll
-    for (int j = 0; j < 32; j += 8) {
-        const int64_t r = r0 + ty + j, c = c0 + tx;
-        tile[ty + j][tx] = (r < R && c < C) ? __ldg(src + r * lds + c) : 0.f;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < 32; j += 8) {
-        const int64_t c = c0 + ty + j, r = r0 + tx;
-        if (c < C && r < R) dst[c * ldd + r] = tile[tx][ty + j];
-    }
-}
-
-// One pass over the [B, K] matrices of a level's backward: dd = -W (dW - t) / T written in place over dW (the operand
-// of v = dd C), and — through 32 x 32 shared-memory tiles — W^T and dd^T (the operands of the codebook-gradient
-// products, whose contraction runs over the rows) plus the column sums of dd (one atomic per tile column).
-__global__ void __launch_bounds__(256) gumbel_dd_transpose_kernel(const float* __restrict__ W, float* __restrict__ dW,
-                                                                  const float* __restrict__ t, int64_t B, int K, int Kp,
-                                                                  float inv_t, float* __restrict__ Wt, float* __restrict__ ddt,
-                                                                  int64_t Bp, float* __restrict__ csum) {
-    __shared__ float tw[32][33], td[32][33];
-    const int c0 = blockIdx.y * 32;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    float colsum[4] = {0.f, 0.f, 0.f, 0.f};           // of columns c0 + ty + 8 j, over this block's 256 rows (lane 0 keeps them)
-    for (int sub = 0; sub < 8; ++sub) {
-        const int64_t r0 = ((int64_t)blockIdx.x * 8 + sub) * 32;
-        if (r0 >= B) break;
-#pragma unroll
-        for (int j = 0; j < 32; j += 8) {
-            const int64_t r = r0 + ty + j;
-            const int c = c0 + tx;
-            float w = 0.f, d = 0.f;
-            if (r < B && c < K) {
-                w = __ldg(W + r * Kp + c);
-                d = -(w * (dW[r * Kp + c] - __ldg(t + r))) * inv_t;
-                dW[r * Kp + c] = d;
-            }
-            tw[ty + j][tx] = w;
-            td[ty + j][tx] = d;
+        for (int u = 0; u < 4; ++u) {
+            w[u] = __ldg(reinterpret_cast<const float4*>(W + (r + u) * Kp + c));
+            d[u] = *reinterpret_cast<const float4*>(dW + (r + u) * Kp + c);
+            tr[u] = __ldg(t + r + u);
         }
-        __syncthreads();
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) {
-            const int c = c0 + ty + j;
-            const int64_t r = r0 + tx;
-            const float d = td[tx][ty + j];
-            if (c < K && r < B) {
-                Wt[(int64_t)c * Bp + r] = tw[tx][ty + j];
-                ddt[(int64_t)c * Bp + r] = d;
-            }
-            float s = d;                               // rows outside B hold zeros
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            colsum[j >> 3] += s;
-        }
-        __syncthreads();
+        for (int u = 0; u < 4; ++u) one(r + u, w[u], d[u], tr[u]);
     }
-    if (tx == 0) {
+    for (; r < r1; ++r)
+        one(r, __ldg(reinterpret_cast<const float4*>(W + r * Kp + c)), *reinterpret_cast<const float4*>(dW + r * Kp + c),
+            __ldg(t + r));
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            if (c0 + ty + 8 * j < K) atomicAdd(csum + c0 + ty + 8 * j, colsum[j]);
-    }
+    for (int i = 0; i < 4; ++i)
+        if (c + i < K) atomicAdd(csum + c + i, acc[i]);
 }
 
 // g_C[k, :] += 2 C[k, :] * colsum(dd)[k]
@@ -424,10 +395,10 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
     using namespace gtc;
     const int64_t B = p.B, Bp = (B + 3) & ~(int64_t)3;
     const int K = p.K, Kp = (K + 3) & ~3;
-    const size_t bytes_S = (size_t)B * Kp * 4, bytes_T = (size_t)K * Bp * 4, bytes_row = (size_t)B * D * 4;
-    const size_t bytes_rt = (size_t)D * Bp * 4, bytes_ct = (size_t)D * Kp * 4, bytes_cc = (size_t)Kp * 4;
-    // scratch: W | dW/dd | W^T | dd^T | emb | de | v | G | de^T | x^T | C^T | cc | t
-    const size_t total = 2 * bytes_S + 2 * bytes_T + 4 * bytes_row + 2 * bytes_rt + bytes_ct + 2 * bytes_cc + (size_t)Bp * 4 + 256;
+    const size_t bytes_S = (size_t)B * Kp * 4, bytes_row = (size_t)B * D * 4;
+    const size_t bytes_ct = (size_t)D * Kp * 4, bytes_cc = (size_t)Kp * 4;
+    // scratch: W | dW/dd | emb | de | v | G | C^T | cc | t | colsum
+    const size_t total = 2 * bytes_S + 4 * bytes_row + bytes_ct + 2 * bytes_cc + (size_t)Bp * 4 + 256;
     uint8_t* scratch = (uint8_t*)engine_pool_alloc(total, st);
     if (!scratch) {
         set_error("rq_quantize_backward: out of device memory for the Gumbel-softmax scratch (%zu bytes)", total);
@@ -437,14 +408,10 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
     auto take = [&](size_t n) { float* q = (float*)cur; cur += n; return q; };
     float* Wbuf = take(bytes_S);
     float* dd = take(bytes_S);
-    float* Wt = take(bytes_T);
-    float* ddt = take(bytes_T);
     float* emb = take(bytes_row);
     float* de = take(bytes_row);
     float* v = take(bytes_row);
     float* G = take(bytes_row);
-    float* det = take(bytes_rt);
-    float* xt = take(bytes_rt);
     float* ct = take(bytes_ct);
     float* cc = take(bytes_cc);
     float* t = take((size_t)Bp * 4);
@@ -453,11 +420,6 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
 #define GTC_CUDA(call)                                                                   \
     do { if (rc == 0) { cudaError_t e_ = (call); if (e_ != cudaSuccess) { set_error("rq_quantize_backward: %s", cudaGetErrorString(e_)); rc = (int)e_; } } } while (0)
     GTC_CUDA(cudaMemsetAsync(G, 0, bytes_row, st));
-    // the padding columns b >= B of the transposed operands are read by the GEMMs' 16-byte loads: keep them zero
-    if (Bp != B) {
-        GTC_CUDA(cudaMemsetAsync(Wt, 0, 2 * bytes_T, st));
-        GTC_CUDA(cudaMemsetAsync(det, 0, 2 * bytes_rt, st));
-    }
     GTC_CUDA(cudaMemsetAsync(p.g_cb, 0, (size_t)p.L * K * D * sizeof(float), st));      // this mode overwrites (rq_engine.h)
     const unsigned rows8 = (unsigned)((B + 7) / 8), rowsq = (unsigned)((B * (D / 4) + 255) / 256);
     const int64_t n_kb = (B + 63) / 64;
@@ -497,18 +459,16 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
         GTC_CUDA(cudaMemsetAsync(csum, 0, bytes_cc, st));
         if (rc) break;
         {
-            dim3 gT((unsigned)((B + 255) / 256), (unsigned)((K + 31) / 32));
-            gumbel_dd_transpose_kernel<<<gT, 256, 0, st>>>(W, dd, t, B, K, Kp, 1.0f / temperature, Wt, ddt, Bp, csum);
-            dim3 gR((unsigned)((B + 31) / 32), (unsigned)((D + 31) / 32));
-            transpose_kernel<<<gR, 256, 0, st>>>(de, det, B, D, D, Bp);
-            transpose_kernel<<<gR, 256, 0, st>>>(x, xt, B, D, D, Bp);
+            dim3 gT((unsigned)((B + 255) / 256), (unsigned)((Kp / 4 + 255) / 256));
+            gumbel_dd_kernel<<<gT, 256, 0, st>>>(W, dd, t, B, K, Kp, 1.0f / temperature, csum);
             RQ_LAUNCHED();
         }
         // v = dd C
         if ((rc = split_gemm(dd, ct, v, B, D, K, Kp, Kp, D, 1.f, 0, 1, st, 3))) break;
-        // codebook gradient: W^T de - 2 dd^T x + 2 C colsum(dd), contraction over the rows
-        if ((rc = split_gemm(Wt, det, gcb, K, D, B, Bp, Bp, D, 1.f, 1, splits, st, 3))) break;
-        if ((rc = split_gemm(ddt, xt, gcb, K, D, B, Bp, Bp, D, -2.f, 1, splits, st, 3))) break;
+        // codebook gradient: W^T de - 2 dd^T x + 2 C colsum(dd), contraction over the rows; W, dd, de and x are read as
+        // they lie in memory (MN-major staging): no [K, B] copies
+        if ((rc = split_gemm_tn(W, de, gcb, K, D, B, Kp, D, D, 1.f, 1, splits, st, 3))) break;
+        if ((rc = split_gemm_tn(dd, x, gcb, K, D, B, Kp, D, D, -2.f, 1, splits, st, 3))) break;
         gumbel_colsum_apply_kernel<<<(K * D + 255) / 256, 256, 0, st>>>(csum, cbl, gcb, K, D);
         RQ_LAUNCHED();
         // G = G + ... - 2 v; the last level processed writes g_x

@@ -50,3 +50,34 @@ def test_split_gemm_strided_operands_and_split_k_accumulation():
     want = C0.double() + 0.5 * (Wt.double() @ det.double().T)
     scale = (Wt.double().norm(dim=1)[:, None] * det.double().norm(dim=1)[None, :]) * 0.5
     assert float(((C.double() - want).abs() / scale).max()) < 1.5e-6
+
+
+def _gemm_tn(At, Bt, C, alpha=1.0, atomic=0, k_splits=1):
+    Kd, M = At.shape
+    N = Bt.shape[1]
+    rc = _lib.lib().rq_debug_split_gemm_tn(At.data_ptr(), Bt.data_ptr(), C.data_ptr(), M, N, Kd, At.stride(0), Bt.stride(0),
+                                           C.stride(0), float(alpha), int(atomic), int(k_splits),
+                                           torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, rc
+    return C
+
+
+@pytest.mark.parametrize("M,N,Kd,splits", [(1024, 64, 65536, 37), (256, 32, 4096, 1), (1000, 64, 777, 3), (130, 20, 200, 2),
+                                           (128, 64, 64, 1), (4, 4, 5, 1)])
+def test_split_gemm_transposed_operands_match_float64(M, N, Kd, splits):
+    """C = At^T Bt with At [Kd, M], Bt [Kd, N] as they lie in memory (the Gumbel backward's W^T de over the batch): staged
+    MN-major, no transposed copies.  fp32-grade (six products) and the two-plane form, split-K with atomics."""
+    g = torch.Generator(device=DEV).manual_seed(M + N + Kd)
+    ldm, ldn = (M + 3) // 4 * 4 + 8, (N + 3) // 4 * 4
+    At = (torch.randn(Kd, ldm, device=DEV, generator=g) * 2.0)[:, :M]
+    Bt = torch.randn(Kd, ldn, device=DEV, generator=g)[:, :N]
+    ref = At.double().t() @ Bt.double()
+    bound = At.double().norm(dim=0)[:, None] * Bt.double().norm(dim=0)[None, :]
+    C = torch.zeros(M, N, device=DEV)
+    _gemm_tn(At, Bt, C, alpha=1.0, atomic=1, k_splits=splits)
+    err = ((C.double() - ref).abs() / bound).max().item()
+    assert err < 2.5e-6, err        # fp32 accumulation (truncating) over up to 4,096 products in one split
+    C3 = torch.zeros(M, N, device=DEV)
+    _gemm_tn(At, Bt, C3, alpha=-2.0, atomic=1, k_splits=-splits)
+    err3 = ((C3.double() + 2.0 * ref).abs() / bound).max().item()
+    assert err3 < 2.0 ** -14, err3
