@@ -109,6 +109,21 @@ __device__ __forceinline__ void tile_store_t(const float4 (&v)[COLS * 16 / THREA
         split3_store(v[j], planes + o, planes + plane_bytes + o, planes + 2 * plane_bytes + o, third);
     }
 }
+// sum over the warp's 32 lanes of v[0..32): lane j returns the total of element j (31 shuffles; v is destroyed)
+__device__ __forceinline__ float warp_colsum32(float (&v)[32]) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+        const bool up = (lane & half) != 0;
+#pragma unroll
+        for (int j = 0; j < half; ++j) {
+            const float keep = up ? v[j + half] : v[j];
+            const float send = up ? v[j] : v[j + half];
+            v[j] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+        }
+    }
+    return v[0];
+}
 }  // namespace sg
 
 struct SplitGemmParams {
@@ -120,6 +135,12 @@ struct SplitGemmParams {
     int atomic;          // 1: C += alpha * A B^T with float atomics (split-K, or accumulation into a live buffer)
     int kb_per_split;    // K-blocks per blockIdx.z
     int terms;           // 6: three planes, fp32-grade (error ~2^-22 |a||b|); 3: two planes, a1.b1 + a1.b2 + a2.b1 (2^-16)
+    // optional epilogue of the B-resident kernel (the softmax Jacobian of the Gumbel backward, fused into dW = de C^T):
+    // C[m, n] = ep_scale * ep_w[m, n] * (acc[m, n] - ep_t[m]) and ep_csum[n] += sum_m C[m, n]; ep_w has C's shape / stride
+    const float* ep_w;
+    const float* ep_t;
+    float ep_scale;
+    float* ep_csum;
 };
 
 // TRANS: A is given as At[Kd, M] and B as Bt[Kd, N] (lda / ldb are their row strides), see mn128_off.
@@ -320,6 +341,7 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(Spli
         }
     };
 
+    float ep_cs[NT / 2 / 32] = {0.f, 0.f, 0.f, 0.f};   // column sums of the fused epilogue (lane = column within a chunk)
     if (n_mine > 0) stage_a(0);
     for (int64_t it = 0; it < n_mine; ++it) {
         // the next tile's rows go in (other A buffer, other accumulator: both were released before the last barrier)
@@ -331,6 +353,45 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(Spli
         const int64_t row = m0 + q * 32 + lane;
         constexpr int HALF = NT / 2;
         const uint32_t trow = tmem_base + (uint32_t)((it & 1) * NT) + ((uint32_t)(q * 32) << 16) + (uint32_t)(h * HALF);
+        if (g.ep_w) {
+            const float tr = row < g.M ? __ldg(g.ep_t + row) : 0.f;
+#pragma unroll
+            for (int ci = 0; ci < HALF / 32; ++ci) {
+                const int c = ci * 32;
+                const int64_t col0 = n0 + h * HALF + c;
+                const int64_t ncol = g.N - col0;
+                const bool fast = row < g.M && ncol >= 32;
+                float w[32];
+                if (fast) {                                          // this row's 128 bytes of W, in flight under the tcgen05.ld
+                    const float4* src = reinterpret_cast<const float4*>(g.ep_w + row * g.ldc + col0);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 t4 = __ldg(src + j);
+                        w[4 * j] = t4.x; w[4 * j + 1] = t4.y; w[4 * j + 2] = t4.z; w[4 * j + 3] = t4.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) w[j] = (row < g.M && j < ncol) ? __ldg(g.ep_w + row * g.ldc + col0 + j) : 0.f;
+                }
+                uint32_t v[32];
+                ptx::tmem_ld_32x32b_x32(trow + c, v);
+                ptx::tmem_ld_wait_for(v);
+                float o[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) o[j] = (row < g.M && j < ncol) ? g.ep_scale * (w[j] * (__uint_as_float(v[j]) - tr)) : 0.f;
+                float* dst = g.C + row * g.ldc + col0;
+                if (fast && ((reinterpret_cast<uintptr_t>(dst) & 31) == 0)) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) ptx::st_global_v8(dst + j, &o[j]);
+                } else if (row < g.M) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncol) dst[j] = o[j];
+                }
+                ep_cs[ci] += warp_colsum32(o);
+            }
+            continue;
+        }
 #pragma unroll 1
         for (int c = 0; c < HALF; c += 32) {
             uint32_t v[32];
@@ -355,6 +416,14 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(Spli
             }
         }
     }
+    if (g.ep_w && g.ep_csum) {                                       // this CTA's column sums: one atomic per warp and column
+        const int h = warp >> 2;
+#pragma unroll
+        for (int ci = 0; ci < NT / 2 / 32; ++ci) {
+            const int64_t col = n0 + h * (NT / 2) + ci * 32 + lane;
+            if (col < g.N) atomicAdd(g.ep_csum + col, ep_cs[ci]);
+        }
+    }
     (void)timed_out;
     ptx::tc_fence_before_sync();
     __syncthreads();
@@ -373,6 +442,7 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
     SplitGemmParams g;
     g.A = A; g.B = B; g.C = C; g.M = M; g.N = N; g.Kd = Kd; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
     g.alpha = alpha;
+    g.ep_w = nullptr; g.ep_t = nullptr; g.ep_scale = 0.f; g.ep_csum = nullptr;
     g.terms = (terms == 3) ? 3 : 6;
     const int64_t n_kb = (Kd + sg::KB - 1) / sg::KB;
     if (k_splits < 1) k_splits = 1;
@@ -414,6 +484,32 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
     return 0;
 }
 
+// C[m, n] = scale * Wm[m, n] * ((A B^T)[m, n] - t[m]) and csum[n] += sum_m C[m, n]: the dd = -W (dW - t) / T step of the
+// Gumbel backward inside the epilogue of dW = de C^T (Kd <= 64, N > 64: the B-resident kernel).  Wm has C's stride.
+int split_gemm_softmax_jacobian(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda,
+                                int64_t ldb, int64_t ldc, const float* Wm, const float* t, float scale, float* csum,
+                                cudaStream_t st) {
+    if (M <= 0 || N <= 0 || Kd <= 0) return 0;
+    if (N <= 64 || Kd > sg::KB || (lda & 3) || (ldb & 3) || (ldc & 3) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15) ||
+        ((uintptr_t)Wm & 15)) {
+        set_error("split_gemm_softmax_jacobian: needs N > 64, Kd <= 64 and 16-byte aligned rows");
+        return RQ_ERR_INVALID_ARGUMENT;
+    }
+    SplitGemmParams g;
+    g.A = A; g.B = B; g.C = C; g.M = M; g.N = N; g.Kd = Kd; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+    g.alpha = 1.f; g.terms = 6; g.atomic = 0; g.kb_per_split = 1;
+    g.ep_w = Wm; g.ep_t = t; g.ep_scale = scale; g.ep_csum = csum;
+    const unsigned gm = (unsigned)((M + sg::TM - 1) / sg::TM), gn = (unsigned)((N + 255) / 256);
+    unsigned per = (unsigned)sm_count() / gn;
+    if (per < 1) per = 1;
+    if (per > gm) per = gm;
+    const size_t smem = 3 * 256 * 128 + 6 * sg::TM * 128 + 64 + 1024;
+    RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_bres_kernel, (int)smem));
+    rq_split_gemm_bres_kernel<<<dim3(gn, per), sg::THREADS, smem, st>>>(g);
+    RQ_LAUNCHED();
+    return 0;
+}
+
 // C[M, N] (+)= alpha * At[Kd, M]^T * Bt[Kd, N]: both operands given with the contraction index as their ROW index (the
 // shape of the Gumbel backward's codebook gradients, W^T de and dd^T x over the batch).  N <= 64; ldat, ldbt multiples of 4.
 int split_gemm_tn(const float* At, const float* Bt, float* C, int64_t M, int64_t N, int64_t Kd, int64_t ldat, int64_t ldbt,
@@ -426,6 +522,7 @@ int split_gemm_tn(const float* At, const float* Bt, float* C, int64_t M, int64_t
     SplitGemmParams g;
     g.A = At; g.B = Bt; g.C = C; g.M = M; g.N = N; g.Kd = Kd; g.lda = ldat; g.ldb = ldbt; g.ldc = ldc;
     g.alpha = alpha;
+    g.ep_w = nullptr; g.ep_t = nullptr; g.ep_scale = 0.f; g.ep_csum = nullptr;
     g.terms = (terms == 3) ? 3 : 6;
     const int64_t n_kb = (Kd + sg::KB - 1) / sg::KB;
     if (k_splits < 1) k_splits = 1;

@@ -31,6 +31,9 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
                int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st, int terms = 6);
 int split_gemm_tn(const float* At, const float* Bt, float* C, int64_t M, int64_t N, int64_t Kd, int64_t ldat, int64_t ldbt,
                   int64_t ldc, float alpha, int atomic, int k_splits, cudaStream_t st, int terms = 6);
+int split_gemm_softmax_jacobian(const float* A, const float* B, float* C, int64_t M, int64_t N, int64_t Kd, int64_t lda,
+                                int64_t ldb, int64_t ldc, const float* Wm, const float* t, float scale, float* csum,
+                                cudaStream_t st);
 
 namespace gtc {
 
@@ -454,11 +457,14 @@ static int gumbel_backward_tc_impl(const BwdParams& p, float temperature, const 
         dq.g_loss = p.g_loss; dq.G = G; dq.de = de; dq.t = t; dq.B = B; dq.beta = p.beta;
         gumbel_de_kernel<D><<<rowsq, 256, 0, st>>>(dq);
         RQ_LAUNCHED();
-        // dW = de C^T, dd in place
-        if ((rc = split_gemm(de, cbl, dd, B, K, D, D, D, Kp, 1.f, 0, 1, st))) break;
+        // dW = de C^T and dd = -W (dW - t) / T with its column sums: one launch when the B-resident GEMM applies (its
+        // epilogue reads W and applies the softmax Jacobian), else the GEMM and a streaming pass over dW
         GTC_CUDA(cudaMemsetAsync(csum, 0, bytes_cc, st));
         if (rc) break;
-        {
+        if (K > 64) {
+            if ((rc = split_gemm_softmax_jacobian(de, cbl, dd, B, K, D, D, D, Kp, W, t, -1.0f / temperature, csum, st))) break;
+        } else {
+            if ((rc = split_gemm(de, cbl, dd, B, K, D, D, D, Kp, 1.f, 0, 1, st))) break;
             dim3 gT((unsigned)((B + 255) / 256), (unsigned)((Kp / 4 + 255) / 256));
             gumbel_dd_kernel<<<gT, 256, 0, st>>>(W, dd, t, B, K, Kp, 1.0f / temperature, csum);
             RQ_LAUNCHED();
