@@ -272,3 +272,30 @@ def test_mlp_engine_plan_is_cuda_inference_only():
         torch.set_float32_matmul_precision(prev)
     assert [k for k in mlp.state_dict()] == ["mlp.0.weight", "mlp.2.weight", "mlp.4.weight"]
     assert "_tf32_weights" not in mlp.state_dict()
+
+
+def test_host_memory_near_gpu_restores_the_default_policy():
+    """parallel.host_memory_near_gpu: without NUMA information (no GPU here) the block changes nothing; with a node it sets
+    MPOL_PREFERRED for the block and puts MPOL_DEFAULT back afterwards (checked with get_mempolicy)."""
+    import ctypes
+    import platform
+    from rq_vae_recommender_b200 import parallel
+    with parallel.host_memory_near_gpu() as h:
+        assert h.node is None
+    nr_get = {"x86_64": 239, "aarch64": 236}.get(platform.machine())
+    if nr_get is None:
+        return
+    libc = ctypes.CDLL(None, use_errno=True)
+
+    def policy():
+        mode = ctypes.c_int(-1)
+        assert libc.syscall(nr_get, ctypes.byref(mode), None, 0, None, 0) == 0
+        return mode.value
+
+    base = policy()
+    h = parallel.host_memory_near_gpu()
+    h.node = 0                                   # node 0 exists on every Linux host
+    with h:
+        inside = policy() if h.node is not None else None
+    assert policy() == base == 0                 # MPOL_DEFAULT
+    assert inside in (1, None)                   # MPOL_PREFERRED, or the syscall is not permitted in this sandbox
