@@ -126,7 +126,10 @@ def test_gumbel_forward_tensor_core_vs_simt(B, D, K, L, noise):
     assert torch.equal(i3, i2)
 
 
-@pytest.mark.parametrize("B,D,K,L", [(5000, 64, 1024, 4), (4097, 32, 256, 3), (4100, 64, 300, 2), (4500, 32, 1000, 2)])
+@pytest.mark.parametrize("B,D,K,L", [(5000, 64, 1024, 4), (4097, 32, 256, 3), (4100, 64, 300, 2), (4500, 32, 1000, 2),
+                                     # K <= 64: GEMM + streaming Jacobian pass instead of the fused epilogue; K = 70, 257:
+                                     # ragged column tails of the fused epilogue and of the MN-major codebook-gradient GEMMs
+                                     (4200, 64, 48, 2), (4300, 32, 70, 2), (4400, 64, 257, 1)])
 @pytest.mark.parametrize("noise", ["given", "philox"])
 def test_gumbel_backward_tensor_core_vs_thread_per_row(B, D, K, L, noise):
     """rq_quantize_backward in Gumbel mode: the GEMM formulation on the tensor cores against the CUDA-core kernel
