@@ -9,6 +9,9 @@
 // registers -> three 128-byte-swizzled bf16 tiles each), one thread issues the 24 tcgen05.mma of the block, the next
 // block is staged when those have completed (single-buffered: the callers are bound by the [M, N] traffic to HBM or run
 // a handful of K-blocks per CTA).  Epilogue: TMEM -> registers -> 32-byte global stores, or float atomics for split-K.
+#include <cuda.h>
+#include <string.h>
+
 #include "rq_common.cuh"
 #include "rq_kernels.h"
 #include "rq_tc_ptx.cuh"
@@ -282,7 +285,10 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_kernel(SplitGemm
 // The same product for Kd <= 64 (one K-block: the [B, D] x [K, D]^T logits of the Gumbel path) as a persistent kernel:
 // a CTA converts its 256-row B tile ONCE and walks over M tiles with two A buffers and two TMEM accumulators, so the
 // MMAs of tile i + 1 run under the epilogue (128 KB of stores) of tile i.  grid = (N tiles, CTAs per N tile).
-__global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(SplitGemmParams g) {
+// map_c (use_tma != 0): C as a tensor map with 32 x 32 boxes - the epilogue then goes through a swizzled 4 KB staging tile
+// per warp and TMA stores (whole 128-byte lines) instead of thread-per-row 32-byte stores.
+__global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(const __grid_constant__ CUtensorMap map_c,
+                                                                            int use_tma, SplitGemmParams g) {
     using namespace sg;
     constexpr int NT = 256;
     extern __shared__ uint8_t smem_raw[];
@@ -290,10 +296,26 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(Spli
     constexpr int A_PLANE = TM * 128, B_PLANE = NT * 128;
     uint8_t* sB = smem;                                   // [3][256 rows][64 bf16]
     uint8_t* sA = smem + 3 * B_PLANE;                     // [2 buffers][3][128 rows][64 bf16]
-    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 3 * B_PLANE + 6 * A_PLANE);     // [2]
+    uint8_t* my_out = smem + 3 * B_PLANE + 6 * A_PLANE + (threadIdx.x >> 5) * 4096;       // [8 warps][32 rows][128 B]
+    uint64_t* mbar = reinterpret_cast<uint64_t*>(smem + 3 * B_PLANE + 6 * A_PLANE + 8 * 4096);     // [2]
     uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(mbar + 2);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t n0 = (int64_t)blockIdx.x * NT;
+    // 32 values of this thread's row -> staging tile (16-byte pieces XOR-swizzled by the row) -> one TMA store
+    auto put_chunk = [&](const float (&o)[32], int64_t col0, int64_t row0) {
+        if (lane == 0) ptx::bulk_wait_group_read0();
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(my_out + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        ptx::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            ptx::tma_store_2d(&map_c, (int)col0, (int)row0, my_out);
+            ptx::bulk_commit_group();
+        }
+    };
     const int64_t m_tiles = (g.M + TM - 1) / TM;
     const int64_t n_mine = (m_tiles > (int64_t)blockIdx.y) ? (m_tiles - 1 - blockIdx.y) / gridDim.y + 1 : 0;
     if (tid == 0) {
@@ -380,7 +402,9 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(Spli
 #pragma unroll
                 for (int j = 0; j < 32; ++j) o[j] = (row < g.M && j < ncol) ? g.ep_scale * (w[j] * (__uint_as_float(v[j]) - tr)) : 0.f;
                 float* dst = g.C + row * g.ldc + col0;
-                if (fast && ((reinterpret_cast<uintptr_t>(dst) & 31) == 0)) {
+                if (use_tma) {
+                    if (ncol > 0) put_chunk(o, col0, m0 + q * 32);
+                } else if (fast && ((reinterpret_cast<uintptr_t>(dst) & 31) == 0)) {
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) ptx::st_global_v8(dst + j, &o[j]);
                 } else if (row < g.M) {
@@ -397,7 +421,14 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(Spli
             uint32_t v[32];
             ptx::tmem_ld_32x32b_x32(trow + c, v);
             ptx::tmem_ld_wait_for(v);
-            if (row < g.M) {
+            if (use_tma) {
+                if (n0 + h * HALF + c < g.N) {
+                    float o[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) o[j] = g.alpha * __uint_as_float(v[j]);
+                    put_chunk(o, n0 + h * HALF + c, m0 + q * 32);
+                }
+            } else if (row < g.M) {
                 float* dst = g.C + row * g.ldc + n0 + h * HALF + c;
                 const int64_t ncol = g.N - (n0 + h * HALF + c);
                 if (ncol >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 31) == 0)) {
@@ -416,6 +447,7 @@ __global__ void __launch_bounds__(sg::THREADS, 1) rq_split_gemm_bres_kernel(Spli
             }
         }
     }
+    if (use_tma && lane == 0) ptx::bulk_wait_group0();
     if (g.ep_w && g.ep_csum) {                                       // this CTA's column sums: one atomic per warp and column
         const int h = warp >> 2;
 #pragma unroll
@@ -457,9 +489,12 @@ int split_gemm(const float* A, const float* B, float* C, int64_t M, int64_t N, i
         unsigned per = (unsigned)sm_count() / gn;
         if (per < 1) per = 1;
         if (per > gm) per = gm;
-        const size_t smem = 3 * 256 * 128 + 6 * sg::TM * 128 + 64 + 1024;
+        const size_t smem = 3 * 256 * 128 + 6 * sg::TM * 128 + 8 * 4096 + 64 + 1024;
         RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_bres_kernel, (int)smem));
-        rq_split_gemm_bres_kernel<<<dim3(gn, per), sg::THREADS, smem, st>>>(g);
+        CUtensorMap mc;
+        const int use_tma = (!(ldc & 3) && !((uintptr_t)C & 15) && make_tensor_map_f32(&mc, C, M, N, ldc, 32)) ? 1 : 0;
+        if (!use_tma) memset(&mc, 0, sizeof(mc));
+        rq_split_gemm_bres_kernel<<<dim3(gn, per), sg::THREADS, smem, st>>>(mc, use_tma, g);
     } else if (N > 64) {
         constexpr int NT = 256;
         const size_t smem = 3 * sg::TM * 128 + 3 * NT * 128 + 64 + 1024;
@@ -503,9 +538,12 @@ int split_gemm_softmax_jacobian(const float* A, const float* B, float* C, int64_
     unsigned per = (unsigned)sm_count() / gn;
     if (per < 1) per = 1;
     if (per > gm) per = gm;
-    const size_t smem = 3 * 256 * 128 + 6 * sg::TM * 128 + 64 + 1024;
+    const size_t smem = 3 * 256 * 128 + 6 * sg::TM * 128 + 8 * 4096 + 64 + 1024;
     RQ_CUDA(ensure_max_dynamic_smem((const void*)rq_split_gemm_bres_kernel, (int)smem));
-    rq_split_gemm_bres_kernel<<<dim3(gn, per), sg::THREADS, smem, st>>>(g);
+    CUtensorMap mc;
+    const int use_tma = (!((uintptr_t)C & 15) && make_tensor_map_f32(&mc, C, M, N, ldc, 32)) ? 1 : 0;
+    if (!use_tma) memset(&mc, 0, sizeof(mc));
+    rq_split_gemm_bres_kernel<<<dim3(gn, per), sg::THREADS, smem, st>>>(mc, use_tma, g);
     RQ_LAUNCHED();
     return 0;
 }

@@ -100,4 +100,8 @@ bool linear_tf32_supported(int64_t M, int N, int Kd, int act);
 int linear_act_tf32(const float* X, const float* W, float* Y, int64_t M, int N, int Kd, int act, cudaStream_t st);
 int linear_tf32_timeout_flag();
 
+// rq_linear_tf32.cu: cuTensorMapEncodeTiled for a row-major fp32 matrix (boxes of box_rows x 32 floats, 128-byte swizzle);
+// `map` is a CUtensorMap*
+bool make_tensor_map_f32(void* map, const float* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+
 }  // namespace rq

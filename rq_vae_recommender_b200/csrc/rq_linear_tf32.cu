@@ -402,6 +402,12 @@ static bool make_map(CUtensorMap* m, const float* base, int64_t rows, int64_t co
 }
 }  // namespace lt
 
+// Shared with the Gumbel GEMMs (rq_gemm_split.cu): a 2-D fp32 tensor map with box_rows x 32-float boxes, 128-byte swizzle.
+// `map` points to a CUtensorMap (declared void* in rq_kernels.h, which does not include <cuda.h>).
+bool make_tensor_map_f32(void* map, const float* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+    return lt::make_map(reinterpret_cast<CUtensorMap*>(map), base, rows, cols, ld, box_rows);
+}
+
 bool linear_tf32_supported(int64_t M, int N, int Kd, int act_flags) {
     const int act = act_flags & ~(RQ_ACT_TF32_OUT | RQ_ACT_CTA_PAIR);
     if (M < 1 || N < 8 || Kd < 4 || (N & 3) || (Kd & 3)) return false;          // 16-byte rows for TMA and the stores
